@@ -1,0 +1,252 @@
+"""ctypes binding of the C-ABI in include/ebt.h (libebt_cuda.so).
+
+This is the product path used by tests and bench.py: every computing call goes
+into the CUDA library.  There is no CPU fallback — if the library is missing
+``load()`` raises, and without a GPU ``Tracker()`` raises ``EbtError``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from .records import EVENT, OPT_RECORD, PATCH_PIXELS, PROBLEM, SOLUTION, TRACK
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libebt_cuda.so")
+_vp = C.c_void_p
+
+
+class EbtError(RuntimeError):
+    pass
+
+
+class Params(C.Structure):
+    _fields_ = [
+        ("width", C.c_int32), ("height", C.c_int32), ("max_patches", C.c_int32),
+        ("init_num_events", C.c_int32), ("min_num_events", C.c_int32),
+        ("max_num_events", C.c_int32), ("batch_stride", C.c_int32),
+        ("max_iterations", C.c_int32), ("border_margin", C.c_int32),
+        ("record_capacity", C.c_int32),
+        ("association_distance", C.c_double), ("huber_loss", C.c_double),
+        ("optimizer_threshold", C.c_double),
+    ]
+
+
+EXPORTS = {
+    "ebt_default_params": (C.c_int, [C.POINTER(Params), C.c_int, C.c_int]),
+    "ebt_create": (C.c_int, [C.POINTER(Params), C.c_int, C.POINTER(_vp)]),
+    "ebt_destroy": (C.c_int, [_vp]),
+    "ebt_last_error": (C.c_char_p, [_vp]),
+    "ebt_new_frame_begin": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int]),
+    "ebt_get_uninit": (C.c_int, [_vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]),
+    "ebt_set_flow": (C.c_int, [_vp, C.c_int32, C.c_int, C.c_float, C.c_float]),
+    "ebt_new_frame_end": (C.c_int, [_vp]),
+    "ebt_push_events": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
+    "ebt_push_events_device": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
+    "ebt_get_tracks": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.POINTER(C.c_int)]),
+    "ebt_get_patch": (C.c_int, [_vp, C.c_int32, C.c_int, _vp]),
+    "ebt_get_trajectory": (C.c_int, [_vp, C.c_int32, _vp, C.c_int, C.POINTER(C.c_int)]),
+    "ebt_get_final_costs": (C.c_int, [_vp, C.c_int32, _vp, C.c_int, C.POINTER(C.c_int)]),
+    "ebt_get_records": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
+    "ebt_clear_records": (C.c_int, [_vp]),
+    "ebt_get_gradients": (C.c_int, [_vp, _vp, _vp]),
+    "ebt_frames_add": (C.c_int, [_vp, _vp]),
+    "ebt_frames_get": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "ebt_optimize_batch": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int64, _vp, _vp]),
+    "ebt_optimize_batch_device": (C.c_int, [_vp, _vp, C.c_int64, _vp, _vp, _vp]),
+    "ebt_sync": (C.c_int, [_vp]),
+    "ebt_timing_enable": (C.c_int, [_vp, C.c_int]),
+    "ebt_timing_get": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
+    "ebt_timing_reset": (C.c_int, [_vp]),
+    "ebt_sizeof_event": (C.c_size_t, []),
+    "ebt_sizeof_track": (C.c_size_t, []),
+    "ebt_sizeof_opt_record": (C.c_size_t, []),
+    "ebt_sizeof_problem": (C.c_size_t, []),
+    "ebt_sizeof_solution": (C.c_size_t, []),
+    "ebt_sizeof_params": (C.c_size_t, []),
+    "ebt_abi_version": (C.c_int, []),
+}
+
+_lib = None
+
+
+def load():
+    """Load libebt_cuda.so; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise EbtError(f"{LIB_PATH} not built: run __graft_entry__.build() "
+                           "(make -C event_based_odomety_b200/csrc)")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in EXPORTS.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return _vp(a)
+    return a.ctypes.data_as(_vp)
+
+
+K_TRACK, K_BATCH, K_GRAD, K_NUMEV = 0, 1, 2, 3
+
+
+class Tracker:
+    """One tracker context = one CUDA device + one stream (ebt_ctx)."""
+
+    def __init__(self, width, height, max_patches=100, device=0, **overrides):
+        self.lib = load()
+        self.width, self.height = width, height
+        self.params = Params()
+        self.lib.ebt_default_params(C.byref(self.params), width, height)
+        self.params.max_patches = max_patches
+        for k, v in overrides.items():
+            setattr(self.params, k, v)
+        self.ctx = _vp()
+        rc = self.lib.ebt_create(C.byref(self.params), device, C.byref(self.ctx))
+        if rc != 0:
+            msg = self.lib.ebt_last_error(None)
+            self.ctx = None
+            raise EbtError(f"ebt_create failed ({rc}): {msg.decode() if msg else ''}")
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.ebt_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        self.close()
+
+    def _ck(self, rc):
+        if rc < 0:
+            raise EbtError(f"ebt error {rc}: {self.lib.ebt_last_error(self.ctx).decode()}")
+        return rc
+
+    # ---- per-frame ------------------------------------------------------
+    def new_frame_begin(self, gray, ts, corners):
+        gray = np.ascontiguousarray(gray, np.uint8)
+        assert gray.shape == (self.height, self.width)
+        corners = np.ascontiguousarray(corners, np.float64).reshape(-1, 2)
+        self._ck(self.lib.ebt_new_frame_begin(self.ctx, _ptr(gray), int(ts), _ptr(corners),
+                                              len(corners)))
+
+    def get_uninit(self, cap=8192):
+        ids = np.zeros(cap, np.int32)
+        xy = np.zeros((cap, 2))
+        n = C.c_int()
+        self._ck(self.lib.ebt_get_uninit(self.ctx, _ptr(ids), _ptr(xy), cap, C.byref(n)))
+        return ids[:n.value].copy(), xy[:n.value].copy()
+
+    def set_flow(self, track_id, found, nx, ny):
+        self._ck(self.lib.ebt_set_flow(self.ctx, int(track_id), int(found), float(nx), float(ny)))
+
+    def new_frame_end(self):
+        self._ck(self.lib.ebt_new_frame_end(self.ctx))
+
+    # ---- events ---------------------------------------------------------
+    def push_events(self, events):
+        events = np.ascontiguousarray(events)
+        assert events.dtype == EVENT
+        n = C.c_int64()
+        self._ck(self.lib.ebt_push_events(self.ctx, _ptr(events), len(events), C.byref(n)))
+        return n.value
+
+    def push_events_ptr(self, host_ptr, n_events):
+        n = C.c_int64()
+        self._ck(self.lib.ebt_push_events(self.ctx, _vp(host_ptr), n_events, C.byref(n)))
+        return n.value
+
+    def push_events_device(self, dev_ptr, n_events):
+        n = C.c_int64()
+        self._ck(self.lib.ebt_push_events_device(self.ctx, _vp(dev_ptr), n_events, C.byref(n)))
+        return n.value
+
+    # ---- getters --------------------------------------------------------
+    def tracks(self, archived=False):
+        n = C.c_int()
+        self._ck(self.lib.ebt_get_tracks(self.ctx, None, 0, int(archived), C.byref(n)))
+        out = np.zeros(max(n.value, 1), TRACK)
+        self._ck(self.lib.ebt_get_tracks(self.ctx, _ptr(out), n.value, int(archived), C.byref(n)))
+        return out[:n.value]
+
+    def records(self):
+        n = C.c_int64()
+        self._ck(self.lib.ebt_get_records(self.ctx, None, 0, C.byref(n)))
+        out = np.zeros(max(n.value, 1), OPT_RECORD)
+        self._ck(self.lib.ebt_get_records(self.ctx, _ptr(out), n.value, C.byref(n)))
+        return out[:n.value]
+
+    def clear_records(self):
+        self._ck(self.lib.ebt_clear_records(self.ctx))
+
+    def patch(self, track_id, which=0):
+        out = np.zeros(PATCH_PIXELS)
+        self._ck(self.lib.ebt_get_patch(self.ctx, int(track_id), which, _ptr(out)))
+        return out
+
+    def trajectory(self, track_id):
+        n = C.c_int()
+        self._ck(self.lib.ebt_get_trajectory(self.ctx, int(track_id), None, 0, C.byref(n)))
+        out = np.zeros((max(n.value, 1), 3))
+        self._ck(self.lib.ebt_get_trajectory(self.ctx, int(track_id), _ptr(out), n.value, C.byref(n)))
+        return out[:n.value]
+
+    def final_costs(self, track_id):
+        n = C.c_int()
+        self._ck(self.lib.ebt_get_final_costs(self.ctx, int(track_id), None, 0, C.byref(n)))
+        out = np.zeros(max(n.value, 1))
+        self._ck(self.lib.ebt_get_final_costs(self.ctx, int(track_id), _ptr(out), n.value, C.byref(n)))
+        return out[:n.value]
+
+    def gradients(self):
+        gx = np.zeros((self.height, self.width))
+        gy = np.zeros((self.height, self.width))
+        self._ck(self.lib.ebt_get_gradients(self.ctx, _ptr(gx), _ptr(gy)))
+        return gx, gy
+
+    # ---- batched --------------------------------------------------------
+    def add_frame(self, gray):
+        gray = np.ascontiguousarray(gray, np.uint8)
+        assert gray.shape == (self.height, self.width)
+        return self._ck(self.lib.ebt_frames_add(self.ctx, _ptr(gray)))
+
+    def frame_gradients(self, slot):
+        gx = np.zeros((self.height, self.width))
+        gy = np.zeros((self.height, self.width))
+        self._ck(self.lib.ebt_frames_get(self.ctx, slot, _ptr(gx), _ptr(gy)))
+        return gx, gy
+
+    def optimize_batch(self, problems, events, want_nabla=True):
+        problems = np.ascontiguousarray(problems)
+        events = np.ascontiguousarray(events)
+        assert problems.dtype == PROBLEM and events.dtype == EVENT
+        sol = np.zeros(len(problems), SOLUTION)
+        nabla = np.zeros((len(problems), PATCH_PIXELS), np.int32) if want_nabla else None
+        self._ck(self.lib.ebt_optimize_batch(self.ctx, _ptr(problems), len(problems), _ptr(events),
+                                             len(events), _ptr(sol), _ptr(nabla)))
+        return sol, nabla
+
+    def optimize_batch_device(self, d_problems, n, d_events, d_solutions, d_nabla=0):
+        self._ck(self.lib.ebt_optimize_batch_device(self.ctx, _vp(d_problems), n, _vp(d_events),
+                                                    _vp(d_solutions), _vp(d_nabla) if d_nabla else None))
+
+    def sync(self):
+        self._ck(self.lib.ebt_sync(self.ctx))
+
+    def timing(self, on=True):
+        self._ck(self.lib.ebt_timing_enable(self.ctx, int(on)))
+        self._ck(self.lib.ebt_timing_reset(self.ctx))
+
+    def timing_get(self, kernel):
+        ms = C.c_double()
+        n = C.c_int64()
+        self._ck(self.lib.ebt_timing_get(self.ctx, kernel, C.byref(ms), C.byref(n)))
+        return ms.value, n.value

@@ -1,0 +1,864 @@
+// ebt_api.cu — host side of the C-ABI declared in include/ebt.h.
+//
+// Owns device memory, the per-frame host logic of tracker::FeatureDetector
+// (association, archiving, flow injection; /root/reference/implementation/
+// feature_tracker/src/feature_detector.cpp:493-566, 630-664) and launches the
+// kernels of ebt_kernels.cu.  No CPU implementation of the hot path lives
+// here: every entry point that computes does so on the GPU or fails.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/ebt.h"
+#include "ebt_device_types.h"
+#include "ebt_kernels.h"
+
+namespace
+{
+std::string g_create_error;
+
+struct HostTrack
+{
+	std::vector<double> traj;   // (x, y, ts) triples: Patch::trajectory_
+	std::vector<double> costs;  // Patch::finalCosts_
+};
+
+struct Frame
+{
+	double2* grid = nullptr;
+	int64_t ts = 0;
+	long long users = 0;  // Optimizer::used_
+	bool alive = false;
+};
+
+enum
+{
+	K_TRACK = 0,
+	K_BATCH = 1,
+	K_GRAD = 2,
+	K_NUMEV = 3,
+	K_COUNT = 4
+};
+}  // namespace
+
+struct ebt_ctx
+{
+	ebt_params prm;
+	DevParams dp;
+	int device = 0;
+	cudaStream_t stream = nullptr;
+	std::string err;
+
+	Frame frames[EBT_MAX_FRAMES];
+	int latest = 0;
+
+	std::vector<DevPatch> h;        // FeatureDetector::patches_ (list order)
+	std::vector<HostTrack> tracks;  // parallel to h
+	std::vector<DevPatch> arch;     // FeatureDetector::archivedPatches_
+	std::vector<HostTrack> arch_tracks;
+	std::vector<std::vector<int>> arch_nabla;
+	std::vector<int> free_slots;
+	bool host_dirty = true;  // h holds changes the device has not seen
+	int next_track_id = 0;
+	int image_counter = 0;  // FlowEstimator::imageCounter_
+	int64_t event_index = 0;
+
+	DevPatch* d_patches = nullptr;
+	ebt_event* d_rings = nullptr;
+	int* d_nablas = nullptr;
+	ebt_opt_record* d_records = nullptr;
+	unsigned long long* d_nrec = nullptr;
+	std::vector<ebt_opt_record> records;
+
+	ebt_event* d_events = nullptr;
+	size_t d_events_cap = 0;
+	unsigned char* d_gray = nullptr;
+	double* d_lut = nullptr;
+
+	ebt_problem* d_problems = nullptr;
+	ebt_solution* d_solutions = nullptr;
+	int* d_bnabla = nullptr;
+	ebt_event* d_bevents = nullptr;
+	size_t cap_problems = 0, cap_bnabla = 0, cap_bevents = 0;
+
+	bool timing = false;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	double ms[K_COUNT] = {0, 0, 0, 0};
+	int64_t launches[K_COUNT] = {0, 0, 0, 0};
+};
+
+namespace
+{
+int fail(ebt_ctx* c, int code, const std::string& msg)
+{
+	if (c)
+		c->err = msg;
+	else
+		g_create_error = msg;
+	return code;
+}
+
+#define CU(call)                                                                          \
+	do                                                                                    \
+	{                                                                                     \
+		cudaError_t e_ = (call);                                                          \
+		if (e_ != cudaSuccess)                                                            \
+			return fail(ctx, EBT_E_CUDA,                                                  \
+						std::string(#call) + ": " + cudaGetErrorString(e_));             \
+	} while (0)
+
+FrameTable frameTable(const ebt_ctx* c)
+{
+	FrameTable ft;
+	for (int i = 0; i < EBT_MAX_FRAMES; ++i) ft.grid[i] = c->frames[i].grid;
+	ft.latest = c->latest;
+	ft.pad = 0;
+	return ft;
+}
+
+void tic(ebt_ctx* c)
+{
+	if (c->timing) cudaEventRecord(c->ev0, c->stream);
+}
+void toc(ebt_ctx* c, int k)
+{
+	c->launches[k]++;
+	if (!c->timing) return;
+	cudaEventRecord(c->ev1, c->stream);
+	cudaEventSynchronize(c->ev1);
+	float ms = 0;
+	cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+	c->ms[k] += ms;
+}
+
+void cornerOf(const DevPatch& p, double& x, double& y)
+{
+	x = p.rx + (EBT_PATCH_SIDE - 1) / 2.;
+	y = p.ry + (EBT_PATCH_SIDE - 1) / 2.;
+}
+
+void addTraj(const DevPatch& p, HostTrack& t)
+{
+	double x, y;
+	cornerOf(p, x, y);
+	t.traj.push_back(x);
+	t.traj.push_back(y);
+	t.traj.push_back(static_cast<double>(p.cur_ts));
+}
+
+int findFrame(const ebt_ctx* c, int64_t ts)
+{
+	for (int i = 0; i < EBT_MAX_FRAMES; ++i)
+		if (c->frames[i].alive && c->frames[i].ts == ts) return i;
+	return -1;
+}
+
+// Upload one gray frame and build its gradient grid in `slot`.
+int buildGrid(ebt_ctx* ctx, const uint8_t* gray, int slot)
+{
+	const size_t npx = static_cast<size_t>(ctx->prm.width) * ctx->prm.height;
+	Frame& f = ctx->frames[slot];
+	if (!f.grid) CU(cudaMalloc(&f.grid, npx * sizeof(double2)));
+	CU(cudaMemcpyAsync(ctx->d_gray, gray, npx, cudaMemcpyHostToDevice, ctx->stream));
+	tic(ctx);
+	CU(ebt_launch_grad(ctx->d_gray, ctx->d_lut, ctx->prm.width, ctx->prm.height, f.grid,
+					   ctx->stream));
+	toc(ctx, K_GRAD);
+	CU(cudaStreamSynchronize(ctx->stream));
+	return EBT_OK;
+}
+
+int uploadPatches(ebt_ctx* ctx)
+{
+	if (!ctx->host_dirty || ctx->h.empty())
+	{
+		ctx->host_dirty = false;
+		return EBT_OK;
+	}
+	CU(cudaMemcpyAsync(ctx->d_patches, ctx->h.data(), ctx->h.size() * sizeof(DevPatch),
+					   cudaMemcpyHostToDevice, ctx->stream));
+	ctx->host_dirty = false;
+	return EBT_OK;
+}
+
+int downloadPatches(ebt_ctx* ctx)
+{
+	if (ctx->h.empty()) return EBT_OK;
+	CU(cudaMemcpyAsync(ctx->h.data(), ctx->d_patches, ctx->h.size() * sizeof(DevPatch),
+					   cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return EBT_OK;
+}
+
+void fillTrack(const DevPatch& p, const HostTrack& t, ebt_track& o)
+{
+	std::memset(&o, 0, sizeof(o));
+	o.track_id = p.track_id;
+	o.lost = p.lost;
+	o.init = p.init;
+	o.num_of_events = p.num_of_events;
+	o.counter = p.counter;
+	o.window_size = p.win_size;
+	o.n_optimizations = static_cast<int32_t>(t.costs.size());
+	o.n_trajectory = static_cast<int32_t>(t.traj.size() / 3);
+	o.rect_x = p.rx;
+	o.rect_y = p.ry;
+	o.init_x = p.ix;
+	o.init_y = p.iy;
+	std::memcpy(o.warp, p.warp, sizeof(o.warp));
+	o.flow_dir = p.init ? static_cast<double>(static_cast<float>(p.flow)) : 0.0;
+	o.last_cost = t.costs.empty() ? 0.0 : t.costs.back();
+	o.current_ts = p.cur_ts;
+	o.time_last_update = p.time_last_update;
+	o.time_without_update = p.time_without_update;
+	o.init_time = p.init_time;
+}
+}  // namespace
+
+extern "C" {
+
+int ebt_default_params(ebt_params* p, int width, int height)
+{
+	if (!p || width <= 0 || height <= 0) return EBT_E_INVALID;
+	std::memset(p, 0, sizeof(*p));
+	p->width = width;
+	p->height = height;
+	p->max_patches = 100;
+	p->init_num_events = 75;
+	p->min_num_events = 100;
+	p->max_num_events = 300;
+	p->batch_stride = 30;
+	p->max_iterations = 10;
+	p->border_margin = 5;
+	p->record_capacity = 1 << 18;
+	p->association_distance = 5.0;
+	p->huber_loss = 0.3;
+	p->optimizer_threshold = 0.6;
+	return EBT_OK;
+}
+
+const char* ebt_last_error(const ebt_ctx* ctx)
+{
+	return ctx ? ctx->err.c_str() : g_create_error.c_str();
+}
+
+int ebt_destroy(ebt_ctx* ctx)
+{
+	if (!ctx) return EBT_E_INVALID;
+	cudaSetDevice(ctx->device);
+	for (auto& f : ctx->frames) cudaFree(f.grid);
+	cudaFree(ctx->d_patches);
+	cudaFree(ctx->d_rings);
+	cudaFree(ctx->d_nablas);
+	cudaFree(ctx->d_records);
+	cudaFree(ctx->d_nrec);
+	cudaFree(ctx->d_events);
+	cudaFree(ctx->d_gray);
+	cudaFree(ctx->d_lut);
+	cudaFree(ctx->d_problems);
+	cudaFree(ctx->d_solutions);
+	cudaFree(ctx->d_bnabla);
+	cudaFree(ctx->d_bevents);
+	if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+	if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+	if (ctx->stream) cudaStreamDestroy(ctx->stream);
+	delete ctx;
+	return EBT_OK;
+}
+
+int ebt_create(const ebt_params* params, int device, ebt_ctx** out)
+{
+	ebt_ctx* ctx = nullptr;  // errors before allocation go to g_create_error
+	if (!params || !out) return fail(ctx, EBT_E_INVALID, "ebt_create: null argument");
+	if (params->width <= 0 || params->height <= 0 || params->max_patches <= 0 ||
+		params->max_num_events > EBT_MAX_WINDOW || params->min_num_events < 1 ||
+		params->min_num_events > params->max_num_events || params->record_capacity <= 0)
+		return fail(ctx, EBT_E_INVALID, "ebt_create: invalid parameters");
+	int n_dev = 0;
+	if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0)
+		return fail(ctx, EBT_E_NODEVICE,
+					"ebt_create: no CUDA device (this library has no CPU fallback)");
+	if (device < 0 || device >= n_dev) return fail(ctx, EBT_E_INVALID, "ebt_create: bad device index");
+	{
+		cudaError_t e = cudaSetDevice(device);
+		if (e != cudaSuccess)
+			return fail(ctx, EBT_E_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+	}
+	ebt_ctx* c = new ebt_ctx();
+	c->prm = *params;
+	c->device = device;
+	DevParams& d = c->dp;
+	d.width = params->width;
+	d.height = params->height;
+	d.max_iterations = params->max_iterations;
+	d.init_num_events = params->init_num_events;
+	d.min_num_events = params->min_num_events;
+	d.max_num_events = params->max_num_events;
+	d.batch_stride = params->batch_stride;
+	d.border_margin = params->border_margin;
+	d.huber_a = params->huber_loss;
+	d.optimizer_threshold = params->optimizer_threshold;
+	// Ceres 2.0 Solver::Options defaults (ceres/include/ceres/solver.h:264-322)
+	d.initial_radius = 1e4;
+	d.max_radius = 1e16;
+	d.min_radius = 1e-32;
+	d.min_relative_decrease = 1e-3;
+	d.min_lm_diagonal = 1e-6;
+	d.max_lm_diagonal = 1e32;
+	d.function_tolerance = 1e-6;
+	d.gradient_tolerance = 1e-10;
+	d.parameter_tolerance = 1e-8;
+	d.max_consecutive_nonmonotonic_steps = 5;
+	d.max_consecutive_invalid_steps = 5;
+
+	ctx = c;
+	const size_t P = static_cast<size_t>(params->max_patches);
+	const size_t npx = static_cast<size_t>(params->width) * params->height;
+#define CUC(call)                                                                         \
+	do                                                                                    \
+	{                                                                                     \
+		cudaError_t e_ = (call);                                                          \
+		if (e_ != cudaSuccess)                                                            \
+		{                                                                                 \
+			g_create_error = std::string(#call) + ": " + cudaGetErrorString(e_);         \
+			ebt_destroy(c);                                                               \
+			return EBT_E_CUDA;                                                            \
+		}                                                                                 \
+	} while (0)
+	CUC(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+	CUC(cudaEventCreate(&c->ev0));
+	CUC(cudaEventCreate(&c->ev1));
+	CUC(cudaMalloc(&c->d_patches, P * sizeof(DevPatch)));
+	CUC(cudaMalloc(&c->d_rings, P * EBT_RING * sizeof(ebt_event)));
+	CUC(cudaMalloc(&c->d_nablas, P * EBT_PATCH_PIXELS * sizeof(int)));
+	CUC(cudaMemset(c->d_nablas, 0, P * EBT_PATCH_PIXELS * sizeof(int)));
+	CUC(cudaMalloc(&c->d_records, static_cast<size_t>(params->record_capacity) * sizeof(ebt_opt_record)));
+	CUC(cudaMalloc(&c->d_nrec, sizeof(unsigned long long)));
+	CUC(cudaMalloc(&c->d_gray, npx));
+	CUC(cudaMalloc(&c->d_lut, 256 * sizeof(double)));
+	{
+		// FeatureDetector::getLogImage (feature_detector.cpp:714-723): the input
+		// is 8-bit, so log(I/255 + 0.1)/8 is a 256-entry table, computed once on
+		// the host with the same libm the reference uses.
+		double lut[256];
+		for (int i = 0; i < 256; ++i)
+		{
+			volatile double v = i * (1.0 / 255.0);  // convertTo, then "+ 10e-2": two roundings
+			v = v + 10e-2;
+			lut[i] = std::log(v) * (1.0 / 8);
+		}
+		CUC(cudaMemcpy(c->d_lut, lut, sizeof(lut), cudaMemcpyHostToDevice));
+	}
+#undef CUC
+	for (int s = static_cast<int>(P) - 1; s >= 0; --s) c->free_slots.push_back(s);
+	*out = c;
+	return EBT_OK;
+}
+
+int ebt_sync(ebt_ctx* ctx)
+{
+	if (!ctx) return EBT_E_INVALID;
+	CU(cudaSetDevice(ctx->device));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return EBT_OK;
+}
+
+int ebt_timing_enable(ebt_ctx* ctx, int on)
+{
+	if (!ctx) return EBT_E_INVALID;
+	ctx->timing = on != 0;
+	return EBT_OK;
+}
+int ebt_timing_reset(ebt_ctx* ctx)
+{
+	if (!ctx) return EBT_E_INVALID;
+	for (int k = 0; k < K_COUNT; ++k)
+	{
+		ctx->ms[k] = 0;
+		ctx->launches[k] = 0;
+	}
+	return EBT_OK;
+}
+int ebt_timing_get(ebt_ctx* ctx, int kernel, double* ms_total, int64_t* launches)
+{
+	if (!ctx || kernel < 0 || kernel >= K_COUNT) return EBT_E_INVALID;
+	if (ms_total) *ms_total = ctx->ms[kernel];
+	if (launches) *launches = ctx->launches[kernel];
+	return EBT_OK;
+}
+
+size_t ebt_sizeof_event(void) { return sizeof(ebt_event); }
+size_t ebt_sizeof_track(void) { return sizeof(ebt_track); }
+size_t ebt_sizeof_opt_record(void) { return sizeof(ebt_opt_record); }
+size_t ebt_sizeof_problem(void) { return sizeof(ebt_problem); }
+size_t ebt_sizeof_solution(void) { return sizeof(ebt_solution); }
+size_t ebt_sizeof_params(void) { return sizeof(ebt_params); }
+int ebt_abi_version(void) { return 1; }
+
+// FeatureDetector::newImage, first half: extractPatches (feature_detector.cpp:
+// 543-566) with injected corners, associatePatches (:630-664).
+int ebt_new_frame_begin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us, const double* cornersXY,
+						int n_corners)
+{
+	if (!ctx || !gray || n_corners < 0 || (n_corners > 0 && !cornersXY))
+		return fail(ctx, EBT_E_INVALID, "ebt_new_frame_begin: bad argument");
+	CU(cudaSetDevice(ctx->device));
+	int slot = findFrame(ctx, ts_us);
+	for (int i = 0; i < EBT_MAX_FRAMES && slot < 0; ++i)
+		if (!ctx->frames[i].alive) slot = i;
+	if (slot < 0) return fail(ctx, EBT_E_CAPACITY, "ebt_new_frame_begin: too many live template frames");
+	{
+		const int rc = buildGrid(ctx, gray, slot);
+		if (rc != EBT_OK) return rc;
+	}
+	Frame& f = ctx->frames[slot];
+	f.ts = ts_us;
+	f.users = 0;
+	f.alive = true;
+	ctx->latest = slot;
+
+	std::vector<int> newIds(static_cast<size_t>(n_corners), -1);
+	for (size_t i = 0; i < ctx->h.size(); ++i)
+	{
+		DevPatch& p = ctx->h[i];
+		double cx, cy;
+		cornerOf(p, cx, cy);
+		for (int j = 0; j < n_corners; ++j)
+		{
+			const double dx = cx - cornersXY[2 * j], dy = cy - cornersXY[2 * j + 1];
+			if (newIds[j] == -1 && std::sqrt(dx * dx + dy * dy) < ctx->prm.association_distance)
+			{
+				newIds[j] = p.track_id;
+				break;
+			}
+		}
+		p.cur_ts = ts_us;  // Patch::setTs
+		addTraj(p, ctx->tracks[i]);
+	}
+	for (int j = 0; j < n_corners; ++j)
+	{
+		if (newIds[j] != -1 || static_cast<int>(ctx->h.size()) >= ctx->prm.max_patches) continue;
+		// Patch::Patch + init (patch.cpp:8-35)
+		DevPatch p;
+		std::memset(&p, 0, sizeof(p));
+		p.rx = cornersXY[2 * j] - EBT_PATCH_EXTENT;
+		p.ry = cornersXY[2 * j + 1] - EBT_PATCH_EXTENT;
+		cornerOf(p, p.ix, p.iy);
+		p.warp[0] = 1.0;
+		p.cur_ts = ts_us;
+		p.time_without_update = static_cast<long long>(1e7);
+		p.init_time = ts_us;
+		p.track_id = ctx->next_track_id++;
+		p.num_of_events = 75;  // patch.cpp:22
+		p.frame_slot = slot;
+		p.store_slot = ctx->free_slots.back();
+		ctx->free_slots.pop_back();
+		HostTrack t;
+		addTraj(p, t);
+		ctx->h.push_back(p);
+		ctx->tracks.push_back(std::move(t));
+		f.users++;
+	}
+	if (ctx->image_counter < 2) ctx->image_counter++;  // FlowEstimator::addImage
+	ctx->host_dirty = true;
+	return EBT_OK;
+}
+
+// FlowEstimator::getFlowPatches, query side (flow_estimator.cpp:27-39).
+int ebt_get_uninit(ebt_ctx* ctx, int32_t* track_ids, double* cornersXY, int cap, int* n_out)
+{
+	if (!ctx || !n_out) return fail(ctx, EBT_E_INVALID, "ebt_get_uninit: bad argument");
+	int n = 0;
+	if (ctx->image_counter == 2)
+		for (const DevPatch& p : ctx->h)
+		{
+			if (p.init) continue;
+			if (n < cap && track_ids && cornersXY)
+			{
+				track_ids[n] = p.track_id;
+				cornerOf(p, cornersXY[2 * n], cornersXY[2 * n + 1]);
+			}
+			++n;
+		}
+	*n_out = n;
+	return EBT_OK;
+}
+
+// Loop body of FlowEstimator::getFlowPatches (flow_estimator.cpp:41-79).
+int ebt_set_flow(ebt_ctx* ctx, int32_t track_id, int found, float next_x, float next_y)
+{
+	if (!ctx) return EBT_E_INVALID;
+	for (DevPatch& p : ctx->h)
+	{
+		if (p.track_id != track_id || p.init) continue;
+		ctx->host_dirty = true;
+		if (!found)
+		{
+			p.lost = 1;
+			return EBT_OK;
+		}
+		double cx, cy;
+		cornerOf(p, cx, cy);
+		const double dx = next_x - cx, dy = next_y - cy;
+		p.warp[0] = 1.0;
+		p.warp[1] = 0.0;
+		p.warp[2] = -dx;
+		p.warp[3] = -dy;
+		p.flow = std::atan2(dy, dx);
+		p.init = 1;
+		p.time_without_update = static_cast<long long>(1e6 / std::fmax(1e-1, std::sqrt(dx * dx + dy * dy)));
+		if (cx <= 5 || cy <= 5 || cx >= ctx->prm.width - 5 || cy >= ctx->prm.height - 5) p.lost = 1;
+		return EBT_OK;
+	}
+	return fail(ctx, EBT_E_INVALID, "ebt_set_flow: no uninitialised patch with this track id");
+}
+
+// FeatureDetector::newImage, second half (feature_detector.cpp:499-535).
+int ebt_new_frame_end(ebt_ctx* ctx)
+{
+	if (!ctx) return EBT_E_INVALID;
+	CU(cudaSetDevice(ctx->device));
+	if (!ctx->h.empty())
+	{
+		const int rc = uploadPatches(ctx);
+		if (rc != EBT_OK) return rc;
+		tic(ctx);
+		CU(ebt_launch_num_events(ctx->d_patches, static_cast<int>(ctx->h.size()), frameTable(ctx),
+								 ctx->dp, ctx->stream));
+		toc(ctx, K_NUMEV);
+		const int rc2 = downloadPatches(ctx);
+		if (rc2 != EBT_OK) return rc2;
+	}
+	// archive lost patches, keep list order (feature_detector.cpp:512-523)
+	size_t k = 0;
+	bool moved = false;
+	for (size_t i = 0; i < ctx->h.size(); ++i)
+	{
+		if (ctx->h[i].lost)
+		{
+			std::vector<int> nab(EBT_PATCH_PIXELS);
+			CU(cudaMemcpy(nab.data(), ctx->d_nablas + static_cast<size_t>(ctx->h[i].store_slot) * EBT_PATCH_PIXELS,
+						  EBT_PATCH_PIXELS * sizeof(int), cudaMemcpyDeviceToHost));
+			CU(cudaMemset(ctx->d_nablas + static_cast<size_t>(ctx->h[i].store_slot) * EBT_PATCH_PIXELS, 0,
+						  EBT_PATCH_PIXELS * sizeof(int)));
+			ctx->arch.push_back(ctx->h[i]);
+			ctx->arch_tracks.push_back(std::move(ctx->tracks[i]));
+			ctx->arch_nabla.push_back(std::move(nab));
+			ctx->free_slots.push_back(ctx->h[i].store_slot);
+			ctx->frames[ctx->h[i].frame_slot].users--;
+			moved = true;
+		}
+		else
+		{
+			if (k != i)
+			{
+				ctx->h[k] = ctx->h[i];
+				ctx->tracks[k] = std::move(ctx->tracks[i]);
+			}
+			++k;
+		}
+	}
+	ctx->h.resize(k);
+	ctx->tracks.resize(k);
+	if (moved) ctx->host_dirty = true;
+	// erase unused optimizers (feature_detector.cpp:525-535)
+	for (auto& f : ctx->frames)
+		if (f.alive && f.users == 0) f.alive = false;
+	return EBT_OK;
+}
+
+static int runStream(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t* n_opt)
+{
+	if (n_opt) *n_opt = 0;
+	const int P = static_cast<int>(ctx->h.size());
+	if (n <= 0 || P == 0)
+	{
+		ctx->event_index += n > 0 ? n : 0;
+		return EBT_OK;
+	}
+	{
+		const int rc = uploadPatches(ctx);
+		if (rc != EBT_OK) return rc;
+	}
+	CU(cudaMemsetAsync(ctx->d_nrec, 0, sizeof(unsigned long long), ctx->stream));
+	tic(ctx);
+	CU(ebt_launch_track_batch(ctx->d_patches, P, ctx->d_rings, ctx->d_nablas, d_events, n,
+							  ctx->event_index, frameTable(ctx), ctx->dp, ctx->d_records,
+							  ctx->d_nrec, static_cast<unsigned long long>(ctx->prm.record_capacity),
+							  ctx->stream));
+	toc(ctx, K_TRACK);
+	unsigned long long nrec = 0;
+	CU(cudaMemcpyAsync(&nrec, ctx->d_nrec, sizeof(nrec), cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->h.data(), ctx->d_patches, ctx->h.size() * sizeof(DevPatch),
+					   cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	ctx->event_index += n;
+	if (n_opt) *n_opt = static_cast<int64_t>(nrec);
+	const unsigned long long got =
+		std::min<unsigned long long>(nrec, static_cast<unsigned long long>(ctx->prm.record_capacity));
+	if (got > 0)
+	{
+		std::vector<ebt_opt_record> recs(got);
+		CU(cudaMemcpy(recs.data(), ctx->d_records, got * sizeof(ebt_opt_record), cudaMemcpyDeviceToHost));
+		// reference order: by event, then by position in patches_
+		std::unordered_map<int, int> pos;
+		for (size_t i = 0; i < ctx->h.size(); ++i) pos[ctx->h[i].track_id] = static_cast<int>(i);
+		std::sort(recs.begin(), recs.end(), [&](const ebt_opt_record& a, const ebt_opt_record& b) {
+			if (a.event_index != b.event_index) return a.event_index < b.event_index;
+			return pos[a.track_id] < pos[b.track_id];
+		});
+		for (const ebt_opt_record& r : recs)
+		{
+			HostTrack& t = ctx->tracks[pos[r.track_id]];
+			t.costs.push_back(r.final_cost);  // Patch::addFinalCost
+			if (!(r.lost & 2))                // not dropped by the cost filter (optimizer.cpp:151-156)
+			{
+				t.traj.push_back(r.x);
+				t.traj.push_back(r.y);
+				t.traj.push_back(static_cast<double>(r.ts));
+			}
+		}
+		ctx->records.insert(ctx->records.end(), recs.begin(), recs.end());
+	}
+	if (nrec > got)
+		return fail(ctx, EBT_E_CAPACITY,
+					"ebt_push_events: record_capacity exceeded; tracks are valid, records/trajectories of this push are truncated");
+	return EBT_OK;
+}
+
+// FeatureDetector::updatePatches for a batch of events (feature_detector.cpp:585-619).
+int ebt_push_events(ebt_ctx* ctx, const ebt_event* events, int64_t n, int64_t* n_optimizations)
+{
+	if (!ctx || n < 0 || (n > 0 && !events)) return fail(ctx, EBT_E_INVALID, "ebt_push_events: bad argument");
+	CU(cudaSetDevice(ctx->device));
+	if (n > 0)
+	{
+		if (static_cast<size_t>(n) > ctx->d_events_cap)
+		{
+			cudaFree(ctx->d_events);
+			ctx->d_events = nullptr;
+			ctx->d_events_cap = 0;
+			const size_t cap = static_cast<size_t>(n) + static_cast<size_t>(n) / 4 + 1024;
+			CU(cudaMalloc(&ctx->d_events, cap * sizeof(ebt_event)));
+			ctx->d_events_cap = cap;
+		}
+		CU(cudaMemcpyAsync(ctx->d_events, events, static_cast<size_t>(n) * sizeof(ebt_event),
+						   cudaMemcpyHostToDevice, ctx->stream));
+	}
+	return runStream(ctx, ctx->d_events, n, n_optimizations);
+}
+
+int ebt_push_events_device(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t* n_optimizations)
+{
+	if (!ctx || n < 0 || (n > 0 && !d_events))
+		return fail(ctx, EBT_E_INVALID, "ebt_push_events_device: bad argument");
+	CU(cudaSetDevice(ctx->device));
+	return runStream(ctx, d_events, n, n_optimizations);
+}
+
+int ebt_get_tracks(ebt_ctx* ctx, ebt_track* out, int cap, int archived, int* n_out)
+{
+	if (!ctx || !n_out) return fail(ctx, EBT_E_INVALID, "ebt_get_tracks: bad argument");
+	const auto& ps = archived ? ctx->arch : ctx->h;
+	const auto& ts = archived ? ctx->arch_tracks : ctx->tracks;
+	for (size_t i = 0; i < ps.size() && static_cast<int>(i) < cap && out; ++i) fillTrack(ps[i], ts[i], out[i]);
+	*n_out = static_cast<int>(ps.size());
+	return EBT_OK;
+}
+
+static const HostTrack* findTrack(ebt_ctx* ctx, int32_t id, const DevPatch** p, int* archIdx)
+{
+	for (size_t i = 0; i < ctx->h.size(); ++i)
+		if (ctx->h[i].track_id == id)
+		{
+			*p = &ctx->h[i];
+			*archIdx = -1;
+			return &ctx->tracks[i];
+		}
+	for (size_t i = 0; i < ctx->arch.size(); ++i)
+		if (ctx->arch[i].track_id == id)
+		{
+			*p = &ctx->arch[i];
+			*archIdx = static_cast<int>(i);
+			return &ctx->arch_tracks[i];
+		}
+	return nullptr;
+}
+
+int ebt_get_patch(ebt_ctx* ctx, int32_t track_id, int which, double* out625)
+{
+	if (!ctx || !out625 || which != 0) return fail(ctx, EBT_E_INVALID, "ebt_get_patch: bad argument");
+	const DevPatch* p = nullptr;
+	int ai = -1;
+	if (!findTrack(ctx, track_id, &p, &ai)) return fail(ctx, EBT_E_INVALID, "ebt_get_patch: unknown track id");
+	int nab[EBT_PATCH_PIXELS];
+	if (ai >= 0)
+		std::memcpy(nab, ctx->arch_nabla[ai].data(), sizeof(nab));
+	else
+	{
+		CU(cudaSetDevice(ctx->device));
+		CU(cudaMemcpy(nab, ctx->d_nablas + static_cast<size_t>(p->store_slot) * EBT_PATCH_PIXELS, sizeof(nab),
+					  cudaMemcpyDeviceToHost));
+	}
+	for (int i = 0; i < EBT_PATCH_PIXELS; ++i) out625[i] = static_cast<double>(nab[i]);
+	return EBT_OK;
+}
+
+int ebt_get_trajectory(ebt_ctx* ctx, int32_t track_id, double* out_xyt, int cap, int* n_out)
+{
+	if (!ctx || !n_out) return fail(ctx, EBT_E_INVALID, "ebt_get_trajectory: bad argument");
+	const DevPatch* p = nullptr;
+	int ai = -1;
+	const HostTrack* t = findTrack(ctx, track_id, &p, &ai);
+	if (!t) return fail(ctx, EBT_E_INVALID, "ebt_get_trajectory: unknown track id");
+	const int n = static_cast<int>(t->traj.size() / 3);
+	if (out_xyt) std::memcpy(out_xyt, t->traj.data(), static_cast<size_t>(std::min(n, cap)) * 3 * sizeof(double));
+	*n_out = n;
+	return EBT_OK;
+}
+
+int ebt_get_final_costs(ebt_ctx* ctx, int32_t track_id, double* out, int cap, int* n_out)
+{
+	if (!ctx || !n_out) return fail(ctx, EBT_E_INVALID, "ebt_get_final_costs: bad argument");
+	const DevPatch* p = nullptr;
+	int ai = -1;
+	const HostTrack* t = findTrack(ctx, track_id, &p, &ai);
+	if (!t) return fail(ctx, EBT_E_INVALID, "ebt_get_final_costs: unknown track id");
+	const int n = static_cast<int>(t->costs.size());
+	if (out) std::memcpy(out, t->costs.data(), static_cast<size_t>(std::min(n, cap)) * sizeof(double));
+	*n_out = n;
+	return EBT_OK;
+}
+
+int ebt_get_records(ebt_ctx* ctx, ebt_opt_record* out, int64_t cap, int64_t* n_out)
+{
+	if (!ctx || !n_out) return fail(ctx, EBT_E_INVALID, "ebt_get_records: bad argument");
+	const int64_t n = static_cast<int64_t>(ctx->records.size());
+	if (out) std::memcpy(out, ctx->records.data(), static_cast<size_t>(std::min(n, cap)) * sizeof(ebt_opt_record));
+	*n_out = n;
+	return EBT_OK;
+}
+
+int ebt_clear_records(ebt_ctx* ctx)
+{
+	if (!ctx) return EBT_E_INVALID;
+	ctx->records.clear();
+	return EBT_OK;
+}
+
+static int copyGrid(ebt_ctx* ctx, int slot, double* gx, double* gy)
+{
+	const size_t npx = static_cast<size_t>(ctx->prm.width) * ctx->prm.height;
+	std::vector<double2> g(npx);
+	CU(cudaSetDevice(ctx->device));
+	CU(cudaMemcpy(g.data(), ctx->frames[slot].grid, npx * sizeof(double2), cudaMemcpyDeviceToHost));
+	for (size_t i = 0; i < npx; ++i)
+	{
+		gx[i] = g[i].x;
+		gy[i] = g[i].y;
+	}
+	return EBT_OK;
+}
+
+int ebt_get_gradients(ebt_ctx* ctx, double* gx, double* gy)
+{
+	if (!ctx || !gx || !gy || !ctx->frames[ctx->latest].grid)
+		return fail(ctx, EBT_E_INVALID, "ebt_get_gradients: no frame yet");
+	return copyGrid(ctx, ctx->latest, gx, gy);
+}
+
+// ---- batched entry -------------------------------------------------------
+int ebt_frames_add(ebt_ctx* ctx, const uint8_t* gray)
+{
+	if (!ctx || !gray) return fail(ctx, EBT_E_INVALID, "ebt_frames_add: bad argument");
+	CU(cudaSetDevice(ctx->device));
+	int slot = -1;
+	for (int i = 0; i < EBT_MAX_FRAMES && slot < 0; ++i)
+		if (!ctx->frames[i].alive) slot = i;
+	if (slot < 0) return fail(ctx, EBT_E_CAPACITY, "ebt_frames_add: no free template frame slot");
+	const int rc = buildGrid(ctx, gray, slot);
+	if (rc != EBT_OK) return rc;
+	ctx->frames[slot].alive = true;
+	ctx->frames[slot].users = 1LL << 40;  // pinned: never released by new_frame_end
+	ctx->frames[slot].ts = INT64_MIN + slot;
+	return slot;
+}
+
+int ebt_frames_get(ebt_ctx* ctx, int slot, double* gx, double* gy)
+{
+	if (!ctx || slot < 0 || slot >= EBT_MAX_FRAMES || !ctx->frames[slot].grid || !gx || !gy)
+		return fail(ctx, EBT_E_INVALID, "ebt_frames_get: bad argument");
+	return copyGrid(ctx, slot, gx, gy);
+}
+
+int ebt_optimize_batch_device(ebt_ctx* ctx, const ebt_problem* d_problems, int64_t n_problems,
+							  const ebt_event* d_events, ebt_solution* d_solutions, int32_t* d_nabla)
+{
+	if (!ctx || n_problems < 0 || n_problems > INT32_MAX || (n_problems > 0 && (!d_problems || !d_events || !d_solutions)))
+		return fail(ctx, EBT_E_INVALID, "ebt_optimize_batch_device: bad argument");
+	CU(cudaSetDevice(ctx->device));
+	tic(ctx);
+	CU(ebt_launch_optimize_batch(d_problems, static_cast<int>(n_problems), d_events, frameTable(ctx),
+								 ctx->dp, d_solutions, d_nabla, ctx->stream));
+	toc(ctx, K_BATCH);
+	return EBT_OK;
+}
+
+}  // extern "C"
+template <typename T>
+static cudaError_t ensure(T** p, size_t* cap, size_t need)
+{
+	if (need <= *cap) return cudaSuccess;
+	cudaFree(*p);
+	*p = nullptr;
+	*cap = 0;
+	cudaError_t e = cudaMalloc(p, need * sizeof(T));
+	if (e == cudaSuccess) *cap = need;
+	return e;
+}
+extern "C" {
+
+int ebt_optimize_batch(ebt_ctx* ctx, const ebt_problem* problems, int64_t n_problems,
+					   const ebt_event* events, int64_t n_events, ebt_solution* solutions,
+					   int32_t* nabla)
+{
+	if (!ctx || n_problems < 0 || n_events < 0 || (n_problems > 0 && (!problems || !events || !solutions)))
+		return fail(ctx, EBT_E_INVALID, "ebt_optimize_batch: bad argument");
+	if (n_problems == 0) return EBT_OK;
+	for (int64_t i = 0; i < n_problems; ++i)
+	{
+		const ebt_problem& p = problems[i];
+		if (p.n_events < 1 || p.event_offset < 0 || static_cast<int64_t>(p.event_offset) + p.n_events > n_events ||
+			p.frame_slot < 0 || p.frame_slot >= EBT_MAX_FRAMES || !ctx->frames[p.frame_slot].grid)
+			return fail(ctx, EBT_E_INVALID, "ebt_optimize_batch: problem " + std::to_string(i) + " is malformed");
+	}
+	CU(cudaSetDevice(ctx->device));
+	const size_t np = static_cast<size_t>(n_problems);
+	{
+		size_t capS = ctx->cap_problems;
+		CU(ensure(&ctx->d_problems, &ctx->cap_problems, np));
+		CU(ensure(&ctx->d_solutions, &capS, np));
+		CU(ensure(&ctx->d_bevents, &ctx->cap_bevents, static_cast<size_t>(n_events)));
+		if (nabla) CU(ensure(&ctx->d_bnabla, &ctx->cap_bnabla, np * EBT_PATCH_PIXELS));
+	}
+	CU(cudaMemcpyAsync(ctx->d_problems, problems, np * sizeof(ebt_problem), cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->d_bevents, events, static_cast<size_t>(n_events) * sizeof(ebt_event),
+					   cudaMemcpyHostToDevice, ctx->stream));
+	const int rc = ebt_optimize_batch_device(ctx, ctx->d_problems, n_problems, ctx->d_bevents,
+											 ctx->d_solutions, nabla ? ctx->d_bnabla : nullptr);
+	if (rc != EBT_OK) return rc;
+	CU(cudaMemcpyAsync(solutions, ctx->d_solutions, np * sizeof(ebt_solution), cudaMemcpyDeviceToHost, ctx->stream));
+	if (nabla)
+		CU(cudaMemcpyAsync(nabla, ctx->d_bnabla, np * EBT_PATCH_PIXELS * sizeof(int), cudaMemcpyDeviceToHost,
+						   ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return EBT_OK;
+}
+
+}  // extern "C"

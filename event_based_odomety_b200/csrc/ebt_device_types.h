@@ -1,0 +1,65 @@
+// ebt_device_types.h — records shared by the host side of the C-ABI
+// (ebt_api.cu) and the sm_100a kernels (ebt_kernels.cu).
+#pragma once
+
+#include <stdint.h>
+
+#include "../../include/ebt_types.h"
+
+#define EBT_MAX_FRAMES 64   // live template frames (FeatureDetector::optimizers_)
+#define EBT_RING 512        // per-feature window ring capacity (>= 300 + one chunk)
+#define EBT_THREADS 128     // threads per feature CTA
+
+// Device mirror of the scalars of tracker::Patch
+// (/root/reference/implementation/feature_tracker/include/feature_tracker/patch.h:98-130).
+// The event window (Patch::events_) lives in rings[store_slot][EBT_RING]
+// (element k-th oldest = ring[(win_tail + k) & (EBT_RING-1)]), the integrated
+// patch (Patch::integratedNabla_) in nabla[store_slot][625] as int32.
+struct DevPatch
+{
+	double rx, ry;   // patch_.tl()
+	double ix, iy;   // initPoint_
+	double warp[4];  // Sophus::SE2d data: cos sin tx ty
+	double flow;     // flowDir_
+	double costs[EBT_COST_HISTORY];  // newest finalCosts_, ring indexed by n_costs
+	long long cur_ts, time_last_update, time_without_update, init_time;
+	int init, lost, track_id, num_of_events;
+	int counter, win_tail, win_size, n_costs;
+	int frame_slot, store_slot, pad0, pad1;
+};
+
+// Solver constants: the reference's OptimizerParams
+// (feature_tracker/optimizer.h:16-27) + the Ceres 2.0 defaults its Solve() call
+// inherits (thirdparty/ceres-solver/include/ceres/solver.h:264-322).
+struct DevParams
+{
+	int width, height;
+	int max_iterations;           // 10
+	int init_num_events;          // 75  (DetectorParams::initNumEvents)
+	int min_num_events;           // 100 (Patch::minNumOfEvents_)
+	int max_num_events;           // 300 (Patch::maxNumOfEvents_)
+	int batch_stride;             // 30  (Patch::isReady)
+	int border_margin;            // 5   (updateNumOfEvents)
+	double huber_a;               // 0.3
+	double optimizer_threshold;   // 0.6
+	double initial_radius;        // 1e4
+	double max_radius;            // 1e16
+	double min_radius;            // 1e-32
+	double min_relative_decrease; // 1e-3
+	double min_lm_diagonal;       // 1e-6
+	double max_lm_diagonal;       // 1e32
+	double function_tolerance;    // 1e-6
+	double gradient_tolerance;    // 1e-10
+	double parameter_tolerance;   // 1e-8
+	int max_consecutive_nonmonotonic_steps;  // 5
+	int max_consecutive_invalid_steps;       // 5
+};
+
+// Gradient grids of the live template frames: interleaved (gx, gy) doubles,
+// row stride = width (Optimizer::setGrad, optimizer.cpp:15-30).
+struct FrameTable
+{
+	const double2* grid[EBT_MAX_FRAMES];
+	int latest;  // slot FeatureDetector::gradX_/gradY_ refer to
+	int pad;
+};

@@ -1,0 +1,1138 @@
+// ebt_kernels.cu — hand-written sm_100a kernels for the event-based feature
+// tracker hot path.  One CTA of EBT_THREADS threads owns
+// one feature: its event window lives in shared memory, the 625 patch pixels
+// are strided over the threads, per-evaluation sums are reduced with warp
+// shuffles, and every thread carries an identical copy of the small scalar
+// Levenberg-Marquardt state so that no broadcast is needed between steps.
+//
+// Arithmetic is FP64 throughout (B200 keeps a 1:2 FP64:FP32 vector rate), no
+// tensor cores: the per-feature systems are 4x4.
+//
+// Reference behaviour mirrored (cited per function):
+//   ft/     = /root/reference/implementation/feature_tracker/
+//   ceres/  = /root/reference/thirdparty/ceres-solver/
+//   sophus/ = /root/reference/thirdparty/Sophus/sophus/
+#include <cuda_runtime.h>
+#include <float.h>
+#include <math.h>
+
+#include "ebt_device_types.h"
+#include "ebt_kernels.h"
+
+#define NPIX EBT_PATCH_PIXELS
+#define SIDE EBT_PATCH_SIDE
+#define NT EBT_THREADS
+#define NW (EBT_THREADS / 32)
+#define RMASK (EBT_RING - 1)
+
+namespace
+{
+// --------------------------------------------------------------------------
+// Shared memory of one feature CTA
+// --------------------------------------------------------------------------
+struct __align__(16) FeatShared
+{
+	ebt_event ring[EBT_RING];  // Patch::events_
+	double m[NPIX];            // normalised integrated patch (patch.cpp:156-159)
+	int nabla[NPIX];           // Patch::integratedNabla_, integer valued
+	double red[NW][20];        // cross-warp reduction scratch
+	unsigned bal[2][NW];       // per-warp containment ballots (double buffered)
+};
+
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+	return v;
+}
+
+// Sum K per-thread partials over the CTA; every thread receives all K totals
+// (fixed summation order => bitwise identical in all threads).
+template <int K>
+__device__ __forceinline__ void block_sum(FeatShared& sh, double (&acc)[K])
+{
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+	for (int k = 0; k < K; ++k)
+	{
+		const double v = warp_sum(acc[k]);
+		if (lane == 0) sh.red[warp][k] = v;
+	}
+	__syncthreads();
+#pragma unroll
+	for (int k = 0; k < K; ++k)
+	{
+		double v = sh.red[0][k];
+#pragma unroll
+		for (int w = 1; w < NW; ++w) v += sh.red[w][k];
+		acc[k] = v;
+	}
+	__syncthreads();
+}
+
+// Catmull-Rom weights of ceres::CubicHermiteSpline (ceres/include/ceres/
+// cubic_interpolation.h:64-90) in basis form: f = sum_k w[k] p[k],
+// df/dx = sum_k d[k] p[k].
+template <bool DERIV>
+__device__ __forceinline__ void cr_weights(double t, double (&w)[4], double (&d)[4])
+{
+	const double t2 = t * t, t3 = t2 * t;
+	w[0] = 0.5 * (-t3 + 2.0 * t2 - t);
+	w[1] = 0.5 * (3.0 * t3 - 5.0 * t2 + 2.0);
+	w[2] = 0.5 * (-3.0 * t3 + 4.0 * t2 + t);
+	w[3] = 0.5 * (t3 - t2);
+	if (DERIV)
+	{
+		d[0] = 0.5 * (-3.0 * t2 + 4.0 * t - 1.0);
+		d[1] = 0.5 * (9.0 * t2 - 10.0 * t);
+		d[2] = 0.5 * (-9.0 * t2 + 8.0 * t + 1.0);
+		d[3] = 0.5 * (3.0 * t2 - 2.0 * t);
+	}
+}
+
+// Sum layout of one evaluation.
+//  [0] sum u^2   [1] sum u*m   [2..5] A_q = sum u du_q   [6..9] B_q = sum du_q m
+//  [10..19] G_qp = sum du_q du_p  (q <= p, row major upper triangle)
+//
+// Per pixel: OptimizerCostFunctor::warp (ft/include/feature_tracker/
+// optimizer_cost.h:47-90): W = R p + t, out-of-image -> u = 0, else bicubic
+// sample (ceres BiCubicInterpolator, cubic_interpolation.h:264-325, clamp to
+// edge :403-421) of the interleaved (gx, gy) grid at (row = W.y, col = W.x),
+// u = gx cos(phi) + gy sin(phi).  Jacobian columns: SE2 local (upsilon_x,
+// upsilon_y, theta) through Dx_this_mul_exp_x_at_0 (sophus/se2.hpp:123-142)
+// and phi.
+template <bool JAC>
+__device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, int W, int H,
+											 const double (&x)[5], double vx, double vy,
+											 double tlx, double tly, const double* m,
+											 double (&acc)[JAC ? 20 : 2])
+{
+	const double cs = x[0], sn = x[1], tx = x[2], ty = x[3];
+#pragma unroll
+	for (int k = 0; k < (JAC ? 20 : 2); ++k) acc[k] = 0.0;
+	for (int i = threadIdx.x; i < NPIX; i += NT)
+	{
+		const int yy = i / SIDE, xx = i - yy * SIDE;
+		const double px = xx + tlx, py = yy + tly;
+		const double wx = cs * px + -sn * py + tx;
+		const double wy = sn * px + cs * py + ty;
+		if (wx >= W || wy >= H || wx < 0.0 || wy < 0.0) continue;
+		const double fr = floor(wy), fc = floor(wx);
+		const int row = (int)fr, col = (int)fc;
+		double wr[4], dr[4], wc[4], dc[4];
+		cr_weights<JAC>(wy - fr, wr, dr);
+		cr_weights<JAC>(wx - fc, wc, dc);
+		int ci[4];
+#pragma unroll
+		for (int j = 0; j < 4; ++j) ci[j] = min(max(col - 1 + j, 0), W - 1);
+		double g0 = 0, g1 = 0, gr0 = 0, gr1 = 0, gc0 = 0, gc1 = 0;
+#pragma unroll
+		for (int r = 0; r < 4; ++r)
+		{
+			const int ri = min(max(row - 1 + r, 0), H - 1);
+			const double2* rowp = grid + (size_t)ri * W;
+			double f0 = 0, f1 = 0, d0 = 0, d1 = 0;
+#pragma unroll
+			for (int j = 0; j < 4; ++j)
+			{
+				const double2 p = __ldg(rowp + ci[j]);
+				f0 += wc[j] * p.x;
+				f1 += wc[j] * p.y;
+				if (JAC)
+				{
+					d0 += dc[j] * p.x;
+					d1 += dc[j] * p.y;
+				}
+			}
+			g0 += wr[r] * f0;
+			g1 += wr[r] * f1;
+			if (JAC)
+			{
+				gr0 += dr[r] * f0;
+				gr1 += dr[r] * f1;
+				gc0 += wr[r] * d0;
+				gc1 += wr[r] * d1;
+			}
+		}
+		const double u = g0 * vx + g1 * vy;
+		const double mi = m[i];
+		acc[0] += u * u;
+		acc[1] += u * mi;
+		if (JAC)
+		{
+			const double ux = gc0 * vx + gc1 * vy;  // du/dW.x
+			const double uy = gr0 * vx + gr1 * vy;  // du/dW.y
+			double du[4];
+			du[0] = ux * cs + uy * sn;
+			du[1] = -ux * sn + uy * cs;
+			du[2] = ux * (-cs * py - sn * px) + uy * (-sn * py + cs * px);
+			du[3] = -g0 * vy + g1 * vx;
+#pragma unroll
+			for (int q = 0; q < 4; ++q)
+			{
+				acc[2 + q] += u * du[q];
+				acc[6 + q] += du[q] * mi;
+			}
+			int k = 10;
+#pragma unroll
+			for (int q = 0; q < 4; ++q)
+#pragma unroll
+				for (int p = q; p < 4; ++p) acc[k++] += du[q] * du[p];
+		}
+	}
+}
+
+// HuberLoss::Evaluate (ceres/internal/ceres/loss_function.cc:48-62) on the
+// whole 625-block (ft/src/optimizer.cpp:97-99): returns rho(s), sets rho'.
+__device__ __forceinline__ double huber(double s, double a, double& rho1)
+{
+	const double b = a * a;
+	if (s > b)
+	{
+		const double r = sqrt(s);
+		rho1 = fmax(DBL_MIN, a / r);
+		return 2.0 * a * r - b;
+	}
+	rho1 = 1.0;
+	return s;
+}
+
+struct EvalCtx
+{
+	const double2* grid;
+	int W, H;
+	double tlx, tly;
+	double smm;  // sum m^2
+	double huber_a;
+};
+
+// Cost-only evaluation (TrustRegionMinimizer::ComputeCandidatePointAndEvaluateCost,
+// ceres/internal/ceres/trust_region_minimizer.cc:731-747).  r_i = u_i/sqrt(N)+m_i
+// (optimizer_cost.h:29-45), s = sum r_i^2 expanded over the three reduced sums.
+__device__ bool eval_cost(FeatShared& sh, const EvalCtx& E, const double (&x)[5], double& cost)
+{
+	double acc[2];
+	double vy, vx;
+	sincos(x[4], &vy, &vx);
+	eval_pixels<false>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, acc);
+	block_sum<2>(sh, acc);
+	const double N = 1e-5 + acc[0];
+	const double s = acc[0] / N + 2.0 * acc[1] / sqrt(N) + E.smm;
+	double rho1;
+	cost = 0.5 * huber(s, E.huber_a, rho1);
+	return isfinite(s);
+}
+
+// Residual + Jacobian evaluation reduced to what the LM step needs: cost,
+// H = J^T J (upper 4x4) and g = J^T r of the Huber-corrected block
+// (ceres/internal/ceres/residual_block.cc:134-175, corrector.cc:81-110: with
+// rho'' <= 0 both r and J are scaled by sqrt(rho')).
+//   dr_i/dq = du_iq/sqrt(N) - u_i A_q / N^1.5
+__device__ bool eval_jac(FeatShared& sh, const EvalCtx& E, const double (&x)[5], double& cost,
+						 double (&Hm)[10], double (&g)[4])
+{
+	double acc[20];
+	double vy, vx;
+	sincos(x[4], &vy, &vx);
+	eval_pixels<true>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, acc);
+	block_sum<20>(sh, acc);
+	const double suu = acc[0], c = acc[1];
+	const double N = 1e-5 + suu;
+	const double sq = sqrt(N);
+	const double s = suu / N + 2.0 * c / sq + E.smm;
+	double rho1;
+	cost = 0.5 * huber(s, E.huber_a, rho1);
+	const double iN = 1.0 / N;
+	const double k2 = iN * iN * (2.0 - suu * iN);
+	bool ok = isfinite(s);
+#pragma unroll
+	for (int q = 0; q < 4; ++q)
+	{
+		const double A = acc[2 + q], B = acc[6 + q];
+		g[q] = rho1 * (A * iN + B / sq - A * suu * iN * iN - A * c * iN / sq);
+		ok = ok && isfinite(g[q]);
+	}
+	int k = 0;
+#pragma unroll
+	for (int q = 0; q < 4; ++q)
+#pragma unroll
+		for (int p = q; p < 4; ++p, ++k)
+		{
+			Hm[k] = rho1 * (acc[10 + k] * iN - acc[2 + q] * acc[2 + p] * k2);
+			ok = ok && isfinite(Hm[k]);
+		}
+	return ok;
+}
+
+// LocalParameterizationSE2::Plus = T * SE2::exp(delta) (ft/include/
+// feature_tracker/local_parameterization_se2.hpp:20-29; sophus/se2.hpp:560-582;
+// SO2 product + renormalisation sophus/so2.hpp:214-239, normalising ctor
+// :388-391); the flow angle block is plain addition.
+__device__ __forceinline__ void plus5(const double (&x)[5], const double (&d)[4], double (&out)[5])
+{
+	const double theta = d[2];
+	double es, ec;
+	sincos(theta, &es, &ec);
+	{
+		const double len = sqrt(ec * ec + es * es);
+		ec /= len;
+		es /= len;
+	}
+	double sbt, omc;
+	if (fabs(theta) < 1e-10)
+	{
+		const double t2 = theta * theta;
+		sbt = 1. - (1. / 6.) * t2;
+		omc = 0.5 * theta - (1. / 24.) * theta * t2;
+	}
+	else
+	{
+		sbt = es / theta;
+		omc = (1. - ec) / theta;
+	}
+	const double ex = sbt * d[0] - omc * d[1];
+	const double ey = omc * d[0] + sbt * d[1];
+	double rc = x[0] * ec - x[1] * es;
+	double rs = x[0] * es + x[1] * ec;
+	const double n2 = rc * rc + rs * rs;
+	if (n2 != 1.0)
+	{
+		const double sc = 2.0 / (1.0 + n2);
+		rc *= sc;
+		rs *= sc;
+	}
+	{
+		const double len = sqrt(rc * rc + rs * rs);
+		rc /= len;
+		rs /= len;
+	}
+	out[0] = rc;
+	out[1] = rs;
+	out[2] = x[2] + (x[0] * ex - x[1] * ey);
+	out[3] = x[3] + (x[1] * ex + x[0] * ey);
+	out[4] = x[4] + d[3];
+}
+
+__device__ __forceinline__ int hidx(int q, int p)
+{
+	// index of (q,p), q <= p, in the packed upper triangle of a 4x4
+	return q * 4 - (q * (q - 1)) / 2 + (p - q);
+}
+
+// Solve (S H S + diag(d2)) y = S g by Cholesky, FP64.  This is the normal-
+// equation form of the least-squares problem DenseQRSolver solves by
+// Householder QR (ceres/internal/ceres/dense_qr_solver.cc:120-165):
+//   min || [J S; diag(sqrt(d2))] y - [r; 0] ||.
+// Returns false when the factorisation breaks down or y is not finite
+// (Ceres: "Failed to compute a finite step", levenberg_marquardt_strategy.cc:
+// 117-121).
+__device__ bool solve4(const double (&Hs)[10], const double (&d2)[4], const double (&gs)[4],
+					   double (&y)[4])
+{
+	double L[4][4];
+#pragma unroll
+	for (int i = 0; i < 4; ++i)
+#pragma unroll
+		for (int j = 0; j <= i; ++j)
+		{
+			double v = Hs[hidx(j, i)] + (i == j ? d2[i] : 0.0);
+#pragma unroll
+			for (int k = 0; k < j; ++k) v -= L[i][k] * L[j][k];
+			if (i == j)
+			{
+				if (!(v > 0.0)) return false;
+				L[i][i] = sqrt(v);
+			}
+			else
+				L[i][j] = v / L[j][j];
+		}
+	double z[4];
+#pragma unroll
+	for (int i = 0; i < 4; ++i)
+	{
+		double v = gs[i];
+#pragma unroll
+		for (int k = 0; k < i; ++k) v -= L[i][k] * z[k];
+		z[i] = v / L[i][i];
+	}
+#pragma unroll
+	for (int i = 3; i >= 0; --i)
+	{
+		double v = z[i];
+#pragma unroll
+		for (int k = i + 1; k < 4; ++k) v -= L[k][i] * y[k];
+		y[i] = v / L[i][i];
+	}
+	return isfinite(y[0]) && isfinite(y[1]) && isfinite(y[2]) && isfinite(y[3]);
+}
+
+struct LmSummary
+{
+	double final_cost;
+	int n_successful, n_unsuccessful, termination;
+	int n_jac, n_cost;
+};
+
+__device__ __forceinline__ double norm5(const double (&a)[5])
+{
+	double s = 0;
+#pragma unroll
+	for (int k = 0; k < 5; ++k) s += a[k] * a[k];
+	return sqrt(s);
+}
+
+// EvaluateGradientAndJacobian (ceres/internal/ceres/trust_region_minimizer.cc:
+// 231-288): evaluate, fix the Jacobi column scaling at iteration 0, return the
+// scaled system Hs = S H S, gs = S g and the projected gradient max norm.
+__device__ bool eval_grad_jac(FeatShared& sh, const EvalCtx& E, const double (&x)[5], bool iter0,
+							  double& x_cost, double (&Hs)[10], double (&gs)[4],
+							  double (&scale)[4], double& grad_max_norm)
+{
+	double Hm[10], g[4];
+	if (!eval_jac(sh, E, x, x_cost, Hm, g)) return false;
+	if (iter0)
+	{
+#pragma unroll
+		for (int q = 0; q < 4; ++q) scale[q] = 1.0 / (1.0 + sqrt(Hm[hidx(q, q)]));
+	}
+#pragma unroll
+	for (int q = 0; q < 4; ++q)
+	{
+		gs[q] = g[q] * scale[q];
+#pragma unroll
+		for (int p = q; p < 4; ++p) Hs[hidx(q, p)] = Hm[hidx(q, p)] * scale[q] * scale[p];
+	}
+	double ng[4], xp[5];
+#pragma unroll
+	for (int q = 0; q < 4; ++q) ng[q] = -g[q];
+	plus5(x, ng, xp);
+	double mx = 0;
+#pragma unroll
+	for (int k = 0; k < 5; ++k) mx = fmax(mx, fabs(x[k] - xp[k]));
+	grad_max_norm = mx;
+	return true;
+}
+
+// TrustRegionMinimizer::Minimize (trust_region_minimizer.cc:67-121 and helpers
+// :300-344, 364-433, 438-470, 680-801), LevenbergMarquardtStrategy
+// (levenberg_marquardt_strategy.cc:67-166), TrustRegionStepEvaluator
+// (trust_region_step_evaluator.cc:40-114), final cost (solver_utils.h:48-56),
+// with the reference's options (ft/src/optimizer.cpp:102-110).  Executed by
+// every thread of the CTA on identical values; the evaluations inside are the
+// only cooperative parts.  params is updated to the lowest-cost accepted
+// iterate, or left alone on FAILURE (solver.cc:428-432).
+__device__ void lm_solve(FeatShared& sh, const EvalCtx& E, const DevParams& P, double (&params)[5],
+						 LmSummary& S)
+{
+	double x[5], cand[5], best[5];
+	double Hs[10], gs[4], scale[4] = {1, 1, 1, 1}, diag[4] = {0, 0, 0, 0};
+	double x_cost = DBL_MAX, minimum_cost = DBL_MAX, x_norm = -1;
+	double radius = P.initial_radius, decrease_factor = 2.0;
+	bool reuse_diagonal = false;
+	int consecutive_invalid = 0;
+	double grad_max_norm = 0, final_cost;
+#pragma unroll
+	for (int k = 0; k < 5; ++k) x[k] = best[k] = params[k];
+	S.n_successful = S.n_unsuccessful = S.termination = 0;
+	S.n_jac = 1;
+	S.n_cost = 0;
+	if (!eval_grad_jac(sh, E, x, true, x_cost, Hs, gs, scale, grad_max_norm))
+	{
+		S.termination = 2;
+		S.final_cost = -1.0;
+		return;
+	}
+	final_cost = x_cost;
+	double se_min = x_cost, se_cur = x_cost, se_ref = x_cost, se_cand = x_cost;
+	double se_acc_ref = 0, se_acc_cand = 0;
+	int se_nonmono = 0;
+	int iteration = 0;
+	bool step_successful = true, failed = false;
+	double iter_cost = x_cost, iter_gmn = grad_max_norm;
+	for (;;)
+	{
+		if (step_successful)
+		{
+			if (iteration > 0) S.n_successful++;
+			if (x_cost < minimum_cost)
+			{
+				minimum_cost = x_cost;
+#pragma unroll
+				for (int k = 0; k < 5; ++k) best[k] = x[k];
+			}
+		}
+		else
+			S.n_unsuccessful++;
+		final_cost = fmin(final_cost, iter_cost);
+		if (iteration >= P.max_iterations) break;
+		if (step_successful && iter_gmn <= P.gradient_tolerance) { S.termination = 1; break; }
+		if (radius <= P.min_radius) { S.termination = 1; break; }
+		++iteration;
+		step_successful = false;
+		iter_gmn = 0;
+		iter_cost = 0;
+
+		if (!reuse_diagonal)
+		{
+#pragma unroll
+			for (int q = 0; q < 4; ++q)
+				diag[q] = fmin(fmax(Hs[hidx(q, q)], P.min_lm_diagonal), P.max_lm_diagonal);
+		}
+		double d2[4], step[4], delta[4];
+#pragma unroll
+		for (int q = 0; q < 4; ++q)
+		{
+			const double l = sqrt(diag[q] / radius);  // lm_diagonal_
+			d2[q] = l * l;
+		}
+		bool valid = solve4(Hs, d2, gs, step);
+		reuse_diagonal = true;
+		double model_cost_change = 0;
+		if (valid)
+		{
+			// -(J step)'(r + J step / 2) = -step'gs - step'Hs step / 2
+			double sg = 0, shs = 0;
+#pragma unroll
+			for (int q = 0; q < 4; ++q)
+			{
+				step[q] = -step[q];
+				sg += step[q] * gs[q];
+			}
+#pragma unroll
+			for (int q = 0; q < 4; ++q)
+			{
+				double row = 0;
+#pragma unroll
+				for (int p = 0; p < 4; ++p)
+					row += Hs[q <= p ? hidx(q, p) : hidx(p, q)] * step[p];
+				shs += step[q] * row;
+			}
+			model_cost_change = -sg - 0.5 * shs;
+			valid = model_cost_change > 0.0;
+		}
+		if (!valid)
+		{
+			if (++consecutive_invalid >= P.max_consecutive_invalid_steps)
+			{
+				S.termination = 2;
+				failed = true;
+				break;
+			}
+			radius /= decrease_factor;
+			decrease_factor *= 2.0;
+			iter_cost = x_cost;
+			continue;
+		}
+		consecutive_invalid = 0;
+#pragma unroll
+		for (int q = 0; q < 4; ++q) delta[q] = step[q] * scale[q];
+		double cand_cost;
+		plus5(x, delta, cand);
+		S.n_cost++;
+		if (!eval_cost(sh, E, cand, cand_cost)) cand_cost = DBL_MAX;
+		{
+			double d5[5];
+#pragma unroll
+			for (int k = 0; k < 5; ++k) d5[k] = x[k] - cand[k];
+			if (norm5(d5) <= P.parameter_tolerance * (x_norm + P.parameter_tolerance))
+			{
+				S.termination = 1;
+				break;
+			}
+		}
+		if (fabs(x_cost - cand_cost) <= P.function_tolerance * x_cost)
+		{
+			S.termination = 1;
+			break;
+		}
+		double rho;
+		if (cand_cost >= DBL_MAX)
+			rho = -DBL_MAX;
+		else
+			rho = fmax((se_cur - cand_cost) / model_cost_change,
+					   (se_ref - cand_cost) / (se_acc_ref + model_cost_change));
+		if (rho > P.min_relative_decrease)
+		{
+#pragma unroll
+			for (int k = 0; k < 5; ++k) x[k] = cand[k];
+			x_norm = norm5(x);
+			S.n_jac++;
+			if (!eval_grad_jac(sh, E, x, false, x_cost, Hs, gs, scale, grad_max_norm))
+			{
+				S.termination = 2;
+				failed = true;
+				break;
+			}
+			iter_cost = x_cost;
+			iter_gmn = grad_max_norm;
+			step_successful = true;
+			const double t = 2.0 * rho - 1.0;
+			radius = fmin(P.max_radius, radius / fmax(1.0 / 3.0, 1.0 - t * t * t));
+			decrease_factor = 2.0;
+			reuse_diagonal = false;
+			se_cur = cand_cost;
+			se_acc_cand += model_cost_change;
+			se_acc_ref += model_cost_change;
+			if (se_cur < se_min)
+			{
+				se_min = se_cur;
+				se_nonmono = 0;
+				se_cand = se_cur;
+				se_acc_cand = 0;
+			}
+			else
+			{
+				++se_nonmono;
+				if (se_cur > se_cand)
+				{
+					se_cand = se_cur;
+					se_acc_cand = 0;
+				}
+			}
+			if (se_nonmono == P.max_consecutive_nonmonotonic_steps)
+			{
+				se_ref = se_cand;
+				se_acc_ref = se_acc_cand;
+			}
+		}
+		else
+		{
+			radius /= decrease_factor;
+			decrease_factor *= 2.0;
+			iter_cost = cand_cost;
+		}
+	}
+	if (!failed)
+	{
+#pragma unroll
+		for (int k = 0; k < 5; ++k) params[k] = best[k];
+	}
+	S.final_cost = final_cost;
+}
+
+// --------------------------------------------------------------------------
+// Per-feature state carried in registers, identical in every thread of the CTA
+// --------------------------------------------------------------------------
+struct FeatState
+{
+	double rx, ry, ix, iy;
+	double warp[4];
+	double flow;
+	long long cur_ts, time_last_update, time_without_update;
+	int init, lost, num_of_events, counter, tail, size, n_costs, frame_slot;
+};
+
+__device__ __forceinline__ long long to_i32(double v)
+{
+	// static_cast<int32_t>(double) as x86-64 cvttsd2si performs it
+	if (!(v > -2147483649.0 && v < 2147483648.0)) return (long long)INT_MIN;
+	return (long long)(int)v;
+}
+
+__device__ __forceinline__ bool in_rect(double rx, double ry, int x, int y)
+{
+	// cv::Rect2d::contains(Point2i -> Point2d)
+	return rx <= x && x < rx + SIDE && ry <= y && y < ry + SIDE;
+}
+
+// Job (1): Patch::integrateEvents (ft/src/patch.cpp:65-84).  Polarity
+// scatter-accumulate of the window (already staged in shared memory) into the
+// 25x25 patch with shared-memory integer atomics; containment is re-tested
+// against the CURRENT rect; timestamps pass through int32.
+__device__ void integrate_window(FeatShared& sh, FeatState& st)
+{
+	for (int i = threadIdx.x; i < NPIX; i += NT) sh.nabla[i] = 0;
+	__syncthreads();
+	for (int k = threadIdx.x; k < st.size; k += NT)
+	{
+		const ebt_event e = sh.ring[(st.tail + k) & RMASK];
+		if (in_rect(st.rx, st.ry, e.x, e.y))
+		{
+			const int px = (int)(e.x - st.rx), py = (int)(e.y - st.ry);
+			atomicAdd(&sh.nabla[py * SIDE + px], (int)e.polarity);
+		}
+	}
+	const long long front = sh.ring[(st.tail + st.size - 1) & RMASK].t_us;
+	const long long back = sh.ring[st.tail & RMASK].t_us;
+	st.cur_ts = to_i32((double)(front + back) * 0.5);
+	st.time_last_update = to_i32((double)back);
+	__syncthreads();
+}
+
+// Patch::updatePatchRect (ft/src/patch.cpp:49-63): centre = warp^-1 * initPoint.
+__device__ __forceinline__ void update_rect(FeatState& st)
+{
+	const double c = st.warp[0], s = st.warp[1];
+	const double mx = st.warp[2] * -1.0, my = st.warp[3] * -1.0;
+	const double itx = __dadd_rn(__dmul_rn(c, mx), -__dmul_rn(-s, my));
+	const double ity = __dadd_rn(__dmul_rn(-s, mx), __dmul_rn(c, my));
+	const double ncx = __dadd_rn(__dadd_rn(__dmul_rn(c, st.ix), __dmul_rn(s, st.iy)), itx);
+	const double ncy = __dadd_rn(__dadd_rn(__dmul_rn(-s, st.ix), __dmul_rn(c, st.iy)), ity);
+	st.rx = ncx - EBT_PATCH_EXTENT;
+	st.ry = ncy - EBT_PATCH_EXTENT;
+}
+
+// One Optimizer::optimize (ft/src/optimizer.cpp:62-206): integrate, normalise,
+// LM solve, cost filter, state update.
+__device__ void optimize_feature(FeatShared& sh, double* costs, FeatState& st,
+								 const FrameTable& ft, const DevParams& P, LmSummary& S)
+{
+	integrate_window(sh, st);
+	double a1[1];
+	a1[0] = 0;
+	for (int i = threadIdx.x; i < NPIX; i += NT)
+	{
+		const double v = (double)sh.nabla[i];
+		a1[0] += v * v;
+	}
+	block_sum<1>(sh, a1);
+	// Patch::getNormalizedIntegratedNabla (patch.cpp:156-159): Mat / s is
+	// evaluated by OpenCV as Mat * (1/s)
+	const double inv = 1.0 / sqrt(a1[0]);
+	a1[0] = 0;
+	for (int i = threadIdx.x; i < NPIX; i += NT)
+	{
+		const double v = (double)sh.nabla[i] * inv;
+		sh.m[i] = v;
+		a1[0] += v * v;
+	}
+	block_sum<1>(sh, a1);
+
+	EvalCtx E;
+	E.grid = ft.grid[st.frame_slot];
+	E.W = P.width;
+	E.H = P.height;
+	E.tlx = st.rx;
+	E.tly = st.ry;
+	E.smm = a1[0];
+	E.huber_a = P.huber_a;
+	// Patch::getFlow() returns float (patch.h:54)
+	double x[5] = {st.warp[0], st.warp[1], st.warp[2], st.warp[3],
+				   (double)__double2float_rn(st.flow)};
+	lm_solve(sh, E, P, x, S);
+
+	// addFinalCost + median-of-5 cost filter (optimizer.cpp:127-157)
+	if (threadIdx.x == 0) costs[st.n_costs & (EBT_COST_HISTORY - 1)] = S.final_cost;
+	st.n_costs++;
+	__syncthreads();
+	if (st.n_costs >= 6)
+	{
+		double v[5];
+#pragma unroll
+		for (int i = 0; i < 5; ++i) v[i] = costs[(st.n_costs - 6 + i) & (EBT_COST_HISTORY - 1)];
+#pragma unroll
+		for (int i = 1; i < 5; ++i)
+#pragma unroll
+			for (int j = i; j > 0; --j)
+				if (v[j] < v[j - 1])
+				{
+					const double t = v[j];
+					v[j] = v[j - 1];
+					v[j - 1] = t;
+				}
+		if (v[2] > P.optimizer_threshold)
+		{
+			st.lost = 1;
+			return;
+		}
+	}
+	st.flow = fmod(x[4], 2 * 3.14159265358979323846);
+#pragma unroll
+	for (int k = 0; k < 4; ++k) st.warp[k] = x[k];
+	st.init = 1;
+	const double ox = st.rx, oy = st.ry;
+	update_rect(st);
+	const double h = (SIDE - 1) / 2.;  // Patch::toCorner
+	const double dx = (st.rx + h) - (ox + h), dy = (st.ry + h) - (oy + h);
+	st.time_without_update = (long long)(1e6 / fmax(1e-1, sqrt(dx * dx + dy * dy)));
+	st.counter = 0;
+}
+
+// Job (2b): FeatureDetector::updateNumOfEvents (ft/src/feature_detector.cpp:
+// 666-712).  cv::warpAffine(flags = WARP_INVERSE_MAP) is nearest-neighbour with
+// 10-bit fixed-point source coordinates; only the cropped rect is sampled, from
+// the LATEST frame's gradients.
+__device__ void update_num_of_events(FeatShared& sh, FeatState& st, const FrameTable& ft,
+									 const DevParams& P)
+{
+	const int W = P.width, H = P.height;
+	const double cx = (st.rx + (st.rx + SIDE)) * 0.5, cy = (st.ry + (st.ry + SIDE)) * 0.5;
+	if (cx <= P.border_margin || cy <= P.border_margin || cx >= W - P.border_margin ||
+		cy >= H - P.border_margin)
+	{
+		st.lost = 1;
+		return;
+	}
+	if (st.rx < 0 || st.ry < 0 || st.rx + SIDE >= W || st.ry + SIDE >= H)
+	{
+		st.num_of_events = min(max(P.init_num_events, P.min_num_events), P.max_num_events);
+		return;
+	}
+	const double2* grid = ft.grid[ft.latest];
+	const double c = st.warp[0], s = st.warp[1], tx = st.warp[2], ty = st.warp[3];
+	const int x0 = __double2int_rn(st.rx), y0 = __double2int_rn(st.ry);
+	const float flow = __double2float_rn(st.flow);
+	// std::cos(float) rounds to float (feature_detector.cpp:702-704)
+	const double a = 0.6 * (double)__double2float_rn(cos((double)flow));
+	const double b = 0.6 * (double)__double2float_rn(sin((double)flow));
+	double acc[1];
+	acc[0] = 0;
+	for (int i = threadIdx.x; i < NPIX; i += NT)
+	{
+		const int yy = i / SIDE;
+		const int x = x0 + (i - yy * SIDE), y = y0 + yy;
+		const int X0 = __double2int_rn(c * x * 1024) +
+					   __double2int_rn(__dadd_rn(__dmul_rn(-s, y), tx) * 1024) + 512;
+		const int Y0 = __double2int_rn(s * x * 1024) +
+					   __double2int_rn(__dadd_rn(__dmul_rn(c, y), ty) * 1024) + 512;
+		const int xi = X0 >> 10, yi = Y0 >> 10;
+		if (xi >= 0 && xi < W && yi >= 0 && yi < H)
+		{
+			const double2 g = __ldg(grid + (size_t)yi * W + xi);
+			acc[0] += fabs(__dadd_rn(__dmul_rn(g.x, a), __dmul_rn(g.y, b)));
+		}
+	}
+	block_sum<1>(sh, acc);
+	// size_t sumPatch = norm; Patch::setNumOfEvents clamps (patch.cpp:208-212)
+	const unsigned long long n = (unsigned long long)acc[0];
+	st.num_of_events = (int)min(max(n, (unsigned long long)P.min_num_events),
+								(unsigned long long)P.max_num_events);
+}
+
+__device__ __forceinline__ void load_state(FeatState& st, const DevPatch& p)
+{
+	st.rx = p.rx; st.ry = p.ry; st.ix = p.ix; st.iy = p.iy;
+#pragma unroll
+	for (int k = 0; k < 4; ++k) st.warp[k] = p.warp[k];
+	st.flow = p.flow;
+	st.cur_ts = p.cur_ts;
+	st.time_last_update = p.time_last_update;
+	st.time_without_update = p.time_without_update;
+	st.init = p.init; st.lost = p.lost; st.num_of_events = p.num_of_events;
+	st.counter = p.counter; st.tail = p.win_tail; st.size = p.win_size;
+	st.n_costs = p.n_costs; st.frame_slot = p.frame_slot;
+}
+
+__device__ __forceinline__ void store_state(const FeatState& st, DevPatch& p)
+{
+	p.rx = st.rx; p.ry = st.ry;
+#pragma unroll
+	for (int k = 0; k < 4; ++k) p.warp[k] = st.warp[k];
+	p.flow = st.flow;
+	p.cur_ts = st.cur_ts;
+	p.time_last_update = st.time_last_update;
+	p.time_without_update = st.time_without_update;
+	p.init = st.init; p.lost = st.lost; p.num_of_events = st.num_of_events;
+	p.counter = st.counter; p.win_tail = st.tail; p.win_size = st.size;
+	p.n_costs = st.n_costs;
+}
+
+__device__ void write_record(ebt_opt_record* records, unsigned long long* n_records,
+							 unsigned long long cap, const FeatState& st, int track_id,
+							 const LmSummary& S, long long event_index)
+{
+	const unsigned long long slot = atomicAdd(n_records, 1ull);
+	if (slot >= cap) return;
+	ebt_opt_record r;
+	r.track_id = track_id;
+	r.n_successful = S.n_successful;
+	r.n_unsuccessful = S.n_unsuccessful;
+	r.termination = S.termination;
+	r.lost = st.lost;
+	r.num_of_events = st.num_of_events;
+	r.ts = st.cur_ts;
+	r.event_index = event_index;
+	r.x = st.rx + (SIDE - 1) / 2.;
+	r.y = st.ry + (SIDE - 1) / 2.;
+	r.final_cost = S.final_cost;
+#pragma unroll
+	for (int k = 0; k < 4; ++k) r.warp[k] = st.warp[k];
+	r.flow_dir = (double)__double2float_rn(st.flow);
+	records[slot] = r;
+}
+
+// --------------------------------------------------------------------------
+// Stream kernel: FeatureDetector::updatePatches (ft/src/feature_detector.cpp:
+// 585-619) for a whole batch of events, one CTA per feature.  Between two
+// newImage calls a patch's evolution depends only on its own state and the
+// ordered event stream, so each CTA replays the per-event loop for its
+// feature: events are read as coalesced 16-byte records (one per thread per
+// chunk, next chunk prefetched), containment is tested against the current
+// rect, accepted events are compacted in order into the shared-memory window
+// ring (ballot + prefix), and the optimisation fires at exactly the event where
+// Patch::isReady() (patch.cpp:296-299) first holds; the rest of the chunk is
+// then re-tested against the moved rect.
+// --------------------------------------------------------------------------
+__global__ void __launch_bounds__(NT)
+track_batch_kernel(DevPatch* __restrict__ patches, int n_patches,
+				   ebt_event* __restrict__ rings, int* __restrict__ nablas,
+				   const ebt_event* __restrict__ events, long long n_events,
+				   long long event_base, FrameTable ft, DevParams P,
+				   ebt_opt_record* __restrict__ records, unsigned long long* n_records,
+				   unsigned long long record_cap)
+{
+	__shared__ FeatShared sh;
+	__shared__ double costs[EBT_COST_HISTORY];
+	const int f = blockIdx.x;
+	if (f >= n_patches) return;
+	DevPatch& gp = patches[f];
+	if (gp.lost) return;  // uniform over the CTA
+	FeatState st;
+	load_state(st, gp);
+	const int track_id = gp.track_id;
+	ebt_event* gring = rings + (size_t)gp.store_slot * EBT_RING;
+	int* gnabla = nablas + (size_t)gp.store_slot * NPIX;
+	for (int k = threadIdx.x; k < st.size; k += NT) sh.ring[k] = gring[(st.tail + k) & RMASK];
+	if (threadIdx.x < EBT_COST_HISTORY) costs[threadIdx.x] = gp.costs[threadIdx.x];
+	st.tail = 0;
+	__syncthreads();
+
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const uint4* ev4 = reinterpret_cast<const uint4*>(events);
+	int n_opt = 0;
+	int buf = 0;
+	uint4 nxt = make_uint4(0, 0, 0, 0);
+	if ((long long)threadIdx.x < n_events) nxt = __ldg(ev4 + threadIdx.x);
+	for (long long base = 0; base < n_events && !st.lost; base += NT)
+	{
+		const uint4 raw = nxt;
+		const long long nidx = base + NT + threadIdx.x;
+		if (nidx < n_events) nxt = __ldg(ev4 + nidx);
+		const int ex = (int)(raw.z & 0xffffu), ey = (int)(raw.z >> 16);
+		const int chunk_len = (int)min((long long)NT, n_events - base);
+		int resume = 0;
+		while (resume < chunk_len)
+		{
+			const bool live = (int)threadIdx.x >= resume && (int)threadIdx.x < chunk_len;
+			const bool inside = live && in_rect(st.rx, st.ry, ex, ey);
+			const unsigned bal = __ballot_sync(0xffffffffu, inside);
+			if (lane == 0) sh.bal[buf][warp] = bal;
+			__syncthreads();
+			unsigned b[NW];
+			int before = 0, total = 0;
+#pragma unroll
+			for (int w = 0; w < NW; ++w)
+			{
+				b[w] = sh.bal[buf][w];
+				const int c = __popc(b[w]);
+				before += (w < warp) ? c : 0;
+				total += c;
+			}
+			buf ^= 1;
+			const int rank = before + __popc(bal & ((1u << lane) - 1u)) + 1;  // if inside
+			// accepted events still needed before isReady() holds
+			const int need = max(P.batch_stride - st.counter, st.num_of_events - st.size);
+			int trig = -1, take = total;
+			if (st.init)
+			{
+				if (need <= 0)
+				{
+					// already ready: the test at feature_detector.cpp:611 fires on
+					// the very next stream event, accepted or not
+					trig = resume;
+					take = (int)((b[resume >> 5] >> (resume & 31)) & 1u);
+				}
+				else if (total >= need)
+				{
+					take = need;
+					int acc = 0;
+#pragma unroll
+					for (int w = 0; w < NW; ++w)
+					{
+						const int c = __popc(b[w]);
+						if (trig < 0 && acc + c >= need)
+							trig = w * 32 + (int)__fns(b[w], 0, need - acc);
+						acc += c;
+					}
+				}
+			}
+			// Patch::addEvent (patch.cpp:37-47) for the first `take` accepted events
+			if (inside && rank <= take)
+			{
+				ebt_event e;
+				*reinterpret_cast<uint4*>(&e) = raw;
+				sh.ring[(st.tail + st.size + rank - 1) & RMASK] = e;
+			}
+			if (take > 0)
+			{
+				const int grown = st.size + take;
+				const int kept = min(grown, st.num_of_events);
+				st.tail = (st.tail + grown - kept) & RMASK;
+				st.size = kept;
+				st.counter += take;
+			}
+			if (trig < 0) break;
+			LmSummary S;
+			optimize_feature(sh, costs, st, ft, P, S);
+			update_num_of_events(sh, st, ft, P);
+			if (threadIdx.x == 0)
+				write_record(records, n_records, record_cap, st, track_id, S,
+							 event_base + base + trig);
+			++n_opt;
+			if (st.lost) break;
+			resume = trig + 1;
+		}
+	}
+	__syncthreads();
+	for (int k = threadIdx.x; k < st.size; k += NT) gring[k] = sh.ring[(st.tail + k) & RMASK];
+	if (n_opt > 0)
+		for (int i = threadIdx.x; i < NPIX; i += NT) gnabla[i] = sh.nabla[i];
+	if (threadIdx.x < EBT_COST_HISTORY) gp.costs[threadIdx.x] = costs[threadIdx.x];
+	st.tail = 0;
+	if (threadIdx.x == 0) store_state(st, gp);
+}
+
+// --------------------------------------------------------------------------
+// Batched kernel: F independent feature-patch problems, one CTA each — one
+// Optimizer::optimize (ft/src/optimizer.cpp:62-206) per problem.
+// --------------------------------------------------------------------------
+__global__ void __launch_bounds__(NT)
+optimize_batch_kernel(const ebt_problem* __restrict__ problems, int n_problems,
+					  const ebt_event* __restrict__ events, FrameTable ft, DevParams P,
+					  ebt_solution* __restrict__ solutions, int* __restrict__ nablas)
+{
+	__shared__ FeatShared sh;
+	__shared__ double costs[EBT_COST_HISTORY];
+	const int b = blockIdx.x;
+	if (b >= n_problems) return;
+	const ebt_problem pr = problems[b];
+	FeatState st;
+	st.ix = pr.init_x;
+	st.iy = pr.init_y;
+#pragma unroll
+	for (int k = 0; k < 4; ++k) st.warp[k] = pr.warp[k];
+	st.flow = pr.flow_dir;
+	st.cur_ts = st.time_last_update = 0;
+	st.time_without_update = 10000000;
+	st.init = 1;
+	st.lost = 0;
+	st.num_of_events = min(max(pr.n_events, P.min_num_events), P.max_num_events);
+	st.size = min(pr.n_events, st.num_of_events);
+	st.counter = pr.n_events;
+	st.tail = 0;
+	st.n_costs = 0;
+	st.frame_slot = pr.frame_slot;
+	st.rx = st.ry = 0;
+	update_rect(st);
+	// window given newest first; ring is chronological
+	const uint4* ev4 = reinterpret_cast<const uint4*>(events + pr.event_offset);
+	for (int k = threadIdx.x; k < st.size; k += NT)
+		*reinterpret_cast<uint4*>(&sh.ring[k]) = __ldg(ev4 + (st.size - 1 - k));
+	__syncthreads();
+	LmSummary S;
+	optimize_feature(sh, costs, st, ft, P, S);
+	if (nablas)
+		for (int i = threadIdx.x; i < NPIX; i += NT) nablas[(size_t)b * NPIX + i] = sh.nabla[i];
+	if (threadIdx.x == 0)
+	{
+		ebt_solution s;
+#pragma unroll
+		for (int k = 0; k < 4; ++k) s.warp[k] = st.warp[k];
+		s.flow_dir = (double)__double2float_rn(st.flow);
+		s.final_cost = S.final_cost;
+		s.x = st.rx + (SIDE - 1) / 2.;
+		s.y = st.ry + (SIDE - 1) / 2.;
+		s.n_successful = S.n_successful;
+		s.n_unsuccessful = S.n_unsuccessful;
+		s.termination = S.termination;
+		s.n_in_rect = S.n_jac * 100 + S.n_cost;  // evaluation counts (jac*100 + cost)
+		s.ts = st.cur_ts;
+		solutions[b] = s;
+	}
+}
+
+// FeatureDetector::newImage loop "updateNumOfEvents(patch)" for every patch
+// (ft/src/feature_detector.cpp:499-502), one CTA per patch.
+__global__ void __launch_bounds__(NT)
+num_events_kernel(DevPatch* __restrict__ patches, int n_patches, FrameTable ft, DevParams P)
+{
+	__shared__ FeatShared sh;
+	const int f = blockIdx.x;
+	if (f >= n_patches) return;
+	FeatState st;
+	load_state(st, patches[f]);
+	update_num_of_events(sh, st, ft, P);
+	if (threadIdx.x == 0)
+	{
+		patches[f].lost = st.lost;
+		patches[f].num_of_events = st.num_of_events;
+	}
+}
+
+// Job (2a): FeatureDetector::getLogImage + getGradients (ft/src/
+// feature_detector.cpp:714-732) fused with Optimizer::setGrad's interleave
+// (ft/src/optimizer.cpp:15-30): L = lut[I] (= log(I/255 + 0.1)/8, 256-entry
+// table uploaded by the host), Sobel 3x3 with BORDER_REFLECT_101, row pass
+// then column pass, written as (gx, gy) pairs.
+__global__ void grad_kernel(const unsigned char* __restrict__ gray, const double* __restrict__ lut,
+							int W, int H, double2* __restrict__ grid)
+{
+	__shared__ double slut[256];
+	for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < 256; i += blockDim.x * blockDim.y)
+		slut[i] = lut[i];
+	__syncthreads();
+	const int x = blockIdx.x * blockDim.x + threadIdx.x;
+	const int y = blockIdx.y * blockDim.y + threadIdx.y;
+	if (x >= W || y >= H) return;
+	const int xm = x - 1 < 0 ? 1 : x - 1, xp = x + 1 >= W ? 2 * W - 2 - (x + 1) : x + 1;
+	const int ym = y - 1 < 0 ? 1 : y - 1, yp = y + 1 >= H ? 2 * H - 2 - (y + 1) : y + 1;
+	double dif[3], smo[3];
+	const int ys[3] = {ym, y, yp};
+#pragma unroll
+	for (int r = 0; r < 3; ++r)
+	{
+		const unsigned char* row = gray + (size_t)ys[r] * W;
+		const double a = slut[row[xm]], b = slut[row[x]], c = slut[row[xp]];
+		dif[r] = c - a;
+		smo[r] = a + b * 2 + c;
+	}
+	double2 g;
+	g.x = dif[0] + dif[1] * 2 + dif[2];
+	g.y = smo[2] - smo[0];
+	grid[(size_t)y * W + x] = g;
+}
+}  // namespace
+
+// --------------------------------------------------------------------------
+// Launchers (called from ebt_api.cu)
+// --------------------------------------------------------------------------
+cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, ebt_event* rings, int* nablas,
+								   const ebt_event* events, long long n_events,
+								   long long event_base, const FrameTable& ft, const DevParams& P,
+								   ebt_opt_record* records, unsigned long long* n_records,
+								   unsigned long long record_cap, cudaStream_t stream)
+{
+	if (n_patches <= 0 || n_events <= 0) return cudaSuccess;
+	track_batch_kernel<<<n_patches, NT, 0, stream>>>(patches, n_patches, rings, nablas, events,
+													 n_events, event_base, ft, P, records,
+													 n_records, record_cap);
+	return cudaGetLastError();
+}
+
+cudaError_t ebt_launch_optimize_batch(const ebt_problem* problems, int n_problems,
+									  const ebt_event* events, const FrameTable& ft,
+									  const DevParams& P, ebt_solution* solutions, int* nablas,
+									  cudaStream_t stream)
+{
+	if (n_problems <= 0) return cudaSuccess;
+	optimize_batch_kernel<<<n_problems, NT, 0, stream>>>(problems, n_problems, events, ft, P,
+														 solutions, nablas);
+	return cudaGetLastError();
+}
+
+cudaError_t ebt_launch_num_events(DevPatch* patches, int n_patches, const FrameTable& ft,
+								  const DevParams& P, cudaStream_t stream)
+{
+	if (n_patches <= 0) return cudaSuccess;
+	num_events_kernel<<<n_patches, NT, 0, stream>>>(patches, n_patches, ft, P);
+	return cudaGetLastError();
+}
+
+cudaError_t ebt_launch_grad(const unsigned char* gray, const double* lut, int W, int H,
+							double2* grid, cudaStream_t stream)
+{
+	const dim3 blk(32, 8);
+	const dim3 grd((W + blk.x - 1) / blk.x, (H + blk.y - 1) / blk.y);
+	grad_kernel<<<grd, blk, 0, stream>>>(gray, lut, W, H, grid);
+	return cudaGetLastError();
+}

@@ -1,0 +1,152 @@
+/* ebt.h — C-ABI of the B200-native event-based feature tracker.
+ *
+ * Drop-in boundary for the reference's tracker API
+ * (/root/reference/implementation/feature_tracker/include/feature_tracker/
+ * feature_detector.h:33-120 and patch.h:14-130).  The reference has no FFI of
+ * its own; each entry point below names the C++ member it replaces.  The C++
+ * facade in include/ebt_tracker.hpp rebuilds tracker::FeatureDetector /
+ * tracker::Patch on top of these calls.
+ *
+ * Conventions: plain pointers and sizes, caller owns every buffer passed in
+ * (copied during the call), outputs are copied into caller arrays, no device
+ * pointer escapes except through the *_device entry points.  Every function
+ * returns 0 on success or a negative EBT_E_* code; ebt_last_error() gives the
+ * message.  There is no CPU fallback: without a CUDA device ebt_create fails.
+ * A context is bound to one CUDA device and one stream and is not thread-safe;
+ * different contexts may be driven from different host threads.
+ */
+#ifndef EBT_H_
+#define EBT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "ebt_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EBT_OK 0
+#define EBT_E_INVALID -1  /* bad argument */
+#define EBT_E_CUDA -2     /* CUDA runtime error (message holds cudaGetErrorString) */
+#define EBT_E_CAPACITY -3 /* a fixed capacity was exceeded */
+#define EBT_E_NODEVICE -4 /* no usable CUDA device */
+
+typedef struct ebt_ctx ebt_ctx;
+
+/* tracker::DetectorParams (feature_detector.h:10-31) + tracker::OptimizerParams
+ * (optimizer.h:16-27) + the constants hard-coded in tracker::Patch
+ * (patch.h:113-114, patch.cpp:22,298), as far as the hot path reads them. */
+typedef struct ebt_params
+{
+	int32_t width, height;          /* DetectorParams::imageSize */
+	int32_t max_patches;            /* DetectorParams::maxPatches (100) */
+	int32_t init_num_events;        /* DetectorParams::initNumEvents (75) */
+	int32_t min_num_events;         /* Patch::minNumOfEvents_ (100) */
+	int32_t max_num_events;         /* Patch::maxNumOfEvents_ (300) */
+	int32_t batch_stride;           /* Patch::isReady literal (30) */
+	int32_t max_iterations;         /* OptimizerParams::maxNumIterations (10) */
+	int32_t border_margin;          /* updateNumOfEvents literal (5) */
+	int32_t record_capacity;        /* optimisation records kept per push (device) */
+	double association_distance;    /* DetectorParams::associationDistance (5) */
+	double huber_loss;              /* OptimizerParams::huberLoss (0.3) */
+	double optimizer_threshold;     /* OptimizerParams::optimizerThreshold (0.6) */
+} ebt_params;
+
+/* Fills *p with the reference defaults for a width x height sensor. */
+int ebt_default_params(ebt_params* p, int width, int height);
+
+/* FeatureDetector::FeatureDetector(const DetectorParams&) (feature_detector.cpp:9-13). */
+int ebt_create(const ebt_params* params, int device, ebt_ctx** out);
+int ebt_destroy(ebt_ctx* ctx);
+const char* ebt_last_error(const ebt_ctx* ctx); /* ctx may be NULL: last create error */
+
+/* FeatureDetector::newImage (feature_detector.cpp:493-541), split at the two
+ * places where the reference calls OpenCV's detector and LK tracker, whose
+ * results the host injects:
+ *   begin:  extractPatches (:543-566) with corners = detectFeatures(image)
+ *           (cornersXY: n x (x, y) doubles) -> log image, Sobel gradients,
+ *           new template grid, associatePatches (:630-664);
+ *   get_uninit / set_flow: FlowEstimator::getFlowPatches (flow_estimator.cpp:
+ *           27-82): query the patches LK would run on, hand back nextPoint;
+ *   end:    updateNumOfEvents for all (:499-502), archive lost patches,
+ *           release unused template grids (:512-535).
+ * gray: height*width uint8, row-major (common::ImageSample::value, CV_8U). */
+int ebt_new_frame_begin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us,
+						const double* cornersXY, int n_corners);
+int ebt_get_uninit(ebt_ctx* ctx, int32_t* track_ids, double* cornersXY, int cap, int* n_out);
+int ebt_set_flow(ebt_ctx* ctx, int32_t track_id, int found, float next_x, float next_y);
+int ebt_new_frame_end(ebt_ctx* ctx);
+
+/* FeatureDetector::updatePatches (feature_detector.cpp:585-619) for n events in
+ * stream order (the reference takes one event per call).  Host buffer; the
+ * call copies it to the device, runs the stream kernel and returns after the
+ * resulting track state and optimisation records are back on the host.
+ * *n_optimizations (may be NULL) receives the number of Optimizer::optimize
+ * equivalents performed. */
+int ebt_push_events(ebt_ctx* ctx, const ebt_event* events, int64_t n, int64_t* n_optimizations);
+
+/* Same, events already resident on the context's device (no H2D copy). */
+int ebt_push_events_device(ebt_ctx* ctx, const ebt_event* d_events, int64_t n,
+						   int64_t* n_optimizations);
+
+/* FeatureDetector::getPatches / getArchivedPatches (feature_detector.h:71-76):
+ * snapshots in list order.  *n_out = number available (may exceed cap). */
+int ebt_get_tracks(ebt_ctx* ctx, ebt_track* out, int cap, int archived, int* n_out);
+
+/* Patch::getIntegratedNabla (patch.h:49): 625 doubles, row-major at<double>(y,x).
+ * which: 0 = integratedNabla_. */
+int ebt_get_patch(ebt_ctx* ctx, int32_t track_id, int which, double* out625);
+
+/* Patch::getTrajectory (patch.h:58): (x, y, t_us) triples. */
+int ebt_get_trajectory(ebt_ctx* ctx, int32_t track_id, double* out_xyt, int cap, int* n_out);
+
+/* Patch::getFinalCosts (patch.h:65). */
+int ebt_get_final_costs(ebt_ctx* ctx, int32_t track_id, double* out, int cap, int* n_out);
+
+/* Optimisation records since the last ebt_clear_records, in the order the
+ * reference would have executed them (Optimizer::getFinalCosts,
+ * optimizer.h:47, is the cost/ts projection of this list). */
+int ebt_get_records(ebt_ctx* ctx, ebt_opt_record* out, int64_t cap, int64_t* n_out);
+int ebt_clear_records(ebt_ctx* ctx);
+
+/* Latest frame's gradients (FeatureDetector::gradX_/gradY_), width*height each. */
+int ebt_get_gradients(ebt_ctx* ctx, double* gx, double* gy);
+
+/* ---- batched entry: F independent feature-patch problems ----------------
+ * One Optimizer::optimize(Patch&) (optimizer.cpp:62-206) per problem.
+ * ebt_frames_add registers a template frame (Optimizer::setGrad,
+ * optimizer.cpp:15-30) and returns its slot (>= 0). */
+int ebt_frames_add(ebt_ctx* ctx, const uint8_t* gray);
+int ebt_frames_get(ebt_ctx* ctx, int slot, double* gx, double* gy);
+int ebt_optimize_batch(ebt_ctx* ctx, const ebt_problem* problems, int64_t n_problems,
+					   const ebt_event* events, int64_t n_events, ebt_solution* solutions,
+					   int32_t* nabla /* n_problems x 625 or NULL */);
+/* Device-resident variant: all pointers are device pointers on ctx's device;
+ * asynchronous on the context stream (call ebt_sync to wait). */
+int ebt_optimize_batch_device(ebt_ctx* ctx, const ebt_problem* d_problems, int64_t n_problems,
+							  const ebt_event* d_events, ebt_solution* d_solutions,
+							  int32_t* d_nabla);
+int ebt_sync(ebt_ctx* ctx);
+
+/* Device-time of the kernels launched since ebt_timing_reset, measured with
+ * CUDA events on the context stream: milliseconds and launch count per kernel
+ * (0 stream kernel, 1 batched kernel, 2 gradient kernel, 3 window-size kernel). */
+int ebt_timing_enable(ebt_ctx* ctx, int on);
+int ebt_timing_get(ebt_ctx* ctx, int kernel, double* ms_total, int64_t* launches);
+int ebt_timing_reset(ebt_ctx* ctx);
+
+/* ABI self-description for binding generators/tests. */
+size_t ebt_sizeof_event(void);
+size_t ebt_sizeof_track(void);
+size_t ebt_sizeof_opt_record(void);
+size_t ebt_sizeof_problem(void);
+size_t ebt_sizeof_solution(void);
+size_t ebt_sizeof_params(void);
+int ebt_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EBT_H_ */

@@ -1,0 +1,77 @@
+"""GPU parity, batched entry: ebt_optimize_batch (CUDA, through the C-ABI) against
+the CPU oracle on the same seeded problems.
+
+Gates (BASELINE.json north_star): integer event patches bit-exact; feature
+positions within 0.05 px; flow angle within 0.5 degrees; same iteration and
+termination path (accepted/rejected step counts and termination type)."""
+import numpy as np
+import pytest
+
+from event_based_odomety_b200 import synth
+from event_based_odomety_b200.cabi import Tracker
+from tests._oracle import CpuBatch, load_oracle
+
+POS_TOL_PX = 0.05
+ANGLE_TOL_DEG = 0.5
+
+
+def _angle_diff_deg(a, b):
+    d = np.abs(a - b) % (2 * np.pi)
+    return np.rad2deg(np.minimum(d, 2 * np.pi - d))
+
+
+def run_case(n, w, h, seed, n_frames=1):
+    ps = synth.make_problems(n, w, h, seed=seed, n_frames=n_frames)
+    ob = CpuBatch(load_oracle(), w, h)
+    tr = Tracker(w, h)
+    for f in ps.frames:
+        so = ob.add_frame(f)
+        sg = tr.add_frame(f)
+        assert so == sg
+        go, gg = ob.gradients(so), tr.frame_gradients(sg)
+        assert np.array_equal(go[0], gg[0]) and np.array_equal(go[1], gg[1]), "gradient grid not bit-exact"
+    osol, onab, _, _ = ob.optimize(ps.problems, ps.events)
+    gsol, gnab = tr.optimize_batch(ps.problems, ps.events)
+    tr.close()
+    return ps, osol, onab, gsol, gnab
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,w,h,seed,nf", [(64, 240, 180, 3064, 1), (500, 346, 260, 3500, 2),
+                                           (2000, 640, 480, 5000, 3)])
+def test_batch_parity(n, w, h, seed, nf):
+    ps, osol, onab, gsol, gnab = run_case(n, w, h, seed, nf)
+    assert np.array_equal(onab.astype(np.int32), gnab), "integer event patches differ"
+    assert np.array_equal(osol["ts"], gsol["ts"])
+    dpos = np.hypot(osol["x"] - gsol["x"], osol["y"] - gsol["y"])
+    dang = _angle_diff_deg(osol["flow_dir"], gsol["flow_dir"])
+    same_path = ((osol["n_successful"] == gsol["n_successful"])
+                 & (osol["n_unsuccessful"] == gsol["n_unsuccessful"])
+                 & (osol["termination"] == gsol["termination"]))
+    print(f"\n[n={n}] max dpos {dpos.max():.3e} px, max dangle {dang.max():.3e} deg, "
+          f"max dcost {np.abs(osol['final_cost'] - gsol['final_cost']).max():.3e}, "
+          f"same LM path {same_path.mean():.4f}")
+    assert dpos.max() <= POS_TOL_PX
+    assert dang.max() <= ANGLE_TOL_DEG
+    assert np.abs(osol["final_cost"] - gsol["final_cost"]).max() < 1e-6
+    assert same_path.mean() >= 0.99
+
+
+@pytest.mark.gpu
+def test_batch_edge_windows():
+    """empty-in-rect window (NaN patch -> Ceres FAILURE path), minimum and maximum windows"""
+    ps = synth.make_problems(8, 240, 180, seed=77)
+    ev = ps.events.copy()
+    p0 = ps.problems[0]
+    sl = slice(p0["event_offset"], p0["event_offset"] + p0["n_events"])
+    ev["x"][sl] = 0  # all events outside the rect -> ||nabla|| = 0 -> NaN
+    ev["y"][sl] = 0
+    ob = CpuBatch(load_oracle(), 240, 180)
+    tr = Tracker(240, 180)
+    ob.add_frame(ps.frames[0]); tr.add_frame(ps.frames[0])
+    osol, onab, _, _ = ob.optimize(ps.problems, ev)
+    gsol, gnab = tr.optimize_batch(ps.problems, ev)
+    assert np.array_equal(onab.astype(np.int32), gnab)
+    assert osol["termination"][0] == 2 and gsol["termination"][0] == 2
+    assert gsol["final_cost"][0] == osol["final_cost"][0] == -1.0
+    assert np.allclose(osol["x"], gsol["x"], atol=POS_TOL_PX) and np.allclose(osol["y"], gsol["y"], atol=POS_TOL_PX)
