@@ -151,3 +151,186 @@ def make_problems(n: int, width: int = 240, height: int = 180, seed: int = 3000,
         true_warp[k] = (c_t, s_t, t_t[0], t_t[1])
         true_flow[k] = phi_t
     return ProblemSet(width, height, frames, problems, events, true_warp, true_flow)
+
+
+# ---------------------------------------------------------------------------
+# Stream generator: frames + events + corner / LK-flow seeds
+# ---------------------------------------------------------------------------
+def harris_corners(gray: np.ndarray, max_corners: int, quality: float = 0.01,
+                   min_distance: float = 10.0, inset: int = PATCH_EXTENT) -> np.ndarray:
+    """Harris response + greedy min-distance selection, in the spirit of
+    cv::goodFeaturesToTrack(..., useHarris, k=0.04) with the reference's mask
+    inset (feature_detector.cpp:34-43, 568-583).  It only has to produce
+    plausible corner seeds: the same seeds are injected into every
+    implementation under test."""
+    I = gray.astype(np.float64)
+    P = np.pad(I, 1, mode="reflect")
+    ix = (P[1:-1, 2:] - P[1:-1, :-2]) * 0.5
+    iy = (P[2:, 1:-1] - P[:-2, 1:-1]) * 0.5
+
+    def box3(a):
+        Q = np.pad(a, 1, mode="reflect")
+        return sum(Q[i:i + a.shape[0], j:j + a.shape[1]] for i in range(3) for j in range(3))
+
+    sxx, syy, sxy = box3(ix * ix), box3(iy * iy), box3(ix * iy)
+    R = sxx * syy - sxy * sxy - 0.04 * (sxx + syy) ** 2
+    h, w = R.shape
+    R[:inset, :] = R[h - inset:, :] = -np.inf
+    R[:, :inset] = R[:, w - inset:] = -np.inf
+    Q = np.pad(R, 1, mode="constant", constant_values=-np.inf)
+    nb = np.max([Q[i:i + h, j:j + w] for i in range(3) for j in range(3) if (i, j) != (1, 1)], axis=0)
+    cand = np.argwhere((R > nb) & (R > quality * R[np.isfinite(R)].max()))
+    order = np.argsort(-R[cand[:, 0], cand[:, 1]], kind="stable")
+    cell = max(int(min_distance), 1)
+    grid = {}
+    out = []
+    for y, x in cand[order]:
+        gy, gx = y // cell, x // cell
+        ok = True
+        for dy in (-1, 0, 1):
+            for dx in (-1, 0, 1):
+                for (py, px) in grid.get((gy + dy, gx + dx), ()):
+                    if (py - y) ** 2 + (px - x) ** 2 < min_distance ** 2:
+                        ok = False
+        if ok:
+            grid.setdefault((gy, gx), []).append((y, x))
+            out.append((float(x), float(y)))
+            if len(out) >= max_corners:
+                break
+    return np.array(out, np.float64).reshape(-1, 2)
+
+
+@dataclasses.dataclass
+class Stream:
+    width: int
+    height: int
+    frames: list          # uint8 (h, w)
+    frame_ts: list        # int microseconds
+    events: np.ndarray    # EVENT records sorted by time
+    corners: list         # per frame (n, 2) float64 corner seeds
+    pose: object          # callable t_s -> (theta, offx, offy)
+    margin: int
+
+    def to_texture(self, t_s, xy):
+        th, ox, oy = self.pose(t_s)
+        c, s = np.cos(th), np.sin(th)
+        cx, cy = (self.width - 1) / 2.0, (self.height - 1) / 2.0
+        x, y = xy[:, 0] - cx, xy[:, 1] - cy
+        return np.stack([c * x - s * y + cx + self.margin + ox,
+                         s * x + c * y + cy + self.margin + oy], axis=1)
+
+    def from_texture(self, t_s, q):
+        th, ox, oy = self.pose(t_s)
+        c, s = np.cos(th), np.sin(th)
+        cx, cy = (self.width - 1) / 2.0, (self.height - 1) / 2.0
+        x, y = q[:, 0] - cx - self.margin - ox, q[:, 1] - cy - self.margin - oy
+        return np.stack([c * x + s * y + cx, -s * x + c * y + cy], axis=1)
+
+    def lk_next(self, k: int, xy: np.ndarray) -> np.ndarray:
+        """What calcOpticalFlowPyrLK(prev=frame k-1, cur=frame k) would return for
+        points xy (ground-truth image motion), as float32 like cv::Point2f."""
+        q = self.to_texture(self.frame_ts[k - 1] * 1e-6, np.asarray(xy, np.float64).reshape(-1, 2))
+        return self.from_texture(self.frame_ts[k] * 1e-6, q).astype(np.float32)
+
+    def events_between(self, k: int) -> np.ndarray:
+        """Events with frame_ts[k] <= t < frame_ts[k+1] (Replayer merge rule:
+        an event goes first when t_event < t_image, replayer.cpp:73)."""
+        t = self.events["t_us"]
+        lo = np.searchsorted(t, self.frame_ts[k], side="left")
+        hi = (np.searchsorted(t, self.frame_ts[k + 1], side="left")
+              if k + 1 < len(self.frame_ts) else len(t))
+        return self.events[lo:hi]
+
+
+def make_stream(width: int, height: int, duration_s: float, rate_ev_s: float, seed: int,
+                max_corners: int = 100, amplitude: float = 30.0, theta_max_deg: float = 5.0,
+                noise_frac: float = 0.05, step_us: int = 1000) -> Stream:
+    rng = np.random.Generator(np.random.PCG64(seed))
+    margin = int(amplitude * 2 + 0.2 * max(width, height) + 8)
+    tex = make_texture(width + 2 * margin, height + 2 * margin, seed * 31 + 7, sigma=2.5).astype(np.float64)
+    f1, f2, f3 = 0.5, 0.35, 0.25
+    thm = np.deg2rad(theta_max_deg)
+
+    def pose(t):
+        return (thm * np.sin(2 * np.pi * f3 * t), amplitude * np.sin(2 * np.pi * f1 * t),
+                amplitude * (1 - np.cos(2 * np.pi * f2 * t)))
+
+    S = Stream(width, height, [], [], np.zeros(0, EVENT), [], pose, margin)
+    yy, xx = np.mgrid[0:height, 0:width]
+    pix = np.stack([xx.ravel().astype(np.float64), yy.ravel().astype(np.float64)], axis=1)
+
+    def render(t):
+        q = S.to_texture(t, pix)
+        return _bilinear(tex, q[:, 0], q[:, 1]).reshape(height, width)
+
+    n_frames = int(duration_s * 1e6 // FRAME_PERIOD_US) + 1
+    for k in range(n_frames):
+        ts = k * FRAME_PERIOD_US
+        fr = np.clip(np.rint(render(ts * 1e-6)), 0, 255).astype(np.uint8)
+        S.frames.append(fr)
+        S.frame_ts.append(ts)
+        S.corners.append(harris_corners(fr, max_corners))
+
+    def simulate(C, n_steps, rr):
+        ref = np.log(render(0.0) / 255.0 + 0.1)
+        chunks = []
+        for i in range(1, n_steps + 1):
+            L = np.log(render(i * step_us * 1e-6) / 255.0 + 0.1)
+            d = L - ref
+            k = np.minimum(np.floor(np.abs(d) / C), 4).astype(np.int64)
+            ys, xs = np.nonzero(k)
+            if len(ys) == 0:
+                continue
+            kk = k[ys, xs]
+            sg = np.sign(d[ys, xs])
+            ref[ys, xs] += sg * kk * C
+            rep = np.repeat(np.arange(len(ys)), kk)
+            ev = np.zeros(len(rep), EVENT)
+            ev["x"] = xs[rep]
+            ev["y"] = ys[rep]
+            ev["polarity"] = sg[rep].astype(np.int8)
+            ev["t_us"] = (i - 1) * step_us + rr.integers(0, step_us, size=len(rep))
+            chunks.append(ev)
+        return np.concatenate(chunks) if chunks else np.zeros(0, EVENT)
+
+    n_steps = int(duration_s * 1e6 // step_us)
+    pilot_steps = min(60, n_steps)
+    pilot = simulate(0.15, pilot_steps, np.random.Generator(np.random.PCG64(seed + 1)))
+    rate0 = len(pilot) / (pilot_steps * step_us * 1e-6)
+    C = float(np.clip(0.15 * rate0 / max(rate_ev_s * (1 - noise_frac), 1.0), 0.01, 2.0))
+    ev = simulate(C, n_steps, np.random.Generator(np.random.PCG64(seed + 2)))
+    n_noise = int(len(ev) * noise_frac / max(1 - noise_frac, 1e-9))
+    nz = np.zeros(n_noise, EVENT)
+    nz["x"] = rng.integers(0, width, n_noise)
+    nz["y"] = rng.integers(0, height, n_noise)
+    nz["polarity"] = rng.choice(np.array([-1, 1], np.int8), n_noise)
+    nz["t_us"] = rng.integers(0, n_steps * step_us, n_noise)
+    ev = np.concatenate([ev, nz])
+    S.events = ev[np.argsort(ev["t_us"], kind="stable")]
+    return S
+
+
+def run_stream(tracker, stream: Stream, n_frames: int | None = None, on_batch=None):
+    """Drive any tracker exposing the C-ABI call shapes (cabi.Tracker or the CPU
+    checkers in tests/_oracle.py) through the stream the way Replayer +
+    Evaluator would (replayer.cpp:56-98, evaluator.cpp:32-101): image k, then
+    the events up to image k+1.  Returns the total number of optimisations."""
+    n_frames = len(stream.frames) if n_frames is None else min(n_frames, len(stream.frames))
+    total = 0
+    for k in range(n_frames):
+        tracker.new_frame_begin(stream.frames[k], stream.frame_ts[k], stream.corners[k])
+        ids, xy = tracker.get_uninit()
+        if len(ids):
+            nxt = stream.lk_next(k, xy)
+            for i, tid in enumerate(ids):
+                inside = (0 <= nxt[i, 0] < stream.width) and (0 <= nxt[i, 1] < stream.height)
+                tracker.set_flow(tid, int(inside), nxt[i, 0], nxt[i, 1])
+        tracker.new_frame_end()
+        ev = stream.events_between(k)
+        if k == n_frames - 1 and n_frames < len(stream.frames):
+            pass
+        n = tracker.push_events(ev)
+        total += n
+        if on_batch:
+            on_batch(k, ev, n)
+    return total

@@ -1,0 +1,95 @@
+"""GPU parity, stream mode: the tracker driven frame by frame / event batch by
+event batch through the C-ABI (ebt_new_frame_* + ebt_push_events) against the
+CPU oracle's per-event FeatureDetector::updatePatches loop on the same seeded
+synthetic stream.
+
+Gates: same optimisations at the same stream events for the same tracks (the
+trigger rule is integer logic), integer event patches bit-exact, window sizes
+equal, positions within 0.05 px, flow angle within 0.5 degrees, same lost
+flags and archive."""
+import numpy as np
+import pytest
+
+from event_based_odomety_b200 import synth
+from event_based_odomety_b200.cabi import Tracker
+from tests._oracle import CpuTracker, load_oracle
+
+POS_TOL_PX = 0.05
+ANGLE_TOL_DEG = 0.5
+
+
+def _angle_diff_deg(a, b):
+    d = np.abs(a - b) % (2 * np.pi)
+    return np.rad2deg(np.minimum(d, 2 * np.pi - d))
+
+
+def compare(stream, max_patches, n_frames=None, split=None):
+    cpu = CpuTracker(load_oracle(), stream.width, stream.height, max_patches)
+    gpu = Tracker(stream.width, stream.height, max_patches)
+    n_cpu = synth.run_stream(cpu, stream, n_frames)
+    if split:
+        # same stream, but every inter-frame batch pushed in `split` pieces:
+        # batching must not change results
+        class Split:
+            def __getattr__(self, k):
+                return getattr(gpu, k)
+
+            def push_events(self, ev):
+                n = 0
+                for part in np.array_split(ev, split):
+                    n += gpu.push_events(part)
+                return n
+        n_gpu = synth.run_stream(Split(), stream, n_frames)
+    else:
+        n_gpu = synth.run_stream(gpu, stream, n_frames)
+    assert n_cpu == n_gpu and n_cpu > 0
+    rc, rg = cpu.records(), gpu.records()
+    assert len(rc) == len(rg) == n_cpu
+    assert np.array_equal(rc["track_id"], rg["track_id"])
+    assert np.array_equal(rc["event_index"], rg["event_index"])
+    assert np.array_equal(rc["ts"], rg["ts"])
+    assert np.array_equal(rc["num_of_events"], rg["num_of_events"])
+    assert np.array_equal(rc["lost"] != 0, rg["lost"] != 0)
+    dpos = np.hypot(rc["x"] - rg["x"], rc["y"] - rg["y"])
+    dang = _angle_diff_deg(rc["flow_dir"], rg["flow_dir"])
+    same = ((rc["n_successful"] == rg["n_successful"]) & (rc["n_unsuccessful"] == rg["n_unsuccessful"])
+            & (rc["termination"] == rg["termination"]))
+    print(f"\n{n_cpu} optimisations: max dpos {dpos.max():.3e} px, max dangle {dang.max():.3e} deg, "
+          f"same LM path {same.mean():.5f}, rejected steps seen {int(rc['n_unsuccessful'].sum())}")
+    assert dpos.max() <= POS_TOL_PX and dang.max() <= ANGLE_TOL_DEG
+    assert same.mean() >= 0.99
+    for arch in (False, True):
+        tc, tg = cpu.tracks(arch), gpu.tracks(arch)
+        assert np.array_equal(tc["track_id"], tg["track_id"])
+        for k in ("lost", "init", "num_of_events", "window_size", "n_optimizations", "n_trajectory",
+                  "current_ts", "time_last_update", "init_time"):
+            assert np.array_equal(tc[k], tg[k]), k
+        assert np.array_equal(tc["counter"], tg["counter"])
+        assert np.abs(tc["rect_x"] - tg["rect_x"]).max() <= POS_TOL_PX
+        for tid in tc["track_id"]:
+            assert np.array_equal(cpu.patch(tid), gpu.patch(tid)), f"integer patch of track {tid}"
+            a, b = cpu.trajectory(tid), gpu.trajectory(tid)
+            assert a.shape == b.shape and np.array_equal(a[:, 2], b[:, 2])
+            assert np.abs(a[:, :2] - b[:, :2]).max() <= POS_TOL_PX
+    cpu.close()
+    gpu.close()
+
+
+@pytest.mark.gpu
+def test_stream_c1_shape():
+    """BASELINE.json configs[0]: DAVIS 240x180, <= 100 patches."""
+    S = synth.make_stream(240, 180, 0.30, 500e3, seed=1001, max_corners=69)
+    compare(S, 100)
+
+
+@pytest.mark.gpu
+def test_stream_split_batches():
+    S = synth.make_stream(240, 180, 0.15, 500e3, seed=1011, max_corners=69)
+    compare(S, 100, split=7)
+
+
+@pytest.mark.gpu
+def test_stream_c2_shape():
+    """BASELINE.json configs[1] shape: 346x260, 500 features, ~2 Mev/s (short)."""
+    S = synth.make_stream(346, 260, 0.10, 2e6, seed=1002, max_corners=500)
+    compare(S, 500)
