@@ -40,6 +40,9 @@ EXPORTS = {
     "ebt_destroy": (C.c_int, [_vp]),
     "ebt_last_error": (C.c_char_p, [_vp]),
     "ebt_new_frame_begin": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int]),
+    "ebt_new_frame_begin_device": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int]),
+    "ebt_reset": (C.c_int, [_vp]),
+    "ebt_measure_fma_peak": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "ebt_get_uninit": (C.c_int, [_vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]),
     "ebt_set_flow": (C.c_int, [_vp, C.c_int32, C.c_int, C.c_float, C.c_float]),
     "ebt_new_frame_end": (C.c_int, [_vp]),
@@ -137,6 +140,19 @@ class Tracker:
         corners = np.ascontiguousarray(corners, np.float64).reshape(-1, 2)
         self._ck(self.lib.ebt_new_frame_begin(self.ctx, _ptr(gray), int(ts), _ptr(corners),
                                               len(corners)))
+
+    def new_frame_begin_device(self, d_gray_ptr, ts, corners):
+        corners = np.ascontiguousarray(corners, np.float64).reshape(-1, 2)
+        self._ck(self.lib.ebt_new_frame_begin_device(self.ctx, _vp(d_gray_ptr), int(ts), _ptr(corners),
+                                                     len(corners)))
+
+    def reset(self):
+        self._ck(self.lib.ebt_reset(self.ctx))
+
+    def measure_fma_peak(self):
+        a, b = C.c_double(), C.c_double()
+        self._ck(self.lib.ebt_measure_fma_peak(self.ctx, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def get_uninit(self, cap=8192):
         ids = np.zeros(cap, np.int32)

@@ -160,12 +160,13 @@ int findFrame(const ebt_ctx* c, int64_t ts)
 }
 
 // Upload one gray frame and build its gradient grid in `slot`.
-int buildGrid(ebt_ctx* ctx, const uint8_t* gray, int slot)
+int buildGrid(ebt_ctx* ctx, const uint8_t* gray, int slot, bool on_device = false)
 {
 	const size_t npx = static_cast<size_t>(ctx->prm.width) * ctx->prm.height;
 	Frame& f = ctx->frames[slot];
 	if (!f.grid) CU(cudaMalloc(&f.grid, npx * sizeof(double2)));
-	CU(cudaMemcpyAsync(ctx->d_gray, gray, npx, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->d_gray, gray, npx,
+					   on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
 	tic(ctx);
 	CU(ebt_launch_grad(ctx->d_gray, ctx->d_lut, ctx->prm.width, ctx->prm.height, f.grid,
 					   ctx->stream));
@@ -361,6 +362,68 @@ int ebt_create(const ebt_params* params, int device, ebt_ctx** out)
 	return EBT_OK;
 }
 
+// Back to the state right after ebt_create (FeatureDetector::setParams ->
+// reset(), feature_detector.cpp:734-742), keeping all allocations.
+int ebt_reset(ebt_ctx* ctx)
+{
+	if (!ctx) return EBT_E_INVALID;
+	CU(cudaSetDevice(ctx->device));
+	CU(cudaStreamSynchronize(ctx->stream));
+	for (auto& f : ctx->frames)
+	{
+		f.alive = false;
+		f.users = 0;
+	}
+	ctx->latest = 0;
+	ctx->h.clear();
+	ctx->tracks.clear();
+	ctx->arch.clear();
+	ctx->arch_tracks.clear();
+	ctx->arch_nabla.clear();
+	ctx->records.clear();
+	ctx->free_slots.clear();
+	for (int s = ctx->prm.max_patches - 1; s >= 0; --s) ctx->free_slots.push_back(s);
+	ctx->host_dirty = true;
+	ctx->next_track_id = 0;
+	ctx->image_counter = 0;
+	ctx->event_index = 0;
+	CU(cudaMemsetAsync(ctx->d_nablas, 0,
+					   static_cast<size_t>(ctx->prm.max_patches) * EBT_PATCH_PIXELS * sizeof(int), ctx->stream));
+	return EBT_OK;
+}
+
+// Measured non-tensor FMA throughput (TFLOP/s) of this device: the roofline
+// denominator for the LM kernels (SURVEY.md 8d asks for a measured figure).
+int ebt_measure_fma_peak(ebt_ctx* ctx, double* fp64_tflops, double* fp32_tflops)
+{
+	if (!ctx) return EBT_E_INVALID;
+	CU(cudaSetDevice(ctx->device));
+	cudaDeviceProp prop;
+	CU(cudaGetDeviceProperties(&prop, ctx->device));
+	const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 4096;
+	void* buf = nullptr;
+	CU(cudaMalloc(&buf, static_cast<size_t>(blocks) * threads * sizeof(double)));
+	for (int fp64 = 1; fp64 >= 0; --fp64)
+	{
+		double best = 0;
+		for (int rep = 0; rep < 5; ++rep)
+		{
+			CU(cudaEventRecord(ctx->ev0, ctx->stream));
+			CU(ebt_launch_fma_peak(fp64, buf, blocks, threads, iters, ctx->stream));
+			CU(cudaEventRecord(ctx->ev1, ctx->stream));
+			CU(cudaEventSynchronize(ctx->ev1));
+			float ms = 0;
+			CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+			const double tf = 2.0 * 8 * iters * static_cast<double>(blocks) * threads / (ms * 1e-3) / 1e12;
+			if (rep > 0 && tf > best) best = tf;
+		}
+		if (fp64 && fp64_tflops) *fp64_tflops = best;
+		if (!fp64 && fp32_tflops) *fp32_tflops = best;
+	}
+	cudaFree(buf);
+	return EBT_OK;
+}
+
 int ebt_sync(ebt_ctx* ctx)
 {
 	if (!ctx) return EBT_E_INVALID;
@@ -403,8 +466,20 @@ int ebt_abi_version(void) { return 1; }
 
 // FeatureDetector::newImage, first half: extractPatches (feature_detector.cpp:
 // 543-566) with injected corners, associatePatches (:630-664).
+static int newFrameBegin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us, const double* cornersXY,
+						 int n_corners, bool on_device);
 int ebt_new_frame_begin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us, const double* cornersXY,
 						int n_corners)
+{
+	return newFrameBegin(ctx, gray, ts_us, cornersXY, n_corners, false);
+}
+int ebt_new_frame_begin_device(ebt_ctx* ctx, const uint8_t* d_gray, int64_t ts_us,
+							   const double* cornersXY, int n_corners)
+{
+	return newFrameBegin(ctx, d_gray, ts_us, cornersXY, n_corners, true);
+}
+static int newFrameBegin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us, const double* cornersXY,
+						 int n_corners, bool on_device)
 {
 	if (!ctx || !gray || n_corners < 0 || (n_corners > 0 && !cornersXY))
 		return fail(ctx, EBT_E_INVALID, "ebt_new_frame_begin: bad argument");
@@ -414,7 +489,7 @@ int ebt_new_frame_begin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us, const 
 		if (!ctx->frames[i].alive) slot = i;
 	if (slot < 0) return fail(ctx, EBT_E_CAPACITY, "ebt_new_frame_begin: too many live template frames");
 	{
-		const int rc = buildGrid(ctx, gray, slot);
+		const int rc = buildGrid(ctx, gray, slot, on_device);
 		if (rc != EBT_OK) return rc;
 	}
 	Frame& f = ctx->frames[slot];

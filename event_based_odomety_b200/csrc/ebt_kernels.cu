@@ -1091,7 +1091,36 @@ __global__ void grad_kernel(const unsigned char* __restrict__ gray, const double
 	g.y = smo[2] - smo[0];
 	grid[(size_t)y * W + x] = g;
 }
+
+// Roofline denominator for the LM kernels: dependent-chain FMA throughput of
+// the non-tensor FP64 / FP32 pipes (8 independent chains per thread).
+template <typename T>
+__global__ void fma_peak_kernel(T* out, int iters, T a, T b)
+{
+	T v[8];
+#pragma unroll
+	for (int k = 0; k < 8; ++k) v[k] = (T)(threadIdx.x + k);
+	for (int i = 0; i < iters; ++i)
+	{
+#pragma unroll
+		for (int k = 0; k < 8; ++k) v[k] = v[k] * a + b;
+	}
+	T s = 0;
+#pragma unroll
+	for (int k = 0; k < 8; ++k) s += v[k];
+	out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
 }  // namespace
+
+cudaError_t ebt_launch_fma_peak(int fp64, void* out, int blocks, int threads, int iters,
+								cudaStream_t stream)
+{
+	if (fp64)
+		fma_peak_kernel<double><<<blocks, threads, 0, stream>>>((double*)out, iters, 1.0000001, 1e-9);
+	else
+		fma_peak_kernel<float><<<blocks, threads, 0, stream>>>((float*)out, iters, 1.0000001f, 1e-9f);
+	return cudaGetLastError();
+}
 
 // --------------------------------------------------------------------------
 // Launchers (called from ebt_api.cu)

@@ -17,3 +17,5 @@ cudaError_t ebt_launch_num_events(DevPatch* patches, int n_patches, const FrameT
 								  const DevParams& P, cudaStream_t stream);
 cudaError_t ebt_launch_grad(const unsigned char* gray, const double* lut, int W, int H,
 							double2* grid, cudaStream_t stream);
+cudaError_t ebt_launch_fma_peak(int fp64, void* out, int blocks, int threads, int iters,
+								cudaStream_t stream);

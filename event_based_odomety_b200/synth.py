@@ -271,11 +271,14 @@ def make_stream(width: int, height: int, duration_s: float, rate_ev_s: float, se
         S.frame_ts.append(ts)
         S.corners.append(harris_corners(fr, max_corners))
 
-    def simulate(C, n_steps, rr):
-        ref = np.log(render(0.0) / 255.0 + 0.1)
+    def simulate(C, n_steps, rr, sub=1):
+        """threshold-crossing event simulation; sub > 1 = every sub-th pixel in
+        x and y only (rate pilot)"""
+        sel = (slice(None, None, sub), slice(None, None, sub))
+        ref = np.log(render(0.0)[sel] / 255.0 + 0.1)
         chunks = []
         for i in range(1, n_steps + 1):
-            L = np.log(render(i * step_us * 1e-6) / 255.0 + 0.1)
+            L = np.log(render(i * step_us * 1e-6)[sel] / 255.0 + 0.1)
             d = L - ref
             k = np.minimum(np.floor(np.abs(d) / C), 4).astype(np.int64)
             ys, xs = np.nonzero(k)
@@ -286,18 +289,22 @@ def make_stream(width: int, height: int, duration_s: float, rate_ev_s: float, se
             ref[ys, xs] += sg * kk * C
             rep = np.repeat(np.arange(len(ys)), kk)
             ev = np.zeros(len(rep), EVENT)
-            ev["x"] = xs[rep]
-            ev["y"] = ys[rep]
+            ev["x"] = xs[rep] * sub
+            ev["y"] = ys[rep] * sub
             ev["polarity"] = sg[rep].astype(np.int8)
             ev["t_us"] = (i - 1) * step_us + rr.integers(0, step_us, size=len(rep))
             chunks.append(ev)
         return np.concatenate(chunks) if chunks else np.zeros(0, EVENT)
 
     n_steps = int(duration_s * 1e6 // step_us)
-    pilot_steps = min(60, n_steps)
-    pilot = simulate(0.15, pilot_steps, np.random.Generator(np.random.PCG64(seed + 1)))
-    rate0 = len(pilot) / (pilot_steps * step_us * 1e-6)
-    C = float(np.clip(0.15 * rate0 / max(rate_ev_s * (1 - noise_frac), 1.0), 0.01, 2.0))
+    # contrast threshold from a pilot over the WHOLE duration on every 4th pixel
+    # in x and y (two passes: the rate is not exactly proportional to 1/C)
+    C = 0.15
+    for _ in range(2):
+        pilot = simulate(C, n_steps, np.random.Generator(np.random.PCG64(seed + 1)), sub=4)
+        n_sub = len(range(0, height, 4)) * len(range(0, width, 4))
+        rate0 = len(pilot) * (width * height / n_sub) / (n_steps * step_us * 1e-6)
+        C = float(np.clip(C * rate0 / max(rate_ev_s * (1 - noise_frac), 1.0), 0.01, 2.0))
     ev = simulate(C, n_steps, np.random.Generator(np.random.PCG64(seed + 2)))
     n_noise = int(len(ev) * noise_frac / max(1 - noise_frac, 1e-9))
     nz = np.zeros(n_noise, EVENT)

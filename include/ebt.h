@@ -75,6 +75,9 @@ const char* ebt_last_error(const ebt_ctx* ctx); /* ctx may be NULL: last create 
  * gray: height*width uint8, row-major (common::ImageSample::value, CV_8U). */
 int ebt_new_frame_begin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us,
 						const double* cornersXY, int n_corners);
+/* Same as ebt_new_frame_begin with the gray frame already on ctx's device. */
+int ebt_new_frame_begin_device(ebt_ctx* ctx, const uint8_t* d_gray, int64_t ts_us,
+							   const double* cornersXY, int n_corners);
 int ebt_get_uninit(ebt_ctx* ctx, int32_t* track_ids, double* cornersXY, int cap, int* n_out);
 int ebt_set_flow(ebt_ctx* ctx, int32_t track_id, int found, float next_x, float next_y);
 int ebt_new_frame_end(ebt_ctx* ctx);
@@ -129,6 +132,14 @@ int ebt_optimize_batch_device(ebt_ctx* ctx, const ebt_problem* d_problems, int64
 							  const ebt_event* d_events, ebt_solution* d_solutions,
 							  int32_t* d_nabla);
 int ebt_sync(ebt_ctx* ctx);
+
+/* FeatureDetector::setParams -> reset() (feature_detector.cpp:734-742): drop all
+ * patches, frames and records, keep the allocations. */
+int ebt_reset(ebt_ctx* ctx);
+
+/* Measured non-tensor FMA throughput of ctx's device in TFLOP/s (roofline
+ * denominator of the LM kernels; not part of the reference's API). */
+int ebt_measure_fma_peak(ebt_ctx* ctx, double* fp64_tflops, double* fp32_tflops);
 
 /* Device-time of the kernels launched since ebt_timing_reset, measured with
  * CUDA events on the context stream: milliseconds and launch count per kernel
