@@ -14,7 +14,7 @@ import numpy as np
 from .records import EVENT, OPT_RECORD, PATCH_PIXELS, PROBLEM, SOLUTION, TRACK
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libebt_cuda.so")
+LIB_PATH = os.environ.get("EBT_LIB", os.path.join(_HERE, "libebt_cuda.so"))
 _vp = C.c_void_p
 
 

@@ -24,9 +24,21 @@
 #define NT EBT_THREADS
 #define NW (EBT_THREADS / 32)
 #define RMASK (EBT_RING - 1)
+#ifdef EBT_INLINE_ALL
+#define EBT_NOINLINE
+#else
+#define EBT_NOINLINE __noinline__
+#endif
+#ifndef EBT_PIX_UNROLL
+#define EBT_PIX_UNROLL 1  // the hot loop must fit the 32 KB L1.5 instruction cache
+#endif
+#ifndef EBT_MIN_CTAS
+#define EBT_MIN_CTAS 4  // resident CTAs per SM the register budget is tuned for
+#endif
 
 namespace
 {
+constexpr int kPixUnroll = EBT_PIX_UNROLL;
 // --------------------------------------------------------------------------
 // Shared memory of one feature CTA
 // --------------------------------------------------------------------------
@@ -47,17 +59,70 @@ __device__ __forceinline__ double warp_sum(double v)
 }
 
 // Sum K per-thread partials over the CTA; every thread receives all K totals
-// (fixed summation order => bitwise identical in all threads).
+// (fixed summation tree => bitwise identical in all threads).
+//
+// Warp stage: a transposing butterfly.  At each of the 5 shuffle steps a lane
+// keeps one half of the values it still holds and hands the other half to its
+// partner, so K values cost K/2 + K/4 + ... ~ K shuffles instead of 5 K; after
+// the last step lane l holds the warp total of value slot_of_lane(l).
+// Block stage: per-warp totals through shared memory, summed in warp order.
+template <int K>
+__device__ __forceinline__ int butterfly_slot(int lane)
+{
+	// mirrors Butterfly<K>::run: both halves are carried as H = ceil(n/2)
+	// entries, the upper one zero padded when n is odd
+	int lo = 0, n = K, real = K;
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1)
+	{
+		const int half = (n + 1) >> 1;
+		if (lane & o)
+		{
+			lo += half;
+			real -= half;
+		}
+		else
+			real = min(real, half);
+		n = half;
+	}
+	return real >= 1 ? lo : -1;
+}
+
+template <int N, int O>
+struct Butterfly
+{
+	template <int K>
+	static __device__ __forceinline__ void run(double (&v)[K], int lane)
+	{
+		constexpr int H = (N + 1) / 2;
+		const bool up = (lane & O) != 0;
+#pragma unroll
+		for (int j = 0; j < H; ++j)
+		{
+			const double hi = (H + j < N) ? v[H + j] : 0.0;
+			const double keep = up ? hi : v[j];
+			const double give = up ? v[j] : hi;
+			v[j] = keep + __shfl_xor_sync(0xffffffffu, give, O);
+		}
+		Butterfly<H, O / 2>::run(v, lane);
+	}
+};
+template <int N>
+struct Butterfly<N, 0>
+{
+	template <int K>
+	static __device__ __forceinline__ void run(double (&)[K], int)
+	{
+	}
+};
+
 template <int K>
 __device__ __forceinline__ void block_sum(FeatShared& sh, double (&acc)[K])
 {
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-	for (int k = 0; k < K; ++k)
-	{
-		const double v = warp_sum(acc[k]);
-		if (lane == 0) sh.red[warp][k] = v;
-	}
+	Butterfly<K, 16>::run(acc, lane);
+	const int slot = butterfly_slot<K>(lane);
+	if (slot >= 0) sh.red[warp][slot] = acc[0];
 	__syncthreads();
 #pragma unroll
 	for (int k = 0; k < K; ++k)
@@ -110,6 +175,7 @@ __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, in
 	const double cs = x[0], sn = x[1], tx = x[2], ty = x[3];
 #pragma unroll
 	for (int k = 0; k < (JAC ? 20 : 2); ++k) acc[k] = 0.0;
+#pragma unroll kPixUnroll
 	for (int i = threadIdx.x; i < NPIX; i += NT)
 	{
 		const int yy = i / SIDE, xx = i - yy * SIDE;
@@ -209,7 +275,7 @@ struct EvalCtx
 // Cost-only evaluation (TrustRegionMinimizer::ComputeCandidatePointAndEvaluateCost,
 // ceres/internal/ceres/trust_region_minimizer.cc:731-747).  r_i = u_i/sqrt(N)+m_i
 // (optimizer_cost.h:29-45), s = sum r_i^2 expanded over the three reduced sums.
-__device__ bool eval_cost(FeatShared& sh, const EvalCtx& E, const double (&x)[5], double& cost)
+__device__ EBT_NOINLINE bool eval_cost(FeatShared& sh, const EvalCtx& E, const double (&x)[5], double& cost)
 {
 	double acc[2];
 	double vy, vx;
@@ -228,7 +294,7 @@ __device__ bool eval_cost(FeatShared& sh, const EvalCtx& E, const double (&x)[5]
 // (ceres/internal/ceres/residual_block.cc:134-175, corrector.cc:81-110: with
 // rho'' <= 0 both r and J are scaled by sqrt(rho')).
 //   dr_i/dq = du_iq/sqrt(N) - u_i A_q / N^1.5
-__device__ bool eval_jac(FeatShared& sh, const EvalCtx& E, const double (&x)[5], double& cost,
+__device__ EBT_NOINLINE bool eval_jac(FeatShared& sh, const EvalCtx& E, const double (&x)[5], double& cost,
 						 double (&Hm)[10], double (&g)[4])
 {
 	double acc[20];
@@ -421,8 +487,8 @@ __device__ bool eval_grad_jac(FeatShared& sh, const EvalCtx& E, const double (&x
 // every thread of the CTA on identical values; the evaluations inside are the
 // only cooperative parts.  params is updated to the lowest-cost accepted
 // iterate, or left alone on FAILURE (solver.cc:428-432).
-__device__ void lm_solve(FeatShared& sh, const EvalCtx& E, const DevParams& P, double (&params)[5],
-						 LmSummary& S)
+__device__ EBT_NOINLINE void lm_solve(FeatShared& sh, const EvalCtx& E, const DevParams& P,
+									  double (&params)[5], LmSummary& S)
 {
 	double x[5], cand[5], best[5];
 	double Hs[10], gs[4], scale[4] = {1, 1, 1, 1}, diag[4] = {0, 0, 0, 0};
@@ -430,142 +496,42 @@ __device__ void lm_solve(FeatShared& sh, const EvalCtx& E, const DevParams& P, d
 	double radius = P.initial_radius, decrease_factor = 2.0;
 	bool reuse_diagonal = false;
 	int consecutive_invalid = 0;
-	double grad_max_norm = 0, final_cost;
+	double grad_max_norm = 0, final_cost = DBL_MAX;
+	double se_min = 0, se_cur = 0, se_ref = 0, se_cand = 0, se_acc_ref = 0, se_acc_cand = 0;
+	int se_nonmono = 0;
+	double rho = 0, cand_cost = 0, model_cost_change = 0;
+	int iteration = 0;
+	bool failed = false;
 #pragma unroll
 	for (int k = 0; k < 5; ++k) x[k] = best[k] = params[k];
 	S.n_successful = S.n_unsuccessful = S.termination = 0;
-	S.n_jac = 1;
+	S.n_jac = 0;
 	S.n_cost = 0;
-	if (!eval_grad_jac(sh, E, x, true, x_cost, Hs, gs, scale, grad_max_norm))
-	{
-		S.termination = 2;
-		S.final_cost = -1.0;
-		return;
-	}
-	final_cost = x_cost;
-	double se_min = x_cost, se_cur = x_cost, se_ref = x_cost, se_cand = x_cost;
-	double se_acc_ref = 0, se_acc_cand = 0;
-	int se_nonmono = 0;
-	int iteration = 0;
-	bool step_successful = true, failed = false;
-	double iter_cost = x_cost, iter_gmn = grad_max_norm;
+	// Outer loop: one residual + Jacobian evaluation per pass (iteration zero,
+	// then once after every accepted step).  Inner loop: trust-region steps from
+	// the current linearisation until one is accepted or the solve terminates.
 	for (;;)
 	{
-		if (step_successful)
+		S.n_jac++;
+		if (!eval_grad_jac(sh, E, x, iteration == 0, x_cost, Hs, gs, scale, grad_max_norm))
 		{
-			if (iteration > 0) S.n_successful++;
-			if (x_cost < minimum_cost)
+			S.termination = 2;
+			if (iteration == 0)
 			{
-				minimum_cost = x_cost;
-#pragma unroll
-				for (int k = 0; k < 5; ++k) best[k] = x[k];
+				S.final_cost = -1.0;  // Summary::initial_cost default (solver.h)
+				return;
 			}
-		}
-		else
-			S.n_unsuccessful++;
-		final_cost = fmin(final_cost, iter_cost);
-		if (iteration >= P.max_iterations) break;
-		if (step_successful && iter_gmn <= P.gradient_tolerance) { S.termination = 1; break; }
-		if (radius <= P.min_radius) { S.termination = 1; break; }
-		++iteration;
-		step_successful = false;
-		iter_gmn = 0;
-		iter_cost = 0;
-
-		if (!reuse_diagonal)
-		{
-#pragma unroll
-			for (int q = 0; q < 4; ++q)
-				diag[q] = fmin(fmax(Hs[hidx(q, q)], P.min_lm_diagonal), P.max_lm_diagonal);
-		}
-		double d2[4], step[4], delta[4];
-#pragma unroll
-		for (int q = 0; q < 4; ++q)
-		{
-			const double l = sqrt(diag[q] / radius);  // lm_diagonal_
-			d2[q] = l * l;
-		}
-		bool valid = solve4(Hs, d2, gs, step);
-		reuse_diagonal = true;
-		double model_cost_change = 0;
-		if (valid)
-		{
-			// -(J step)'(r + J step / 2) = -step'gs - step'Hs step / 2
-			double sg = 0, shs = 0;
-#pragma unroll
-			for (int q = 0; q < 4; ++q)
-			{
-				step[q] = -step[q];
-				sg += step[q] * gs[q];
-			}
-#pragma unroll
-			for (int q = 0; q < 4; ++q)
-			{
-				double row = 0;
-#pragma unroll
-				for (int p = 0; p < 4; ++p)
-					row += Hs[q <= p ? hidx(q, p) : hidx(p, q)] * step[p];
-				shs += step[q] * row;
-			}
-			model_cost_change = -sg - 0.5 * shs;
-			valid = model_cost_change > 0.0;
-		}
-		if (!valid)
-		{
-			if (++consecutive_invalid >= P.max_consecutive_invalid_steps)
-			{
-				S.termination = 2;
-				failed = true;
-				break;
-			}
-			radius /= decrease_factor;
-			decrease_factor *= 2.0;
-			iter_cost = x_cost;
-			continue;
-		}
-		consecutive_invalid = 0;
-#pragma unroll
-		for (int q = 0; q < 4; ++q) delta[q] = step[q] * scale[q];
-		double cand_cost;
-		plus5(x, delta, cand);
-		S.n_cost++;
-		if (!eval_cost(sh, E, cand, cand_cost)) cand_cost = DBL_MAX;
-		{
-			double d5[5];
-#pragma unroll
-			for (int k = 0; k < 5; ++k) d5[k] = x[k] - cand[k];
-			if (norm5(d5) <= P.parameter_tolerance * (x_norm + P.parameter_tolerance))
-			{
-				S.termination = 1;
-				break;
-			}
-		}
-		if (fabs(x_cost - cand_cost) <= P.function_tolerance * x_cost)
-		{
-			S.termination = 1;
+			failed = true;
 			break;
 		}
-		double rho;
-		if (cand_cost >= DBL_MAX)
-			rho = -DBL_MAX;
-		else
-			rho = fmax((se_cur - cand_cost) / model_cost_change,
-					   (se_ref - cand_cost) / (se_acc_ref + model_cost_change));
-		if (rho > P.min_relative_decrease)
+		if (iteration == 0)
 		{
-#pragma unroll
-			for (int k = 0; k < 5; ++k) x[k] = cand[k];
-			x_norm = norm5(x);
-			S.n_jac++;
-			if (!eval_grad_jac(sh, E, x, false, x_cost, Hs, gs, scale, grad_max_norm))
-			{
-				S.termination = 2;
-				failed = true;
-				break;
-			}
-			iter_cost = x_cost;
-			iter_gmn = grad_max_norm;
-			step_successful = true;
+			final_cost = x_cost;
+			se_min = se_cur = se_ref = se_cand = x_cost;  // TrustRegionStepEvaluator ctor
+		}
+		else
+		{
+			// HandleSuccessfulStep: strategy + step evaluator bookkeeping
 			const double t = 2.0 * rho - 1.0;
 			radius = fmin(P.max_radius, radius / fmax(1.0 / 3.0, 1.0 - t * t * t));
 			decrease_factor = 2.0;
@@ -595,12 +561,131 @@ __device__ void lm_solve(FeatShared& sh, const EvalCtx& E, const DevParams& P, d
 				se_acc_ref = se_acc_cand;
 			}
 		}
-		else
+		bool step_successful = true;
+		double iter_cost = x_cost, iter_gmn = grad_max_norm;
+		bool stop = false;
+		for (;;)
 		{
+			// FinalizeIterationAndCheckIfMinimizerCanContinue
+			if (step_successful)
+			{
+				if (iteration > 0) S.n_successful++;
+				if (x_cost < minimum_cost)
+				{
+					minimum_cost = x_cost;
+#pragma unroll
+					for (int k = 0; k < 5; ++k) best[k] = x[k];
+				}
+			}
+			else
+				S.n_unsuccessful++;
+			final_cost = fmin(final_cost, iter_cost);
+			if (iteration >= P.max_iterations) { stop = true; break; }
+			if (step_successful && iter_gmn <= P.gradient_tolerance) { S.termination = 1; stop = true; break; }
+			if (radius <= P.min_radius) { S.termination = 1; stop = true; break; }
+			++iteration;
+			step_successful = false;
+			iter_gmn = 0;
+			iter_cost = 0;
+
+			// LevenbergMarquardtStrategy::ComputeStep
+			if (!reuse_diagonal)
+			{
+#pragma unroll
+				for (int q = 0; q < 4; ++q)
+					diag[q] = fmin(fmax(Hs[hidx(q, q)], P.min_lm_diagonal), P.max_lm_diagonal);
+			}
+			double d2[4], step[4], delta[4];
+#pragma unroll
+			for (int q = 0; q < 4; ++q)
+			{
+				const double l = sqrt(diag[q] / radius);  // lm_diagonal_
+				d2[q] = l * l;
+			}
+			bool valid = solve4(Hs, d2, gs, step);
+			reuse_diagonal = true;
+			model_cost_change = 0;
+			if (valid)
+			{
+				// -(J step)'(r + J step / 2) = -step'gs - step'Hs step / 2
+				double sg = 0, shs = 0;
+#pragma unroll
+				for (int q = 0; q < 4; ++q)
+				{
+					step[q] = -step[q];
+					sg += step[q] * gs[q];
+				}
+#pragma unroll
+				for (int q = 0; q < 4; ++q)
+				{
+					double row = 0;
+#pragma unroll
+					for (int p = 0; p < 4; ++p)
+						row += Hs[q <= p ? hidx(q, p) : hidx(p, q)] * step[p];
+					shs += step[q] * row;
+				}
+				model_cost_change = -sg - 0.5 * shs;
+				valid = model_cost_change > 0.0;
+			}
+			if (!valid)
+			{
+				// HandleInvalidStep
+				if (++consecutive_invalid >= P.max_consecutive_invalid_steps)
+				{
+					S.termination = 2;
+					failed = true;
+					stop = true;
+					break;
+				}
+				radius /= decrease_factor;
+				decrease_factor *= 2.0;
+				iter_cost = x_cost;
+				continue;
+			}
+			consecutive_invalid = 0;
+#pragma unroll
+			for (int q = 0; q < 4; ++q) delta[q] = step[q] * scale[q];
+			plus5(x, delta, cand);
+			S.n_cost++;
+			if (!eval_cost(sh, E, cand, cand_cost)) cand_cost = DBL_MAX;
+			{
+				// ParameterToleranceReached
+				double d5[5];
+#pragma unroll
+				for (int k = 0; k < 5; ++k) d5[k] = x[k] - cand[k];
+				if (norm5(d5) <= P.parameter_tolerance * (x_norm + P.parameter_tolerance))
+				{
+					S.termination = 1;
+					stop = true;
+					break;
+				}
+			}
+			// FunctionToleranceReached
+			if (fabs(x_cost - cand_cost) <= P.function_tolerance * x_cost)
+			{
+				S.termination = 1;
+				stop = true;
+				break;
+			}
+			// TrustRegionStepEvaluator::StepQuality
+			if (cand_cost >= DBL_MAX)
+				rho = -DBL_MAX;
+			else
+				rho = fmax((se_cur - cand_cost) / model_cost_change,
+						   (se_ref - cand_cost) / (se_acc_ref + model_cost_change));
+			if (rho > P.min_relative_decrease)
+			{
+#pragma unroll
+				for (int k = 0; k < 5; ++k) x[k] = cand[k];
+				x_norm = norm5(x);
+				break;  // accepted: re-linearise in the outer loop
+			}
+			// HandleUnsuccessfulStep
 			radius /= decrease_factor;
 			decrease_factor *= 2.0;
 			iter_cost = cand_cost;
 		}
+		if (stop) break;
 	}
 	if (!failed)
 	{
@@ -674,7 +759,7 @@ __device__ __forceinline__ void update_rect(FeatState& st)
 
 // One Optimizer::optimize (ft/src/optimizer.cpp:62-206): integrate, normalise,
 // LM solve, cost filter, state update.
-__device__ void optimize_feature(FeatShared& sh, double* costs, FeatState& st,
+__device__ EBT_NOINLINE void optimize_feature(FeatShared& sh, double* costs, FeatState& st,
 								 const FrameTable& ft, const DevParams& P, LmSummary& S)
 {
 	integrate_window(sh, st);
@@ -752,7 +837,7 @@ __device__ void optimize_feature(FeatShared& sh, double* costs, FeatState& st,
 // 666-712).  cv::warpAffine(flags = WARP_INVERSE_MAP) is nearest-neighbour with
 // 10-bit fixed-point source coordinates; only the cropped rect is sampled, from
 // the LATEST frame's gradients.
-__device__ void update_num_of_events(FeatShared& sh, FeatState& st, const FrameTable& ft,
+__device__ EBT_NOINLINE void update_num_of_events(FeatShared& sh, FeatState& st, const FrameTable& ft,
 									 const DevParams& P)
 {
 	const int W = P.width, H = P.height;
@@ -863,7 +948,7 @@ __device__ void write_record(ebt_opt_record* records, unsigned long long* n_reco
 // Patch::isReady() (patch.cpp:296-299) first holds; the rest of the chunk is
 // then re-tested against the moved rect.
 // --------------------------------------------------------------------------
-__global__ void __launch_bounds__(NT)
+__global__ void __launch_bounds__(NT, EBT_MIN_CTAS)
 track_batch_kernel(DevPatch* __restrict__ patches, int n_patches,
 				   ebt_event* __restrict__ rings, int* __restrict__ nablas,
 				   const ebt_event* __restrict__ events, long long n_events,
@@ -986,7 +1071,7 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches,
 // Batched kernel: F independent feature-patch problems, one CTA each — one
 // Optimizer::optimize (ft/src/optimizer.cpp:62-206) per problem.
 // --------------------------------------------------------------------------
-__global__ void __launch_bounds__(NT)
+__global__ void __launch_bounds__(NT, EBT_MIN_CTAS)
 optimize_batch_kernel(const ebt_problem* __restrict__ problems, int n_problems,
 					  const ebt_event* __restrict__ events, FrameTable ft, DevParams P,
 					  ebt_solution* __restrict__ solutions, int* __restrict__ nablas)
