@@ -32,7 +32,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-from event_based_odomety_b200 import synth  # noqa: E402
+from event_based_odomety_b200 import multi, synth  # noqa: E402
 from event_based_odomety_b200.records import EVENT, OPT_RECORD, TRACK  # noqa: E402
 
 WORKLOADS = {
@@ -57,7 +57,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--duration", type=float, default=0.30, help="stream seconds per step")
-    ap.add_argument("--cpu-frames", type=int, default=3, help="frames of the stream in the CPU sample")
+    ap.add_argument("--cpu-frames", type=int, default=2, help="frames of the stream in the CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -147,20 +147,19 @@ def cpu_lib():
 
 def cpu_run(S, max_feat, n_frames, threads):
     """Reference CPU tracker on the first n_frames frames (+ their event
-    batches).  threads > 1: corners dealt round-robin to independent tracker
-    instances, one host thread each (ctypes releases the GIL)."""
+    batches).  threads > 1: the path shards by independent stream,
+    so every host thread tracks its own copy of the stream sample with its own
+    tracker instance (ctypes releases the GIL); units = threads x optimisations."""
     from tests._oracle import CpuTracker
     lib, kind = cpu_lib()
     flows = FlowCache(S)
     counts = [0] * threads
 
     def work(t):
-        class Shard:
-            corners = [c[t::threads] for c in S.corners]
-        tr = CpuTracker(lib, S.width, S.height, max(1, -(-max_feat // threads)))
+        tr = CpuTracker(lib, S.width, S.height, max_feat)
 
         def frame_fn(k):
-            tr.new_frame_begin(S.frames[k], S.frame_ts[k], Shard.corners[k])
+            tr.new_frame_begin(S.frames[k], S.frame_ts[k], S.corners[k])
         counts[t] = run_step(tr, S, flows, frame_fn, lambda k: tr.push_events(S.events_between(k)), n_frames)
         tr.close()
 
@@ -173,7 +172,7 @@ def cpu_run(S, max_feat, n_frames, threads):
         [x.join() for x in th]
     dt = time.perf_counter() - t0
     n_ev = sum(len(S.events_between(k)) for k in range(n_frames))
-    return sum(counts), n_ev, dt, kind
+    return sum(counts), n_ev * threads, dt, kind
 
 
 def main_reference(args):
@@ -194,7 +193,8 @@ def main_reference(args):
     T = float(np.sum(times))
     value = opts * args.steps / T
     sample = (f"first {args.cpu_frames} frames + event batches of the {args.workload} stream "
-              f"({nev} events, {opts} optimisations per step), features dealt over {cores} threads")
+              f"({nev} events, {opts} optimisations per step summed over {cores} host threads, "
+              f"one independent copy of the stream sample per thread)")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "optimisations/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -229,7 +229,7 @@ def main_ours(args):
     w, h, feat, rate, seed = WORKLOADS[args.workload]
     # rank 0 tracks the named stream; further ranks track independent streams
     # of the same shape (configs[3], seeds 2000 + rank)
-    S = synth.make_stream(w, h, args.duration, rate, seed if rank == 0 else 2000 + rank, max_corners=feat)
+    S = synth.make_stream(w, h, args.duration, rate, multi.stream_seed(seed, rank), max_corners=feat)
     nF = len(S.frames)
     bounds = [(int(np.searchsorted(S.events["t_us"], S.frame_ts[k], "left")),
                int(np.searchsorted(S.events["t_us"], S.frame_ts[k + 1], "left")) if k + 1 < nF else len(S.events))
@@ -303,13 +303,7 @@ def main_ours(args):
 
     # whole-job aggregate: sum of units over ranks / max time over ranks
     def agg(units, seconds):
-        if world == 1:
-            return units, seconds
-        t = torch.tensor([float(units)], device="cuda", dtype=torch.float64)
-        m = torch.tensor([float(seconds)], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        dist.all_reduce(m, op=dist.ReduceOp.MAX)
-        return t.item(), m.item()
+        return multi.aggregate(units, seconds, device="cuda")
 
     g_opts, g_secs = agg(opts, secs)
     g_events, _ = agg(n_events * args.steps, secs)

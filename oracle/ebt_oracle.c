@@ -1300,3 +1300,28 @@ int oracle_patch_integrate(double cx, double cy, const ebt_event* ev, int n,
 	free(p);
 	return NPIX;
 }
+
+/* cv::warpAffine nearest-neighbour index map (the rule update_num_of_events
+ * uses) for a 2x3 dst->src matrix; pinned against cv2 in tests/golden. */
+void oracle_warp_index_map(const double* M6, int w, int h, int32_t* xi, int32_t* yi)
+{
+	for (int y = 0; y < h; ++y)
+		for (int x = 0; x < w; ++x)
+		{
+			const int X0 = cv_round(M6[0] * x * 1024) + cv_round((M6[1] * y + M6[2]) * 1024) + 512;
+			const int Y0 = cv_round(M6[3] * x * 1024) + cv_round((M6[4] * y + M6[5]) * 1024) + 512;
+			xi[y * w + x] = X0 >> 10;
+			yi[y * w + x] = Y0 >> 10;
+		}
+}
+
+/* std::cos(float) / std::sin(float) as the host libm evaluates them
+ * (feature_detector.cpp:702-704), for the GPU float-rounding check. */
+void oracle_cosf_sinf(const float* in, int n, float* c, float* s)
+{
+	for (int i = 0; i < n; ++i)
+	{
+		c[i] = cosf(in[i]);
+		s[i] = sinf(in[i]);
+	}
+}

@@ -97,6 +97,8 @@ def _declare(dll, prefix):
         fn("eval_functor", C.c_int, _vp, C.c_int, _vp, C.c_double, C.c_double, _vp, C.c_double,
            _vp, _vp)
         fn("patch_integrate", C.c_int, C.c_double, C.c_double, _vp, C.c_int, _vp, _vp)
+        fn("warp_index_map", None, _vp, C.c_int, C.c_int, _vp, _vp)
+        fn("cosf_sinf", None, _vp, C.c_int, _vp, _vp)
     return L
 
 
