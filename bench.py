@@ -337,7 +337,7 @@ def main_ours(args):
             "events_per_s": g_events / g_secs,
             "e2e": {"value": ge_opts / ge_secs, "unit": "optimisations/s",
                     "h2d_bytes_per_step": int(n_events * 16 + nF * w * h + 8 * sum(len(c) * 2 for c in S.corners)),
-                    "d2h_bytes_per_step": int(opts_step * OPT_RECORD.itemsize + 2 * nF * feat * 176)},
+                    "d2h_bytes_per_step": int(opts_step * OPT_RECORD.itemsize + 2 * nF * feat * 216)},
             "gpu_launches": int(kt_n + kg_n + kn_n),
             "roofline": {"bound": "fp64", "kernel": "track_batch_kernel", "achieved": achieved,
                          "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
