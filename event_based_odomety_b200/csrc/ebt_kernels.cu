@@ -42,6 +42,16 @@ constexpr int kPixUnroll = EBT_PIX_UNROLL;
 // --------------------------------------------------------------------------
 // Shared memory of one feature CTA
 // --------------------------------------------------------------------------
+// What one pixel evaluation needs besides the evaluation point
+struct EvalCtx
+{
+	const double2* grid;  // (gx, gy) template grid of the patch's frame
+	int W, H;
+	double tlx, tly;      // patch top-left
+	double smm;           // sum m^2
+	double huber_a;
+};
+
 struct __align__(16) FeatShared
 {
 	ebt_event ring[EBT_RING];  // Patch::events_
@@ -49,7 +59,13 @@ struct __align__(16) FeatShared
 	int nabla[NPIX];           // Patch::integratedNabla_, integer valued
 	double red[NW][20];        // cross-warp reduction scratch
 	unsigned bal[2][NW];       // per-warp containment ballots (double buffered)
+	double req[8];             // leader -> workers: evaluation point x[5], cos/sin(phi)
+	double res[8];             // leader -> all: solved x[5], final cost
+	int req_kind;              // 0 stop, 1 cost-only evaluation, 2 Jacobian evaluation
+	int res_i[5];              // n_successful, n_unsuccessful, termination, n_jac, n_cost
+	EvalCtx ctx;               // written by thread 0 before the solve
 };
+
 
 __device__ __forceinline__ double warp_sum(double v)
 {
@@ -263,71 +279,187 @@ __device__ __forceinline__ double huber(double s, double a, double& rho1)
 	return s;
 }
 
-struct EvalCtx
+// --------------------------------------------------------------------------
+// Leader / worker split.  The scalar trust-region logic is one long dependent
+// chain; it runs on warp 0 only (the "leader").  Warps 1..3 ("workers") sit in
+// lm_worker() and join every pixel evaluation the leader posts:
+//   leader : post request -> bar.sync 1 -> pixel_service -> bar.sync 2 -> totals
+//   worker :                 bar.sync 1 -> pixel_service -> bar.arrive 2
+// so a worker blocks once per evaluation.  pixel_service is the only copy of
+// the two pixel loops in the kernel (one call site per role, not inlined).
+// --------------------------------------------------------------------------
+__device__ __forceinline__ void handshake()
 {
-	const double2* grid;
-	int W, H;
-	double tlx, tly;
-	double smm;  // sum m^2
-	double huber_a;
-};
-
-// Cost-only evaluation (TrustRegionMinimizer::ComputeCandidatePointAndEvaluateCost,
-// ceres/internal/ceres/trust_region_minimizer.cc:731-747).  r_i = u_i/sqrt(N)+m_i
-// (optimizer_cost.h:29-45), s = sum r_i^2 expanded over the three reduced sums.
-__device__ EBT_NOINLINE bool eval_cost(FeatShared& sh, const EvalCtx& E, const double (&x)[5], double& cost)
+	asm volatile("bar.sync 1, %0;" ::"n"(EBT_THREADS) : "memory");
+}
+__device__ __forceinline__ void partials_arrive()
 {
-	double acc[2];
-	double vy, vx;
-	sincos(x[4], &vy, &vx);
-	eval_pixels<false>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, acc);
-	block_sum<2>(sh, acc);
-	const double N = 1e-5 + acc[0];
-	const double s = acc[0] / N + 2.0 * acc[1] / sqrt(N) + E.smm;
-	double rho1;
-	cost = 0.5 * huber(s, E.huber_a, rho1);
-	return isfinite(s);
+	asm volatile("bar.arrive 2, %0;" ::"n"(EBT_THREADS) : "memory");
+}
+__device__ __forceinline__ void partials_wait()
+{
+	asm volatile("bar.sync 2, %0;" ::"n"(EBT_THREADS) : "memory");
 }
 
-// Residual + Jacobian evaluation reduced to what the LM step needs: cost,
-// H = J^T J (upper 4x4) and g = J^T r of the Huber-corrected block
-// (ceres/internal/ceres/residual_block.cc:134-175, corrector.cc:81-110: with
-// rho'' <= 0 both r and J are scaled by sqrt(rho')).
-//   dr_i/dq = du_iq/sqrt(N) - u_i A_q / N^1.5
-__device__ EBT_NOINLINE bool eval_jac(FeatShared& sh, const EvalCtx& E, const double (&x)[5], double& cost,
-						 double (&Hm)[10], double (&g)[4])
+// Branch-free reciprocal / reciprocal square root for the leader's chain:
+// MUFU seed (>= 20 bits) + two Newton steps, ~1 ulp, no slow-path call.  The
+// arguments here are normal, finite and non-zero by construction.
+__device__ __forceinline__ double rcp_fast(double x)
 {
-	double acc[20];
+	double r;
+	asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+	double e = fma(-x, r, 1.0);
+	r = fma(r, e, r);
+	e = fma(-x, r, 1.0);
+	return fma(r, e, r);
+}
+__device__ __forceinline__ double rsqrt_fast(double x)
+{
+	double y;
+	asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+	double e = fma(-x * y, y, 1.0);
+	y = fma(0.5 * y, e, y);
+	e = fma(-x * y, y, 1.0);
+	return fma(0.5 * y, e, y);
+}
+// sqrt for x >= 0 (0 -> 0): x * rsqrt(x) with one Heron correction
+__device__ __forceinline__ double sqrt_fast(double x)
+{
+	const double y = rsqrt_fast(fmax(x, DBL_MIN));
+	const double s = x * y;
+	return fma(fma(-s, s, x), 0.5 * y, s);
+}
+
+__device__ __forceinline__ void post_request(FeatShared& sh, int kind, const double (&x)[5], double vx,
+											 double vy)
+{
+	if ((threadIdx.x & 31) == 0)
+	{
+#pragma unroll
+		for (int k = 0; k < 5; ++k) sh.req[k] = x[k];
+		sh.req[5] = vx;
+		sh.req[6] = vy;
+		sh.req_kind = kind;
+	}
+	handshake();
+}
+
+// Cooperative part of one evaluation: every warp evaluates its pixels of the
+// posted request and leaves its warp totals in sh.red[warp][].
+__device__ __noinline__ void pixel_service(FeatShared& sh)
+{
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	double x[5];
+#pragma unroll
+	for (int k = 0; k < 5; ++k) x[k] = sh.req[k];
+	const double vx = sh.req[5], vy = sh.req[6];
+	const EvalCtx& E = sh.ctx;
+	if (sh.req_kind == 2)
+	{
+		double acc[20];
+		eval_pixels<true>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, acc);
+		Butterfly<20, 16>::run(acc, lane);
+		const int slot = butterfly_slot<20>(lane);
+		if (slot >= 0) sh.red[warp][slot] = acc[0];
+	}
+	else
+	{
+		double acc[2];
+		eval_pixels<false>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, acc);
+		Butterfly<2, 16>::run(acc, lane);
+		const int slot = butterfly_slot<2>(lane);
+		if (slot >= 0) sh.red[warp][slot] = acc[0];
+	}
+}
+
+__device__ void lm_worker(FeatShared& sh)
+{
+	for (;;)
+	{
+		handshake();
+		if (sh.req_kind == 0) break;
+		pixel_service(sh);
+		partials_arrive();
+	}
+}
+
+// Leader side of one evaluation at `x`.  kind 2: cost, H = J^T J (upper 4x4) and
+// g = J^T r of the Huber-corrected 625-block; kind 1: cost only.
+//   r_i = u_i/sqrt(N) + m_i, N = 1e-5 + sum u^2   (optimizer_cost.h:29-45)
+//   dr_i/dq = du_iq/sqrt(N) - u_i A_q / N^1.5
+// Loss correction: HuberLoss::Evaluate (loss_function.cc:48-62) on the block's
+// squared norm; with rho'' <= 0 residuals and Jacobian are scaled by
+// sqrt(rho') (residual_block.cc:134-175, corrector.cc:81-110).
+// Returns false when the evaluation is not finite (ResidualBlock::Evaluate's
+// IsArrayValid check).
+__device__ __forceinline__ bool leader_eval(FeatShared& sh, int kind, const double (&x)[5],
+											double& cost, double (&Hm)[10], double (&g)[4])
+{
 	double vy, vx;
 	sincos(x[4], &vy, &vx);
-	eval_pixels<true>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, acc);
-	block_sum<20>(sh, acc);
-	const double suu = acc[0], c = acc[1];
+	post_request(sh, kind, x, vx, vy);
+	pixel_service(sh);
+	partials_wait();
+	const EvalCtx& E = sh.ctx;
+	const double suu = (sh.red[0][0] + sh.red[1][0]) + (sh.red[2][0] + sh.red[3][0]);
+	const double c = (sh.red[0][1] + sh.red[1][1]) + (sh.red[2][1] + sh.red[3][1]);
 	const double N = 1e-5 + suu;
-	const double sq = sqrt(N);
-	const double s = suu / N + 2.0 * c / sq + E.smm;
-	double rho1;
-	cost = 0.5 * huber(s, E.huber_a, rho1);
-	const double iN = 1.0 / N;
-	const double k2 = iN * iN * (2.0 - suu * iN);
-	bool ok = isfinite(s);
-#pragma unroll
-	for (int q = 0; q < 4; ++q)
+	const double iN = rcp_fast(N), isq = rsqrt_fast(N);
+	const double s = suu * iN + 2.0 * c * isq + E.smm;
+	// Huber
+	const double a = E.huber_a, b = a * a;
+	double rho0 = s, rho1 = 1.0;
+	if (s > b)
 	{
-		const double A = acc[2 + q], B = acc[6 + q];
-		g[q] = rho1 * (A * iN + B / sq - A * suu * iN * iN - A * c * iN / sq);
-		ok = ok && isfinite(g[q]);
+		const double ir = rsqrt_fast(s);
+		rho0 = 2.0 * a * (s * ir) - b;
+		rho1 = fmax(DBL_MIN, a * ir);
 	}
-	int k = 0;
+	cost = 0.5 * rho0;
+	bool ok = isfinite(s);
+	if (kind == 2)
+	{
+		double A[4], B[4];
 #pragma unroll
-	for (int q = 0; q < 4; ++q)
-#pragma unroll
-		for (int p = q; p < 4; ++p, ++k)
+		for (int q = 0; q < 4; ++q)
 		{
-			Hm[k] = rho1 * (acc[10 + k] * iN - acc[2 + q] * acc[2 + p] * k2);
-			ok = ok && isfinite(Hm[k]);
+			A[q] = (sh.red[0][2 + q] + sh.red[1][2 + q]) + (sh.red[2][2 + q] + sh.red[3][2 + q]);
+			B[q] = (sh.red[0][6 + q] + sh.red[1][6 + q]) + (sh.red[2][6 + q] + sh.red[3][6 + q]);
 		}
+		// g_q = rho' [ A_q/N (1 - suu/N - c/sqrt(N)) + B_q/sqrt(N) ]
+		const double k1 = rho1 * iN * (1.0 - suu * iN - c * isq);
+		const double kb = rho1 * isq;
+		const double k2 = rho1 * iN * iN * (2.0 - suu * iN);
+		const double kg = rho1 * iN;
+		double chk = 0.0;
+#pragma unroll
+		for (int q = 0; q < 4; ++q)
+		{
+			g[q] = A[q] * k1 + B[q] * kb;
+			chk += g[q];
+		}
+		int k = 0;
+#pragma unroll
+		for (int q = 0; q < 4; ++q)
+#pragma unroll
+			for (int p = q; p < 4; ++p, ++k)
+			{
+				const double G = (sh.red[0][10 + k] + sh.red[1][10 + k]) + (sh.red[2][10 + k] + sh.red[3][10 + k]);
+				Hm[k] = G * kg - A[q] * A[p] * k2;
+				chk += Hm[k];
+			}
+		ok = ok && isfinite(chk);  // any non-finite term poisons the sum
+	}
 	return ok;
+}
+
+// 1/|z| for z = (c, s) with |z|^2 = n2; unit up to rounding in every call here,
+// where the first-order term is exact to double precision.
+__device__ __forceinline__ double inv_len(double n2)
+{
+	const double e = n2 - 1.0;
+	if (fabs(e) < 1e-7) return fma(e, fma(0.375, e, -0.5), 1.0);
+	return rsqrt_fast(n2);
 }
 
 // LocalParameterizationSE2::Plus = T * SE2::exp(delta) (ft/include/
@@ -340,9 +472,9 @@ __device__ __forceinline__ void plus5(const double (&x)[5], const double (&d)[4]
 	double es, ec;
 	sincos(theta, &es, &ec);
 	{
-		const double len = sqrt(ec * ec + es * es);
-		ec /= len;
-		es /= len;
+		const double il = inv_len(ec * ec + es * es);
+		ec *= il;
+		es *= il;
 	}
 	double sbt, omc;
 	if (fabs(theta) < 1e-10)
@@ -353,8 +485,9 @@ __device__ __forceinline__ void plus5(const double (&x)[5], const double (&d)[4]
 	}
 	else
 	{
-		sbt = es / theta;
-		omc = (1. - ec) / theta;
+		const double it = rcp_fast(theta);
+		sbt = es * it;
+		omc = (1. - ec) * it;
 	}
 	const double ex = sbt * d[0] - omc * d[1];
 	const double ey = omc * d[0] + sbt * d[1];
@@ -363,14 +496,14 @@ __device__ __forceinline__ void plus5(const double (&x)[5], const double (&d)[4]
 	const double n2 = rc * rc + rs * rs;
 	if (n2 != 1.0)
 	{
-		const double sc = 2.0 / (1.0 + n2);
+		const double sc = 2.0 * rcp_fast(1.0 + n2);
 		rc *= sc;
 		rs *= sc;
 	}
 	{
-		const double len = sqrt(rc * rc + rs * rs);
-		rc /= len;
-		rs /= len;
+		const double il = inv_len(rc * rc + rs * rs);
+		rc *= il;
+		rs *= il;
 	}
 	out[0] = rc;
 	out[1] = rs;
@@ -385,33 +518,40 @@ __device__ __forceinline__ int hidx(int q, int p)
 	return q * 4 - (q * (q - 1)) / 2 + (p - q);
 }
 
-// Solve (S H S + diag(d2)) y = S g by Cholesky, FP64.  This is the normal-
-// equation form of the least-squares problem DenseQRSolver solves by
+// Solve (Hs + diag(d2)) y = gs by an LDL^T factorisation, FP64.  This is the
+// normal-equation form of the least-squares problem DenseQRSolver solves by
 // Householder QR (ceres/internal/ceres/dense_qr_solver.cc:120-165):
 //   min || [J S; diag(sqrt(d2))] y - [r; 0] ||.
-// Returns false when the factorisation breaks down or y is not finite
-// (Ceres: "Failed to compute a finite step", levenberg_marquardt_strategy.cc:
-// 117-121).
-__device__ bool solve4(const double (&Hs)[10], const double (&d2)[4], const double (&gs)[4],
-					   double (&y)[4])
+// Returns false when a pivot is not positive or y is not finite (Ceres:
+// "Failed to compute a finite step", levenberg_marquardt_strategy.cc:117-121).
+__device__ __forceinline__ bool solve4(const double (&Hs)[10], const double (&d2)[4],
+									   const double (&gs)[4], double (&y)[4])
 {
-	double L[4][4];
+	double L[4][4], D[4], id[4];  // unit lower factor, pivots and their inverses
+	bool pd = true;
 #pragma unroll
-	for (int i = 0; i < 4; ++i)
+	for (int j = 0; j < 4; ++j)
+	{
+		double w[4];
+		double v = Hs[hidx(j, j)] + d2[j];
 #pragma unroll
-		for (int j = 0; j <= i; ++j)
+		for (int k = 0; k < j; ++k)
 		{
-			double v = Hs[hidx(j, i)] + (i == j ? d2[i] : 0.0);
-#pragma unroll
-			for (int k = 0; k < j; ++k) v -= L[i][k] * L[j][k];
-			if (i == j)
-			{
-				if (!(v > 0.0)) return false;
-				L[i][i] = sqrt(v);
-			}
-			else
-				L[i][j] = v / L[j][j];
+			w[k] = L[j][k] * D[k];
+			v -= L[j][k] * w[k];
 		}
+		D[j] = v;
+		pd = pd && (v > 0.0);
+		id[j] = rcp_fast(v);
+#pragma unroll
+		for (int i = j + 1; i < 4; ++i)
+		{
+			double t = Hs[hidx(j, i)];
+#pragma unroll
+			for (int k = 0; k < j; ++k) t -= L[i][k] * w[k];
+			L[i][j] = t * id[j];
+		}
+	}
 	double z[4];
 #pragma unroll
 	for (int i = 0; i < 4; ++i)
@@ -419,17 +559,17 @@ __device__ bool solve4(const double (&Hs)[10], const double (&d2)[4], const doub
 		double v = gs[i];
 #pragma unroll
 		for (int k = 0; k < i; ++k) v -= L[i][k] * z[k];
-		z[i] = v / L[i][i];
+		z[i] = v;
 	}
 #pragma unroll
 	for (int i = 3; i >= 0; --i)
 	{
-		double v = z[i];
+		double v = z[i] * id[i];
 #pragma unroll
 		for (int k = i + 1; k < 4; ++k) v -= L[k][i] * y[k];
-		y[i] = v / L[i][i];
+		y[i] = v;
 	}
-	return isfinite(y[0]) && isfinite(y[1]) && isfinite(y[2]) && isfinite(y[3]);
+	return pd && isfinite((y[0] + y[1]) + (y[2] + y[3]));
 }
 
 struct LmSummary
@@ -444,22 +584,24 @@ __device__ __forceinline__ double norm5(const double (&a)[5])
 	double s = 0;
 #pragma unroll
 	for (int k = 0; k < 5; ++k) s += a[k] * a[k];
-	return sqrt(s);
+	return sqrt_fast(s);
 }
 
-// EvaluateGradientAndJacobian (ceres/internal/ceres/trust_region_minimizer.cc:
-// 231-288): evaluate, fix the Jacobi column scaling at iteration 0, return the
-// scaled system Hs = S H S, gs = S g and the projected gradient max norm.
-__device__ bool eval_grad_jac(FeatShared& sh, const EvalCtx& E, const double (&x)[5], bool iter0,
-							  double& x_cost, double (&Hs)[10], double (&gs)[4],
-							  double (&scale)[4], double& grad_max_norm)
+// Scaled system of EvaluateGradientAndJacobian (ceres/internal/ceres/
+// trust_region_minimizer.cc:231-288): Jacobi column scaling fixed at iteration
+// 0, Hs = S H S, gs = S g, and the projected gradient max norm
+// max |x - Plus(x, -g)|.  The norm only feeds the gradient-tolerance test; its
+// flow-angle component is |g[3]| up to one rounding of x[4], so the Plus is
+// evaluated only when that lower bound does not already decide the test.
+__device__ __forceinline__ void scale_system(const double (&x)[5], bool iter0, const double (&Hm)[10],
+											 const double (&g)[4], double (&scale)[4],
+											 double (&Hs)[10], double (&gs)[4], double tol,
+											 double& grad_max_norm)
 {
-	double Hm[10], g[4];
-	if (!eval_jac(sh, E, x, x_cost, Hm, g)) return false;
 	if (iter0)
 	{
 #pragma unroll
-		for (int q = 0; q < 4; ++q) scale[q] = 1.0 / (1.0 + sqrt(Hm[hidx(q, q)]));
+		for (int q = 0; q < 4; ++q) scale[q] = rcp_fast(1.0 + sqrt_fast(fmax(Hm[hidx(q, q)], 0.0)));
 	}
 #pragma unroll
 	for (int q = 0; q < 4; ++q)
@@ -467,6 +609,12 @@ __device__ bool eval_grad_jac(FeatShared& sh, const EvalCtx& E, const double (&x
 		gs[q] = g[q] * scale[q];
 #pragma unroll
 		for (int p = q; p < 4; ++p) Hs[hidx(q, p)] = Hm[hidx(q, p)] * scale[q] * scale[p];
+	}
+	const double lower = fabs(g[3]) - 8.0 * DBL_EPSILON * (fabs(x[4]) + fabs(g[3]));
+	if (lower > tol)
+	{
+		grad_max_norm = fabs(g[3]);
+		return;
 	}
 	double ng[4], xp[5];
 #pragma unroll
@@ -476,216 +624,218 @@ __device__ bool eval_grad_jac(FeatShared& sh, const EvalCtx& E, const double (&x
 #pragma unroll
 	for (int k = 0; k < 5; ++k) mx = fmax(mx, fabs(x[k] - xp[k]));
 	grad_max_norm = mx;
-	return true;
 }
 
 // TrustRegionMinimizer::Minimize (trust_region_minimizer.cc:67-121 and helpers
 // :300-344, 364-433, 438-470, 680-801), LevenbergMarquardtStrategy
 // (levenberg_marquardt_strategy.cc:67-166), TrustRegionStepEvaluator
 // (trust_region_step_evaluator.cc:40-114), final cost (solver_utils.h:48-56),
-// with the reference's options (ft/src/optimizer.cpp:102-110).  Executed by
-// every thread of the CTA on identical values; the evaluations inside are the
-// only cooperative parts.  params is updated to the lowest-cost accepted
+// with the reference's options (ft/src/optimizer.cpp:102-110).  Leader warp
+// only.  One pixel evaluation per trust-region step: the candidate's cost and
+// its Jacobian sums come from the same pass (Ceres evaluates the cost first and
+// the Jacobian again after acceptance - same values, twice the pixel work);
+// the sums are dropped when the step is rejected.  The step that reaches the
+// iteration limit needs no Jacobian (the limit is tested before the gradient),
+// so it is evaluated cost-only.  params is updated to the lowest-cost accepted
 // iterate, or left alone on FAILURE (solver.cc:428-432).
-__device__ EBT_NOINLINE void lm_solve(FeatShared& sh, const EvalCtx& E, const DevParams& P,
-									  double (&params)[5], LmSummary& S)
+__device__ void lm_solve(FeatShared& sh, const DevParams& P, double (&params)[5], LmSummary& S)
 {
 	double x[5], cand[5], best[5];
+	double Hm[10], g[4];
 	double Hs[10], gs[4], scale[4] = {1, 1, 1, 1}, diag[4] = {0, 0, 0, 0};
 	double x_cost = DBL_MAX, minimum_cost = DBL_MAX, x_norm = -1;
 	double radius = P.initial_radius, decrease_factor = 2.0;
 	bool reuse_diagonal = false;
 	int consecutive_invalid = 0;
 	double grad_max_norm = 0, final_cost = DBL_MAX;
-	double se_min = 0, se_cur = 0, se_ref = 0, se_cand = 0, se_acc_ref = 0, se_acc_cand = 0;
+	double se_min, se_cur, se_ref, se_cand, se_acc_ref = 0, se_acc_cand = 0;
 	int se_nonmono = 0;
-	double rho = 0, cand_cost = 0, model_cost_change = 0;
 	int iteration = 0;
 	bool failed = false;
 #pragma unroll
 	for (int k = 0; k < 5; ++k) x[k] = best[k] = params[k];
 	S.n_successful = S.n_unsuccessful = S.termination = 0;
-	S.n_jac = 0;
+	S.n_jac = 1;
 	S.n_cost = 0;
-	// Outer loop: one residual + Jacobian evaluation per pass (iteration zero,
-	// then once after every accepted step).  Inner loop: trust-region steps from
-	// the current linearisation until one is accepted or the solve terminates.
+	if (!leader_eval(sh, 2, x, x_cost, Hm, g))
+	{
+		S.termination = 2;
+		S.final_cost = -1.0;  // Summary::initial_cost default (solver.h)
+		return;
+	}
+	scale_system(x, true, Hm, g, scale, Hs, gs, P.gradient_tolerance, grad_max_norm);
+	final_cost = x_cost;
+	se_min = se_cur = se_ref = se_cand = x_cost;  // TrustRegionStepEvaluator ctor
+	bool step_successful = true;
+	double iter_cost = x_cost, iter_gmn = grad_max_norm;
 	for (;;)
 	{
-		S.n_jac++;
-		if (!eval_grad_jac(sh, E, x, iteration == 0, x_cost, Hs, gs, scale, grad_max_norm))
+		// FinalizeIterationAndCheckIfMinimizerCanContinue
+		if (step_successful)
 		{
-			S.termination = 2;
-			if (iteration == 0)
+			if (iteration > 0) S.n_successful++;
+			if (x_cost < minimum_cost)
 			{
-				S.final_cost = -1.0;  // Summary::initial_cost default (solver.h)
-				return;
+				minimum_cost = x_cost;
+#pragma unroll
+				for (int k = 0; k < 5; ++k) best[k] = x[k];
 			}
-			failed = true;
-			break;
-		}
-		if (iteration == 0)
-		{
-			final_cost = x_cost;
-			se_min = se_cur = se_ref = se_cand = x_cost;  // TrustRegionStepEvaluator ctor
 		}
 		else
-		{
-			// HandleSuccessfulStep: strategy + step evaluator bookkeeping
-			const double t = 2.0 * rho - 1.0;
-			radius = fmin(P.max_radius, radius / fmax(1.0 / 3.0, 1.0 - t * t * t));
-			decrease_factor = 2.0;
-			reuse_diagonal = false;
-			se_cur = cand_cost;
-			se_acc_cand += model_cost_change;
-			se_acc_ref += model_cost_change;
-			if (se_cur < se_min)
-			{
-				se_min = se_cur;
-				se_nonmono = 0;
-				se_cand = se_cur;
-				se_acc_cand = 0;
-			}
-			else
-			{
-				++se_nonmono;
-				if (se_cur > se_cand)
-				{
-					se_cand = se_cur;
-					se_acc_cand = 0;
-				}
-			}
-			if (se_nonmono == P.max_consecutive_nonmonotonic_steps)
-			{
-				se_ref = se_cand;
-				se_acc_ref = se_acc_cand;
-			}
-		}
-		bool step_successful = true;
-		double iter_cost = x_cost, iter_gmn = grad_max_norm;
-		bool stop = false;
-		for (;;)
-		{
-			// FinalizeIterationAndCheckIfMinimizerCanContinue
-			if (step_successful)
-			{
-				if (iteration > 0) S.n_successful++;
-				if (x_cost < minimum_cost)
-				{
-					minimum_cost = x_cost;
-#pragma unroll
-					for (int k = 0; k < 5; ++k) best[k] = x[k];
-				}
-			}
-			else
-				S.n_unsuccessful++;
-			final_cost = fmin(final_cost, iter_cost);
-			if (iteration >= P.max_iterations) { stop = true; break; }
-			if (step_successful && iter_gmn <= P.gradient_tolerance) { S.termination = 1; stop = true; break; }
-			if (radius <= P.min_radius) { S.termination = 1; stop = true; break; }
-			++iteration;
-			step_successful = false;
-			iter_gmn = 0;
-			iter_cost = 0;
+			S.n_unsuccessful++;
+		final_cost = fmin(final_cost, iter_cost);
+		if (iteration >= P.max_iterations) break;
+		if (step_successful && iter_gmn <= P.gradient_tolerance) { S.termination = 1; break; }
+		if (radius <= P.min_radius) { S.termination = 1; break; }
+		++iteration;
+		step_successful = false;
+		iter_gmn = 0;
+		iter_cost = 0;
 
-			// LevenbergMarquardtStrategy::ComputeStep
-			if (!reuse_diagonal)
-			{
+		// LevenbergMarquardtStrategy::ComputeStep
+		if (!reuse_diagonal)
+		{
 #pragma unroll
-				for (int q = 0; q < 4; ++q)
-					diag[q] = fmin(fmax(Hs[hidx(q, q)], P.min_lm_diagonal), P.max_lm_diagonal);
-			}
-			double d2[4], step[4], delta[4];
+			for (int q = 0; q < 4; ++q)
+				diag[q] = fmin(fmax(Hs[hidx(q, q)], P.min_lm_diagonal), P.max_lm_diagonal);
+		}
+		double d2[4], step[4], delta[4];
+		{
+			const double ir = rcp_fast(radius);
+#pragma unroll
+			for (int q = 0; q < 4; ++q) d2[q] = diag[q] * ir;  // lm_diagonal_^2
+		}
+		bool valid = solve4(Hs, d2, gs, step);
+		reuse_diagonal = true;
+		double model_cost_change = 0;
+		if (valid)
+		{
+			// -(J step)'(r + J step / 2) = -step'gs - step'Hs step / 2
+			double sg = 0, shs = 0;
 #pragma unroll
 			for (int q = 0; q < 4; ++q)
 			{
-				const double l = sqrt(diag[q] / radius);  // lm_diagonal_
-				d2[q] = l * l;
+				step[q] = -step[q];
+				sg += step[q] * gs[q];
 			}
-			bool valid = solve4(Hs, d2, gs, step);
-			reuse_diagonal = true;
-			model_cost_change = 0;
-			if (valid)
+#pragma unroll
+			for (int q = 0; q < 4; ++q)
 			{
-				// -(J step)'(r + J step / 2) = -step'gs - step'Hs step / 2
-				double sg = 0, shs = 0;
+				double row = 0;
 #pragma unroll
-				for (int q = 0; q < 4; ++q)
-				{
-					step[q] = -step[q];
-					sg += step[q] * gs[q];
-				}
-#pragma unroll
-				for (int q = 0; q < 4; ++q)
-				{
-					double row = 0;
-#pragma unroll
-					for (int p = 0; p < 4; ++p)
-						row += Hs[q <= p ? hidx(q, p) : hidx(p, q)] * step[p];
-					shs += step[q] * row;
-				}
-				model_cost_change = -sg - 0.5 * shs;
-				valid = model_cost_change > 0.0;
+				for (int p = 0; p < 4; ++p) row += Hs[q <= p ? hidx(q, p) : hidx(p, q)] * step[p];
+				shs += step[q] * row;
 			}
-			if (!valid)
+			model_cost_change = -sg - 0.5 * shs;
+			valid = model_cost_change > 0.0;
+		}
+		if (!valid)
+		{
+			// HandleInvalidStep
+			if (++consecutive_invalid >= P.max_consecutive_invalid_steps)
 			{
-				// HandleInvalidStep
-				if (++consecutive_invalid >= P.max_consecutive_invalid_steps)
-				{
-					S.termination = 2;
-					failed = true;
-					stop = true;
-					break;
-				}
-				radius /= decrease_factor;
-				decrease_factor *= 2.0;
-				iter_cost = x_cost;
-				continue;
-			}
-			consecutive_invalid = 0;
-#pragma unroll
-			for (int q = 0; q < 4; ++q) delta[q] = step[q] * scale[q];
-			plus5(x, delta, cand);
-			S.n_cost++;
-			if (!eval_cost(sh, E, cand, cand_cost)) cand_cost = DBL_MAX;
-			{
-				// ParameterToleranceReached
-				double d5[5];
-#pragma unroll
-				for (int k = 0; k < 5; ++k) d5[k] = x[k] - cand[k];
-				if (norm5(d5) <= P.parameter_tolerance * (x_norm + P.parameter_tolerance))
-				{
-					S.termination = 1;
-					stop = true;
-					break;
-				}
-			}
-			// FunctionToleranceReached
-			if (fabs(x_cost - cand_cost) <= P.function_tolerance * x_cost)
-			{
-				S.termination = 1;
-				stop = true;
+				S.termination = 2;
+				failed = true;
 				break;
 			}
-			// TrustRegionStepEvaluator::StepQuality
-			if (cand_cost >= DBL_MAX)
-				rho = -DBL_MAX;
-			else
-				rho = fmax((se_cur - cand_cost) / model_cost_change,
-						   (se_ref - cand_cost) / (se_acc_ref + model_cost_change));
-			if (rho > P.min_relative_decrease)
-			{
+			radius /= decrease_factor;
+			decrease_factor *= 2.0;
+			iter_cost = x_cost;
+			continue;
+		}
+		consecutive_invalid = 0;
 #pragma unroll
-				for (int k = 0; k < 5; ++k) x[k] = cand[k];
-				x_norm = norm5(x);
-				break;  // accepted: re-linearise in the outer loop
+		for (int q = 0; q < 4; ++q) delta[q] = step[q] * scale[q];
+		plus5(x, delta, cand);
+		const bool last = iteration >= P.max_iterations;
+		double cand_cost;
+		if (last)
+			S.n_cost++;
+		else
+			S.n_jac++;
+		const bool eval_ok = leader_eval(sh, last ? 1 : 2, cand, cand_cost, Hm, g);
+		// ComputeCandidatePointAndEvaluateCost: a failed evaluation is an
+		// infinitely bad candidate (trust_region_minimizer.cc:731-747)
+		const bool cost_ok = isfinite(cand_cost);
+		if (!cost_ok) cand_cost = DBL_MAX;
+		{
+			// ParameterToleranceReached
+			double d5[5];
+#pragma unroll
+			for (int k = 0; k < 5; ++k) d5[k] = x[k] - cand[k];
+			if (norm5(d5) <= P.parameter_tolerance * (x_norm + P.parameter_tolerance))
+			{
+				S.termination = 1;
+				break;
 			}
+		}
+		// FunctionToleranceReached
+		if (fabs(x_cost - cand_cost) <= P.function_tolerance * x_cost)
+		{
+			S.termination = 1;
+			break;
+		}
+		// TrustRegionStepEvaluator::StepQuality
+		double rho;
+		if (!cost_ok)
+			rho = -DBL_MAX;
+		else
+			rho = fmax((se_cur - cand_cost) * rcp_fast(model_cost_change),
+					   (se_ref - cand_cost) * rcp_fast(se_acc_ref + model_cost_change));
+		if (!(rho > P.min_relative_decrease))
+		{
 			// HandleUnsuccessfulStep
 			radius /= decrease_factor;
 			decrease_factor *= 2.0;
 			iter_cost = cand_cost;
+			continue;
 		}
-		if (stop) break;
+		// HandleSuccessfulStep
+#pragma unroll
+		for (int k = 0; k < 5; ++k) x[k] = cand[k];
+		x_norm = norm5(x);
+		if (!eval_ok)
+		{
+			// cost finite, Jacobian not: "Residual and Jacobian evaluation failed"
+			S.termination = 2;
+			failed = true;
+			break;
+		}
+		x_cost = cand_cost;
+		if (!last) scale_system(x, false, Hm, g, scale, Hs, gs, P.gradient_tolerance, grad_max_norm);
+		{
+			const double t = 2.0 * rho - 1.0;
+			radius = fmin(P.max_radius, radius * rcp_fast(fmax(1.0 / 3.0, 1.0 - t * t * t)));
+		}
+		decrease_factor = 2.0;
+		reuse_diagonal = false;
+		se_cur = cand_cost;
+		se_acc_cand += model_cost_change;
+		se_acc_ref += model_cost_change;
+		if (se_cur < se_min)
+		{
+			se_min = se_cur;
+			se_nonmono = 0;
+			se_cand = se_cur;
+			se_acc_cand = 0;
+		}
+		else
+		{
+			++se_nonmono;
+			if (se_cur > se_cand)
+			{
+				se_cand = se_cur;
+				se_acc_cand = 0;
+			}
+		}
+		if (se_nonmono == P.max_consecutive_nonmonotonic_steps)
+		{
+			se_ref = se_cand;
+			se_acc_ref = se_acc_cand;
+		}
+		step_successful = true;
+		iter_cost = x_cost;
+		iter_gmn = grad_max_norm;
 	}
 	if (!failed)
 	{
@@ -783,18 +933,48 @@ __device__ EBT_NOINLINE void optimize_feature(FeatShared& sh, double* costs, Fea
 	}
 	block_sum<1>(sh, a1);
 
-	EvalCtx E;
-	E.grid = ft.grid[st.frame_slot];
-	E.W = P.width;
-	E.H = P.height;
-	E.tlx = st.rx;
-	E.tly = st.ry;
-	E.smm = a1[0];
-	E.huber_a = P.huber_a;
+	if (threadIdx.x == 0)
+	{
+		EvalCtx& E = sh.ctx;
+		E.grid = ft.grid[st.frame_slot];
+		E.W = P.width;
+		E.H = P.height;
+		E.tlx = st.rx;
+		E.tly = st.ry;
+		E.smm = a1[0];
+		E.huber_a = P.huber_a;
+	}
 	// Patch::getFlow() returns float (patch.h:54)
 	double x[5] = {st.warp[0], st.warp[1], st.warp[2], st.warp[3],
 				   (double)__double2float_rn(st.flow)};
-	lm_solve(sh, E, P, x, S);
+	if (threadIdx.x < 32)
+	{
+		lm_solve(sh, P, x, S);  // its first post_request publishes sh.ctx
+		if (threadIdx.x == 0)
+		{
+#pragma unroll
+			for (int k = 0; k < 5; ++k) sh.res[k] = x[k];
+			sh.res[5] = S.final_cost;
+			sh.res_i[0] = S.n_successful;
+			sh.res_i[1] = S.n_unsuccessful;
+			sh.res_i[2] = S.termination;
+			sh.res_i[3] = S.n_jac;
+			sh.res_i[4] = S.n_cost;
+			sh.req_kind = 0;
+		}
+		handshake();
+	}
+	else
+		lm_worker(sh);
+#pragma unroll
+	for (int k = 0; k < 5; ++k) x[k] = sh.res[k];
+	S.final_cost = sh.res[5];
+	S.n_successful = sh.res_i[0];
+	S.n_unsuccessful = sh.res_i[1];
+	S.termination = sh.res_i[2];
+	S.n_jac = sh.res_i[3];
+	S.n_cost = sh.res_i[4];
+	__syncthreads();
 
 	// addFinalCost + median-of-5 cost filter (optimizer.cpp:127-157)
 	if (threadIdx.x == 0) costs[st.n_costs & (EBT_COST_HISTORY - 1)] = S.final_cost;
