@@ -63,6 +63,7 @@ EXPORTS = {
     "ebt_timing_enable": (C.c_int, [_vp, C.c_int]),
     "ebt_timing_get": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "ebt_timing_reset": (C.c_int, [_vp]),
+    "ebt_set_prefilter_margin": (C.c_int, [_vp, C.c_double]),
     "ebt_sizeof_event": (C.c_size_t, []),
     "ebt_sizeof_track": (C.c_size_t, []),
     "ebt_sizeof_opt_record": (C.c_size_t, []),
@@ -256,6 +257,9 @@ class Tracker:
 
     def sync(self):
         self._ck(self.lib.ebt_sync(self.ctx))
+
+    def set_prefilter_margin(self, pixels):
+        self._ck(self.lib.ebt_set_prefilter_margin(self.ctx, float(pixels)))
 
     def timing(self, on=True):
         self._ck(self.lib.ebt_timing_enable(self.ctx, int(on)))

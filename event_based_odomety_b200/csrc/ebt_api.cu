@@ -75,6 +75,22 @@ struct ebt_ctx
 	ebt_opt_record* d_records = nullptr;
 	unsigned long long* d_nrec = nullptr;
 	std::vector<ebt_opt_record> records;
+	size_t records_sorted = 0;  // records[0 .. records_sorted) are in reference order
+	std::vector<size_t> record_batches;  // end offset of every push behind records_sorted
+
+	// pinned staging (device <-> host copies never touch pageable memory)
+	DevPatch* h_stage = nullptr;
+	ebt_opt_record* rec_stage = nullptr;
+	size_t rec_stage_cap = 0;
+	unsigned long long* nrec_stage = nullptr;
+	std::vector<int> pos_of_id;  // track id -> index in h, rebuilt per push
+
+	// stream-kernel scratch: prefilter mask (P rows), CTA order
+	unsigned* d_mask = nullptr;
+	size_t mask_cap_words = 0;
+	int* d_order = nullptr;
+	int* h_order = nullptr;  // pinned
+	double prefilter_margin = 8.0;
 
 	ebt_event* d_events = nullptr;
 	size_t d_events_cap = 0;
@@ -171,7 +187,8 @@ int buildGrid(ebt_ctx* ctx, const uint8_t* gray, int slot, bool on_device = fals
 	CU(ebt_launch_grad(ctx->d_gray, ctx->d_lut, ctx->prm.width, ctx->prm.height, f.grid,
 					   ctx->stream));
 	toc(ctx, K_GRAD);
-	CU(cudaStreamSynchronize(ctx->stream));
+	// a host source may be reused by the caller as soon as we return
+	if (!on_device) CU(cudaStreamSynchronize(ctx->stream));
 	return EBT_OK;
 }
 
@@ -182,7 +199,9 @@ int uploadPatches(ebt_ctx* ctx)
 		ctx->host_dirty = false;
 		return EBT_OK;
 	}
-	CU(cudaMemcpyAsync(ctx->d_patches, ctx->h.data(), ctx->h.size() * sizeof(DevPatch),
+	// the previous use of h_stage (a download) was synchronised before h was read
+	std::memcpy(ctx->h_stage, ctx->h.data(), ctx->h.size() * sizeof(DevPatch));
+	CU(cudaMemcpyAsync(ctx->d_patches, ctx->h_stage, ctx->h.size() * sizeof(DevPatch),
 					   cudaMemcpyHostToDevice, ctx->stream));
 	ctx->host_dirty = false;
 	return EBT_OK;
@@ -191,10 +210,31 @@ int uploadPatches(ebt_ctx* ctx)
 int downloadPatches(ebt_ctx* ctx)
 {
 	if (ctx->h.empty()) return EBT_OK;
-	CU(cudaMemcpyAsync(ctx->h.data(), ctx->d_patches, ctx->h.size() * sizeof(DevPatch),
+	CU(cudaMemcpyAsync(ctx->h_stage, ctx->d_patches, ctx->h.size() * sizeof(DevPatch),
 					   cudaMemcpyDeviceToHost, ctx->stream));
 	CU(cudaStreamSynchronize(ctx->stream));
+	std::memcpy(ctx->h.data(), ctx->h_stage, ctx->h.size() * sizeof(DevPatch));
 	return EBT_OK;
+}
+
+// Reference order of optimisations: by event, then by position in patches_
+// (feature_detector.cpp:585-619).  patches_ only ever appends new tracks (with
+// increasing ids) and erases in place, so position order is track-id order.
+void sortRecords(ebt_ctx* ctx)
+{
+	size_t lo = ctx->records_sorted;
+	for (size_t hi : ctx->record_batches)
+	{
+		std::sort(ctx->records.begin() + static_cast<std::ptrdiff_t>(lo),
+				  ctx->records.begin() + static_cast<std::ptrdiff_t>(hi),
+				  [](const ebt_opt_record& a, const ebt_opt_record& b) {
+					  if (a.event_index != b.event_index) return a.event_index < b.event_index;
+					  return a.track_id < b.track_id;
+				  });
+		lo = hi;
+	}
+	ctx->records_sorted = ctx->records.size();
+	ctx->record_batches.clear();
 }
 
 void fillTrack(const DevPatch& p, const HostTrack& t, ebt_track& o)
@@ -266,6 +306,12 @@ int ebt_destroy(ebt_ctx* ctx)
 	cudaFree(ctx->d_solutions);
 	cudaFree(ctx->d_bnabla);
 	cudaFree(ctx->d_bevents);
+	cudaFree(ctx->d_mask);
+	cudaFree(ctx->d_order);
+	cudaFreeHost(ctx->h_order);
+	cudaFreeHost(ctx->h_stage);
+	cudaFreeHost(ctx->rec_stage);
+	cudaFreeHost(ctx->nrec_stage);
 	if (ctx->ev0) cudaEventDestroy(ctx->ev0);
 	if (ctx->ev1) cudaEventDestroy(ctx->ev1);
 	if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -341,6 +387,10 @@ int ebt_create(const ebt_params* params, int device, ebt_ctx** out)
 	CUC(cudaMemset(c->d_nablas, 0, P * EBT_PATCH_PIXELS * sizeof(int)));
 	CUC(cudaMalloc(&c->d_records, static_cast<size_t>(params->record_capacity) * sizeof(ebt_opt_record)));
 	CUC(cudaMalloc(&c->d_nrec, sizeof(unsigned long long)));
+	CUC(cudaHostAlloc(&c->h_stage, P * sizeof(DevPatch), cudaHostAllocDefault));
+	CUC(cudaMalloc(&c->d_order, P * sizeof(int)));
+	CUC(cudaHostAlloc(&c->h_order, P * sizeof(int), cudaHostAllocDefault));
+	CUC(cudaHostAlloc(&c->nrec_stage, sizeof(unsigned long long), cudaHostAllocDefault));
 	CUC(cudaMalloc(&c->d_gray, npx));
 	CUC(cudaMalloc(&c->d_lut, 256 * sizeof(double)));
 	{
@@ -381,6 +431,8 @@ int ebt_reset(ebt_ctx* ctx)
 	ctx->arch_tracks.clear();
 	ctx->arch_nabla.clear();
 	ctx->records.clear();
+	ctx->records_sorted = 0;
+	ctx->record_batches.clear();
 	ctx->free_slots.clear();
 	for (int s = ctx->prm.max_patches - 1; s >= 0; --s) ctx->free_slots.push_back(s);
 	ctx->host_dirty = true;
@@ -463,6 +515,14 @@ size_t ebt_sizeof_problem(void) { return sizeof(ebt_problem); }
 size_t ebt_sizeof_solution(void) { return sizeof(ebt_solution); }
 size_t ebt_sizeof_params(void) { return sizeof(ebt_params); }
 int ebt_abi_version(void) { return 1; }
+
+int ebt_set_prefilter_margin(ebt_ctx* ctx, double pixels)
+{
+	if (!ctx || !(pixels >= 0.0) || pixels > 4096.0)
+		return fail(ctx, EBT_E_INVALID, "ebt_set_prefilter_margin: margin must be in [0, 4096] px");
+	ctx->prefilter_margin = pixels;
+	return EBT_OK;
+}
 
 // FeatureDetector::newImage, first half: extractPatches (feature_detector.cpp:
 // 543-566) with injected corners, associatePatches (:630-664).
@@ -661,36 +721,67 @@ static int runStream(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t
 		const int rc = uploadPatches(ctx);
 		if (rc != EBT_OK) return rc;
 	}
+	// scratch for the prefilter mask
+	const int wpr = ebt_mask_words_per_row(n);
+	const size_t need_words = static_cast<size_t>(P) * static_cast<size_t>(wpr);
+	if (need_words > ctx->mask_cap_words)
+	{
+		cudaFree(ctx->d_mask);
+		ctx->d_mask = nullptr;
+		ctx->mask_cap_words = 0;
+		const size_t cap = need_words + need_words / 4;
+		CU(cudaMalloc(&ctx->d_mask, cap * sizeof(unsigned)));
+		ctx->mask_cap_words = cap;
+	}
+	// CTA order: features with the most optimisations in the previous push first
+	// (longest-processing-time-first keeps the kernel's tail short)
+	for (int i = 0; i < P; ++i) ctx->h_order[i] = i;
+	std::stable_sort(ctx->h_order, ctx->h_order + P,
+					 [&](int a, int b) { return ctx->h[static_cast<size_t>(a)].last_n_opt > ctx->h[static_cast<size_t>(b)].last_n_opt; });
+	CU(cudaMemcpyAsync(ctx->d_order, ctx->h_order, static_cast<size_t>(P) * sizeof(int), cudaMemcpyHostToDevice,
+					   ctx->stream));
 	CU(cudaMemsetAsync(ctx->d_nrec, 0, sizeof(unsigned long long), ctx->stream));
 	tic(ctx);
-	CU(ebt_launch_track_batch(ctx->d_patches, P, ctx->d_rings, ctx->d_nablas, d_events, n,
-							  ctx->event_index, frameTable(ctx), ctx->dp, ctx->d_records,
-							  ctx->d_nrec, static_cast<unsigned long long>(ctx->prm.record_capacity),
-							  ctx->stream));
+	CU(ebt_launch_track_batch(ctx->d_patches, P, ctx->d_order, ctx->d_rings, ctx->d_nablas, d_events, n,
+							  ctx->event_index, ctx->d_mask, wpr, ctx->prefilter_margin, frameTable(ctx),
+							  ctx->dp, ctx->d_records, ctx->d_nrec,
+							  static_cast<unsigned long long>(ctx->prm.record_capacity), ctx->stream));
 	toc(ctx, K_TRACK);
-	unsigned long long nrec = 0;
-	CU(cudaMemcpyAsync(&nrec, ctx->d_nrec, sizeof(nrec), cudaMemcpyDeviceToHost, ctx->stream));
-	CU(cudaMemcpyAsync(ctx->h.data(), ctx->d_patches, ctx->h.size() * sizeof(DevPatch),
+	CU(cudaMemcpyAsync(ctx->nrec_stage, ctx->d_nrec, sizeof(unsigned long long), cudaMemcpyDeviceToHost,
+					   ctx->stream));
+	CU(cudaMemcpyAsync(ctx->h_stage, ctx->d_patches, ctx->h.size() * sizeof(DevPatch),
 					   cudaMemcpyDeviceToHost, ctx->stream));
 	CU(cudaStreamSynchronize(ctx->stream));
+	std::memcpy(ctx->h.data(), ctx->h_stage, ctx->h.size() * sizeof(DevPatch));
+	const unsigned long long nrec = *ctx->nrec_stage;
 	ctx->event_index += n;
 	if (n_opt) *n_opt = static_cast<int64_t>(nrec);
 	const unsigned long long got =
 		std::min<unsigned long long>(nrec, static_cast<unsigned long long>(ctx->prm.record_capacity));
 	if (got > 0)
 	{
-		std::vector<ebt_opt_record> recs(got);
-		CU(cudaMemcpy(recs.data(), ctx->d_records, got * sizeof(ebt_opt_record), cudaMemcpyDeviceToHost));
-		// reference order: by event, then by position in patches_
-		std::unordered_map<int, int> pos;
-		for (size_t i = 0; i < ctx->h.size(); ++i) pos[ctx->h[i].track_id] = static_cast<int>(i);
-		std::sort(recs.begin(), recs.end(), [&](const ebt_opt_record& a, const ebt_opt_record& b) {
-			if (a.event_index != b.event_index) return a.event_index < b.event_index;
-			return pos[a.track_id] < pos[b.track_id];
-		});
-		for (const ebt_opt_record& r : recs)
+		if (got > ctx->rec_stage_cap)
 		{
-			HostTrack& t = ctx->tracks[pos[r.track_id]];
+			cudaFreeHost(ctx->rec_stage);
+			ctx->rec_stage = nullptr;
+			ctx->rec_stage_cap = 0;
+			const size_t cap = static_cast<size_t>(got) + static_cast<size_t>(got) / 2 + 4096;
+			CU(cudaHostAlloc(&ctx->rec_stage, cap * sizeof(ebt_opt_record), cudaHostAllocDefault));
+			ctx->rec_stage_cap = cap;
+		}
+		CU(cudaMemcpyAsync(ctx->rec_stage, ctx->d_records, got * sizeof(ebt_opt_record), cudaMemcpyDeviceToHost,
+						   ctx->stream));
+		CU(cudaStreamSynchronize(ctx->stream));
+		// A feature's records sit in the buffer in the order it produced them,
+		// which is all the per-track histories need; the global reference order
+		// is restored lazily (sortRecords) when the list is asked for.
+		ctx->pos_of_id.assign(static_cast<size_t>(ctx->next_track_id), -1);
+		for (size_t i = 0; i < ctx->h.size(); ++i) ctx->pos_of_id[static_cast<size_t>(ctx->h[i].track_id)] = static_cast<int>(i);
+		const ebt_opt_record* recs = ctx->rec_stage;
+		for (unsigned long long k = 0; k < got; ++k)
+		{
+			const ebt_opt_record& r = recs[k];
+			HostTrack& t = ctx->tracks[static_cast<size_t>(ctx->pos_of_id[static_cast<size_t>(r.track_id)])];
 			t.costs.push_back(r.final_cost);  // Patch::addFinalCost
 			if (!(r.lost & 2))                // not dropped by the cost filter (optimizer.cpp:151-156)
 			{
@@ -699,11 +790,32 @@ static int runStream(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t
 				t.traj.push_back(static_cast<double>(r.ts));
 			}
 		}
-		ctx->records.insert(ctx->records.end(), recs.begin(), recs.end());
+		ctx->records.insert(ctx->records.end(), recs, recs + got);
+		ctx->record_batches.push_back(ctx->records.size());
 	}
 	if (nrec > got)
 		return fail(ctx, EBT_E_CAPACITY,
 					"ebt_push_events: record_capacity exceeded; tracks are valid, records/trajectories of this push are truncated");
+	return EBT_OK;
+}
+
+// A push is cut into pieces small enough for the prefilter scratch (256 MiB);
+// the stream kernel is sequential in the events, so the cut changes nothing.
+static int runPieces(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t* n_opt)
+{
+	if (n_opt) *n_opt = 0;
+	const int64_t rows = std::max<int64_t>(1, static_cast<int64_t>(ctx->h.size()));
+	const int64_t piece = std::max<int64_t>(1 << 16, ((int64_t(1) << 26) / rows) * 32);
+	int64_t done = 0;
+	do
+	{
+		const int64_t m = std::min(piece, n - done);
+		int64_t k = 0;
+		const int rc = runStream(ctx, d_events + done, m, &k);
+		if (n_opt) *n_opt += k;
+		if (rc != EBT_OK) return rc;
+		done += m;
+	} while (done < n);
 	return EBT_OK;
 }
 
@@ -726,7 +838,7 @@ int ebt_push_events(ebt_ctx* ctx, const ebt_event* events, int64_t n, int64_t* n
 		CU(cudaMemcpyAsync(ctx->d_events, events, static_cast<size_t>(n) * sizeof(ebt_event),
 						   cudaMemcpyHostToDevice, ctx->stream));
 	}
-	return runStream(ctx, ctx->d_events, n, n_optimizations);
+	return runPieces(ctx, ctx->d_events, n, n_optimizations);
 }
 
 int ebt_push_events_device(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t* n_optimizations)
@@ -734,7 +846,7 @@ int ebt_push_events_device(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, i
 	if (!ctx || n < 0 || (n > 0 && !d_events))
 		return fail(ctx, EBT_E_INVALID, "ebt_push_events_device: bad argument");
 	CU(cudaSetDevice(ctx->device));
-	return runStream(ctx, d_events, n, n_optimizations);
+	return runPieces(ctx, d_events, n, n_optimizations);
 }
 
 int ebt_get_tracks(ebt_ctx* ctx, ebt_track* out, int cap, int archived, int* n_out)
@@ -814,6 +926,7 @@ int ebt_get_final_costs(ebt_ctx* ctx, int32_t track_id, double* out, int cap, in
 int ebt_get_records(ebt_ctx* ctx, ebt_opt_record* out, int64_t cap, int64_t* n_out)
 {
 	if (!ctx || !n_out) return fail(ctx, EBT_E_INVALID, "ebt_get_records: bad argument");
+	sortRecords(ctx);
 	const int64_t n = static_cast<int64_t>(ctx->records.size());
 	if (out) std::memcpy(out, ctx->records.data(), static_cast<size_t>(std::min(n, cap)) * sizeof(ebt_opt_record));
 	*n_out = n;
@@ -824,6 +937,8 @@ int ebt_clear_records(ebt_ctx* ctx)
 {
 	if (!ctx) return EBT_E_INVALID;
 	ctx->records.clear();
+	ctx->records_sorted = 0;
+	ctx->record_batches.clear();
 	return EBT_OK;
 }
 

@@ -25,7 +25,9 @@ struct DevPatch
 	long long cur_ts, time_last_update, time_without_update, init_time;
 	int init, lost, track_id, num_of_events;
 	int counter, win_tail, win_size, n_costs;
-	int frame_slot, store_slot, pad0, pad1;
+	int frame_slot, store_slot;
+	int last_n_opt;  // optimisations in the previous push (CTA ordering estimate)
+	int pad1;
 };
 
 // Solver constants: the reference's OptimizerParams

@@ -1117,29 +1117,149 @@ __device__ void write_record(ebt_opt_record* records, unsigned long long* n_reco
 }
 
 // --------------------------------------------------------------------------
+// Prefilter: one bit per (feature, event) saying whether the event's pixel lies
+// in the feature's *candidate region* = its rect at launch grown by `margin`
+// pixels on every side.  While the rect stays within `margin` of where it was,
+// every event the rect can contain is a candidate, so the feature CTA only has
+// to visit set bits (about 2 % of the stream) instead of every event.
+//
+// HBM/L2-bound integer work.  Grid: x = tiles of 1024 events, y = groups of
+// PF_FEATS features.  A CTA stages the packed (x, y) word of its 1024 events in
+// shared memory once; each warp then takes one feature at a time and produces
+// the tile's 32 mask words with 32 ballots, stored as one coalesced 128-byte
+// row segment mask[feature][tile * 32 + lane].
+// --------------------------------------------------------------------------
+#define PF_TILE 1024
+#define PF_THREADS 256
+#define PF_FEATS 128
+
+// integer bounds [x0, x1] x [y0, y1] of the candidate region (a superset)
+__device__ __forceinline__ int4 candidate_bounds(double rx, double ry, double margin)
+{
+	int4 b;
+	b.x = (int)floor(rx - margin);
+	b.y = (int)ceil(rx + margin + SIDE);
+	b.z = (int)floor(ry - margin);
+	b.w = (int)ceil(ry + margin + SIDE);
+	return b;
+}
+
+__global__ void __launch_bounds__(PF_THREADS)
+prefilter_kernel(const DevPatch* __restrict__ patches, int n_patches,
+				 const ebt_event* __restrict__ events, long long n_events, double margin,
+				 unsigned* __restrict__ mask, int words_per_row)
+{
+	__shared__ unsigned xy[PF_TILE];
+	__shared__ int4 bounds[PF_FEATS];
+	const long long tile0 = (long long)blockIdx.x * PF_TILE;
+	const int f0 = blockIdx.y * PF_FEATS;
+	const unsigned* ev32 = reinterpret_cast<const unsigned*>(events);
+	for (int k = threadIdx.x; k < PF_TILE; k += PF_THREADS)
+	{
+		const long long e = tile0 + k;
+		// word 2 of the 16-byte record = x | y << 16; out-of-range events get a
+		// coordinate no region contains
+		xy[k] = e < n_events ? __ldg(ev32 + 4 * e + 2) : 0xffffffffu;
+	}
+	for (int k = threadIdx.x; k < PF_FEATS; k += PF_THREADS)
+	{
+		const int f = f0 + k;
+		int4 b = make_int4(1, 0, 1, 0);  // empty
+		if (f < n_patches && !patches[f].lost) b = candidate_bounds(patches[f].rx, patches[f].ry, margin);
+		bounds[k] = b;
+	}
+	__syncthreads();
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	for (int k = warp; k < PF_FEATS && f0 + k < n_patches; k += PF_THREADS / 32)
+	{
+		const int4 b = bounds[k];
+		unsigned mine = 0;
+#pragma unroll 8
+		for (int j = 0; j < 32; ++j)
+		{
+			const unsigned v = xy[j * 32 + lane];
+			const int x = (int)(v & 0xffffu), y = (int)(v >> 16);
+			const unsigned bal = __ballot_sync(0xffffffffu, x >= b.x && x <= b.y && y >= b.z && y <= b.w);
+			if (lane == j) mine = bal;
+		}
+		mask[(size_t)(f0 + k) * words_per_row + (size_t)blockIdx.x * 32 + lane] = mine;
+	}
+}
+
+// Rebuild one feature's mask row from event `from` on, for a candidate region
+// around the rect's current position (the rect left the old region).
+__device__ void rebuild_mask_row(unsigned* __restrict__ row, const ebt_event* __restrict__ events,
+								 long long n_events, long long from, double rx, double ry, double margin)
+{
+	const int4 b = candidate_bounds(rx, ry, margin);
+	const unsigned* ev32 = reinterpret_cast<const unsigned*>(events);
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const long long n_words = (n_events + 31) >> 5;
+	for (long long w = (from >> 5) + warp; w < n_words; w += NW)
+	{
+		const long long e = w * 32 + lane;
+		bool in = false;
+		if (e < n_events)
+		{
+			const unsigned v = __ldg(ev32 + 4 * e + 2);
+			const int x = (int)(v & 0xffffu), y = (int)(v >> 16);
+			in = x >= b.x && x <= b.y && y >= b.z && y <= b.w;
+		}
+		const unsigned bal = __ballot_sync(0xffffffffu, in);
+		if (lane == 0) row[w] = bal;
+	}
+	__syncthreads();  // global writes of this CTA are read back by this CTA only
+}
+
+// --------------------------------------------------------------------------
 // Stream kernel: FeatureDetector::updatePatches (ft/src/feature_detector.cpp:
 // 585-619) for a whole batch of events, one CTA per feature.  Between two
 // newImage calls a patch's evolution depends only on its own state and the
 // ordered event stream, so each CTA replays the per-event loop for its
-// feature: events are read as coalesced 16-byte records (one per thread per
-// chunk, next chunk prefetched), containment is tested against the current
-// rect, accepted events are compacted in order into the shared-memory window
-// ring (ballot + prefix), and the optimisation fires at exactly the event where
-// Patch::isReady() (patch.cpp:296-299) first holds; the rest of the chunk is
-// then re-tested against the moved rect.
+// feature.  It walks its prefilter mask row in segments of SEG_WORDS words:
+// the set bits of a segment are expanded, in stream order, into a candidate
+// list in shared memory; candidates are loaded as 16-byte records (one per
+// thread per chunk), tested against the CURRENT rect, compacted in order into
+// the shared-memory window ring (ballot + prefix), and the optimisation fires
+// at exactly the event where Patch::isReady() (patch.cpp:296-299) first holds;
+// the rest of the chunk is then re-tested against the moved rect.  When the
+// rect leaves the candidate region the CTA rebuilds its own mask row from the
+// next event on and carries on.
+// CTA b works on feature order[b] (host-sorted, heaviest first).
 // --------------------------------------------------------------------------
+#define SEG_WORDS NT
+
+__device__ __forceinline__ int window_need(const FeatState& st, const DevParams& P)
+{
+	// accepted events still needed before isReady() holds
+	return max(P.batch_stride - st.counter, st.num_of_events - st.size);
+}
+
+__device__ __forceinline__ void window_grow(FeatState& st, int take)
+{
+	// Patch::addEvent (patch.cpp:37-47): append, trim to numOfEvents_
+	const int grown = st.size + take;
+	const int kept = min(grown, st.num_of_events);
+	st.tail = (st.tail + grown - kept) & RMASK;
+	st.size = kept;
+	st.counter += take;
+}
+
 __global__ void __launch_bounds__(NT, EBT_MIN_CTAS)
-track_batch_kernel(DevPatch* __restrict__ patches, int n_patches,
+track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __restrict__ order,
 				   ebt_event* __restrict__ rings, int* __restrict__ nablas,
 				   const ebt_event* __restrict__ events, long long n_events,
-				   long long event_base, FrameTable ft, DevParams P,
+				   long long event_base, unsigned* mask, int words_per_row, double margin,
+				   FrameTable ft, DevParams P,
 				   ebt_opt_record* __restrict__ records, unsigned long long* n_records,
 				   unsigned long long record_cap)
 {
 	__shared__ FeatShared sh;
 	__shared__ double costs[EBT_COST_HISTORY];
-	const int f = blockIdx.x;
-	if (f >= n_patches) return;
+	__shared__ unsigned short cand[SEG_WORDS * 32];
+	__shared__ int scan[NW];
+	if ((int)blockIdx.x >= n_patches) return;
+	const int f = order[blockIdx.x];
 	DevPatch& gp = patches[f];
 	if (gp.lost) return;  // uniform over the CTA
 	FeatState st;
@@ -1154,89 +1274,146 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches,
 
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const uint4* ev4 = reinterpret_cast<const uint4*>(events);
+	unsigned* row = mask + (size_t)f * words_per_row;
+	double srx = st.rx, sry = st.ry;  // where the candidate region is centred
+	long long start = 0;              // first stream event not consumed yet
 	int n_opt = 0;
 	int buf = 0;
-	uint4 nxt = make_uint4(0, 0, 0, 0);
-	if ((long long)threadIdx.x < n_events) nxt = __ldg(ev4 + threadIdx.x);
-	for (long long base = 0; base < n_events && !st.lost; base += NT)
-	{
-		const uint4 raw = nxt;
-		const long long nidx = base + NT + threadIdx.x;
-		if (nidx < n_events) nxt = __ldg(ev4 + nidx);
-		const int ex = (int)(raw.z & 0xffffu), ey = (int)(raw.z >> 16);
-		const int chunk_len = (int)min((long long)NT, n_events - base);
-		int resume = 0;
-		while (resume < chunk_len)
+
+	// One Optimizer::optimize at stream event `at`, then the bookkeeping around it.
+	// Returns true when the mask row was rebuilt (the caller re-expands).
+	auto optimise_at = [&](long long at) -> bool {
+		LmSummary S;
+		optimize_feature(sh, costs, st, ft, P, S);
+		update_num_of_events(sh, st, ft, P);
+		if (threadIdx.x == 0) write_record(records, n_records, record_cap, st, track_id, S, event_base + at);
+		++n_opt;
+		start = at + 1;
+		if (!st.lost && (fabs(st.rx - srx) > margin || fabs(st.ry - sry) > margin))
 		{
-			const bool live = (int)threadIdx.x >= resume && (int)threadIdx.x < chunk_len;
-			const bool inside = live && in_rect(st.rx, st.ry, ex, ey);
-			const unsigned bal = __ballot_sync(0xffffffffu, inside);
-			if (lane == 0) sh.bal[buf][warp] = bal;
-			__syncthreads();
-			unsigned b[NW];
-			int before = 0, total = 0;
+			rebuild_mask_row(row, events, n_events, start, st.rx, st.ry, margin);
+			srx = st.rx;
+			sry = st.ry;
+			return true;
+		}
+		return false;
+	};
+
+	// Already ready at entry (newImage shrank numOfEvents_): the test at
+	// feature_detector.cpp:611 fires on the very next stream event, accepted or
+	// not.  Event 0 is then the only candidate of a first pass.
+	bool pre = st.init && n_events > 0 && window_need(st, P) <= 0;
+
+	const long long n_words = (n_events + 31) >> 5;
+	long long seg = start >> 5;
+	while (!st.lost && seg < n_words)
+	{
+		// expand the segment's set bits into cand[], in stream order
+		const long long wi = seg + threadIdx.x;
+		unsigned word = wi < n_words ? row[wi] : 0u;
+		{
+			const long long first = wi << 5;
+			if (first < start) word = (start - first >= 32) ? 0u : (word & (0xffffffffu << (int)(start - first)));
+		}
+		const int c = __popc(word);
+		int incl = c;
 #pragma unroll
-			for (int w = 0; w < NW; ++w)
+		for (int o = 1; o < 32; o <<= 1)
+		{
+			const int up = __shfl_up_sync(0xffffffffu, incl, o);
+			if (lane >= o) incl += up;
+		}
+		if (lane == 31) scan[warp] = incl;
+		__syncthreads();
+		int off = incl - c, n_c = 0;
+#pragma unroll
+		for (int w = 0; w < NW; ++w)
+		{
+			const int v = scan[w];
+			off += (w < warp) ? v : 0;
+			n_c += v;
+		}
+		if (pre)
+		{
+			n_c = 1;
+			if (threadIdx.x == 0) cand[0] = 0;
+		}
+		else
+			while (word)
 			{
-				b[w] = sh.bal[buf][w];
-				const int c = __popc(b[w]);
-				before += (w < warp) ? c : 0;
-				total += c;
+				const int bit = __ffs(word) - 1;
+				word &= word - 1;
+				cand[off++] = (unsigned short)(threadIdx.x * 32 + bit);
 			}
-			buf ^= 1;
-			const int rank = before + __popc(bal & ((1u << lane) - 1u)) + 1;  // if inside
-			// accepted events still needed before isReady() holds
-			const int need = max(P.batch_stride - st.counter, st.num_of_events - st.size);
-			int trig = -1, take = total;
-			if (st.init)
+		__syncthreads();
+
+		bool restart = false;
+		for (int cbase = 0; cbase < n_c && !restart && !st.lost; cbase += NT)
+		{
+			const int chunk_len = min(NT, n_c - cbase);
+			uint4 raw = make_uint4(0, 0, 0, 0);
+			if ((int)threadIdx.x < chunk_len) raw = __ldg(ev4 + ((seg << 5) + cand[cbase + threadIdx.x]));
+			const int ex = (int)(raw.z & 0xffffu), ey = (int)(raw.z >> 16);
+			int resume = 0;
+			while (resume < chunk_len)
 			{
-				if (need <= 0)
+				const bool live = (int)threadIdx.x >= resume && (int)threadIdx.x < chunk_len;
+				const bool inside = live && in_rect(st.rx, st.ry, ex, ey);
+				const unsigned bal = __ballot_sync(0xffffffffu, inside);
+				if (lane == 0) sh.bal[buf][warp] = bal;
+				__syncthreads();
+				unsigned b[NW];
+				int before = 0, total = 0;
+#pragma unroll
+				for (int w = 0; w < NW; ++w)
 				{
-					// already ready: the test at feature_detector.cpp:611 fires on
-					// the very next stream event, accepted or not
+					b[w] = sh.bal[buf][w];
+					const int cw = __popc(b[w]);
+					before += (w < warp) ? cw : 0;
+					total += cw;
+				}
+				buf ^= 1;
+				const int rank = before + __popc(bal & ((1u << lane) - 1u)) + 1;  // if inside
+				const int need = window_need(st, P);  // <= 0 only in the `pre` pass
+				int trig = -1, take = total;
+				if (st.init && need <= 0)
+				{
 					trig = resume;
 					take = (int)((b[resume >> 5] >> (resume & 31)) & 1u);
 				}
-				else if (total >= need)
+				else if (st.init && total >= need)
 				{
 					take = need;
 					int acc = 0;
 #pragma unroll
 					for (int w = 0; w < NW; ++w)
 					{
-						const int c = __popc(b[w]);
-						if (trig < 0 && acc + c >= need)
-							trig = w * 32 + (int)__fns(b[w], 0, need - acc);
-						acc += c;
+						const int cw = __popc(b[w]);
+						if (trig < 0 && acc + cw >= need) trig = w * 32 + (int)__fns(b[w], 0, need - acc);
+						acc += cw;
 					}
 				}
+				if (inside && rank <= take)
+					*reinterpret_cast<uint4*>(&sh.ring[(st.tail + st.size + rank - 1) & RMASK]) = raw;
+				if (take > 0) window_grow(st, take);
+				if (trig < 0) break;
+				const long long at = (seg << 5) + cand[cbase + trig];
+				if (optimise_at(at))
+				{
+					restart = true;
+					break;
+				}
+				if (st.lost) break;
+				resume = trig + 1;
 			}
-			// Patch::addEvent (patch.cpp:37-47) for the first `take` accepted events
-			if (inside && rank <= take)
-			{
-				ebt_event e;
-				*reinterpret_cast<uint4*>(&e) = raw;
-				sh.ring[(st.tail + st.size + rank - 1) & RMASK] = e;
-			}
-			if (take > 0)
-			{
-				const int grown = st.size + take;
-				const int kept = min(grown, st.num_of_events);
-				st.tail = (st.tail + grown - kept) & RMASK;
-				st.size = kept;
-				st.counter += take;
-			}
-			if (trig < 0) break;
-			LmSummary S;
-			optimize_feature(sh, costs, st, ft, P, S);
-			update_num_of_events(sh, st, ft, P);
-			if (threadIdx.x == 0)
-				write_record(records, n_records, record_cap, st, track_id, S,
-							 event_base + base + trig);
-			++n_opt;
-			if (st.lost) break;
-			resume = trig + 1;
 		}
+		__syncthreads();  // cand[] is rewritten by the next expansion
+		if (pre)
+		{
+			pre = false;  // event 0 is consumed; expand the real first segment
+			restart = true;
+		}
+		seg = restart ? (start >> 5) : seg + SEG_WORDS;
 	}
 	__syncthreads();
 	for (int k = threadIdx.x; k < st.size; k += NT) gring[k] = sh.ring[(st.tail + k) & RMASK];
@@ -1244,7 +1421,11 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches,
 		for (int i = threadIdx.x; i < NPIX; i += NT) gnabla[i] = sh.nabla[i];
 	if (threadIdx.x < EBT_COST_HISTORY) gp.costs[threadIdx.x] = costs[threadIdx.x];
 	st.tail = 0;
-	if (threadIdx.x == 0) store_state(st, gp);
+	if (threadIdx.x == 0)
+	{
+		store_state(st, gp);
+		gp.last_n_opt = n_opt;  // load estimate for the next launch's CTA order
+	}
 }
 
 // --------------------------------------------------------------------------
@@ -1390,17 +1571,29 @@ cudaError_t ebt_launch_fma_peak(int fp64, void* out, int blocks, int threads, in
 // --------------------------------------------------------------------------
 // Launchers (called from ebt_api.cu)
 // --------------------------------------------------------------------------
-cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, ebt_event* rings, int* nablas,
-								   const ebt_event* events, long long n_events,
-								   long long event_base, const FrameTable& ft, const DevParams& P,
-								   ebt_opt_record* records, unsigned long long* n_records,
-								   unsigned long long record_cap, cudaStream_t stream)
+cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, const int* order,
+								   ebt_event* rings, int* nablas, const ebt_event* events,
+								   long long n_events, long long event_base, unsigned* mask,
+								   int words_per_row, double margin, const FrameTable& ft,
+								   const DevParams& P, ebt_opt_record* records,
+								   unsigned long long* n_records, unsigned long long record_cap,
+								   cudaStream_t stream)
 {
 	if (n_patches <= 0 || n_events <= 0) return cudaSuccess;
-	track_batch_kernel<<<n_patches, NT, 0, stream>>>(patches, n_patches, rings, nablas, events,
-													 n_events, event_base, ft, P, records,
-													 n_records, record_cap);
+	const dim3 pf_grid((unsigned)((n_events + PF_TILE - 1) / PF_TILE),
+					   (unsigned)((n_patches + PF_FEATS - 1) / PF_FEATS));
+	prefilter_kernel<<<pf_grid, PF_THREADS, 0, stream>>>(patches, n_patches, events, n_events, margin,
+														  mask, words_per_row);
+	track_batch_kernel<<<n_patches, NT, 0, stream>>>(patches, n_patches, order, rings, nablas, events,
+													 n_events, event_base, mask, words_per_row,
+													 margin, ft, P, records, n_records, record_cap);
 	return cudaGetLastError();
+}
+
+// mask words per feature row for a push of n_events (whole prefilter tiles)
+int ebt_mask_words_per_row(long long n_events)
+{
+	return (int)(((n_events + PF_TILE - 1) / PF_TILE) * (PF_TILE / 32));
 }
 
 cudaError_t ebt_launch_optimize_batch(const ebt_problem* problems, int n_problems,

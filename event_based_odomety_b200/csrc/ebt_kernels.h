@@ -4,11 +4,18 @@
 
 #include "ebt_device_types.h"
 
-cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, ebt_event* rings, int* nablas,
-								   const ebt_event* events, long long n_events,
-								   long long event_base, const FrameTable& ft, const DevParams& P,
-								   ebt_opt_record* records, unsigned long long* n_records,
-								   unsigned long long record_cap, cudaStream_t stream);
+// Prefilter + stream kernel.  `order`: feature index per CTA (heaviest first);
+// `mask`: n_patches x words_per_row scratch words (ebt_mask_words_per_row);
+// `margin`: how far (px) a rect may drift from its position at launch before
+// its CTA rebuilds its candidate row.
+cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, const int* order,
+								   ebt_event* rings, int* nablas, const ebt_event* events,
+								   long long n_events, long long event_base, unsigned* mask,
+								   int words_per_row, double margin, const FrameTable& ft,
+								   const DevParams& P, ebt_opt_record* records,
+								   unsigned long long* n_records, unsigned long long record_cap,
+								   cudaStream_t stream);
+int ebt_mask_words_per_row(long long n_events);
 cudaError_t ebt_launch_optimize_batch(const ebt_problem* problems, int n_problems,
 									  const ebt_event* events, const FrameTable& ft,
 									  const DevParams& P, ebt_solution* solutions, int* nablas,

@@ -148,6 +148,15 @@ int ebt_timing_enable(ebt_ctx* ctx, int on);
 int ebt_timing_get(ebt_ctx* ctx, int kernel, double* ms_total, int64_t* launches);
 int ebt_timing_reset(ebt_ctx* ctx);
 
+/* Tuning knob of ebt_push_events (not part of the reference's API).  Before the
+ * stream kernel runs, a prefilter marks, per feature, the events whose pixel
+ * lies within `pixels` of the feature's patch rect as it stands at the push;
+ * the feature then only visits marked events.  A rect that drifts further than
+ * `pixels` during the push re-marks its remaining events, so results do not
+ * depend on the value (0 forces a re-mark after nearly every optimisation).
+ * Default 8. */
+int ebt_set_prefilter_margin(ebt_ctx* ctx, double pixels);
+
 /* ABI self-description for binding generators/tests. */
 size_t ebt_sizeof_event(void);
 size_t ebt_sizeof_track(void);

@@ -23,9 +23,11 @@ def _angle_diff_deg(a, b):
     return np.rad2deg(np.minimum(d, 2 * np.pi - d))
 
 
-def compare(stream, max_patches, n_frames=None, split=None):
+def compare(stream, max_patches, n_frames=None, split=None, margin=None):
     cpu = CpuTracker(load_oracle(), stream.width, stream.height, max_patches)
     gpu = Tracker(stream.width, stream.height, max_patches)
+    if margin is not None:
+        gpu.set_prefilter_margin(margin)
     n_cpu = synth.run_stream(cpu, stream, n_frames)
     if split:
         # same stream, but every inter-frame batch pushed in `split` pieces:
@@ -93,3 +95,13 @@ def test_stream_c2_shape():
     """BASELINE.json configs[1] shape: 346x260, 500 features, ~2 Mev/s (short)."""
     S = synth.make_stream(346, 260, 0.10, 2e6, seed=1002, max_corners=500)
     compare(S, 500)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("margin", [0.0, 0.5, 64.0])
+def test_stream_prefilter_margin(margin):
+    """The prefilter is an index, not a filter: results must not depend on how
+    far a rect may drift before its candidate row is rebuilt.  0 rebuilds after
+    nearly every optimisation, 64 px never does on this stream."""
+    S = synth.make_stream(240, 180, 0.15, 500e3, seed=1021, max_corners=69)
+    compare(S, 100, margin=margin)
