@@ -321,6 +321,13 @@ def main_ours(args):
         except Exception:
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        traffic = None  # DRAM bytes of one stream-kernel launch, from the committed ncu --set full capture
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_kernel_traffic.json")))[
+                "track_batch_kernel"]["dram_bytes_per_launch"]
+        except Exception:
+            pass
+        launches_step = kt_n / args.steps
         line = {
             "metric": METRIC, "value": g_opts / g_secs, "unit": "optimisations/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -338,10 +345,16 @@ def main_ours(args):
             "e2e": {"value": ge_opts / ge_secs, "unit": "optimisations/s",
                     "h2d_bytes_per_step": int(n_events * 16 + nF * w * h + 8 * sum(len(c) * 2 for c in S.corners)),
                     "d2h_bytes_per_step": int(opts_step * OPT_RECORD.itemsize + 2 * nF * feat * 216)},
-            "gpu_launches": int(kt_n + kg_n + kn_n),
-            "roofline": {"bound": "fp64", "kernel": "track_batch_kernel", "achieved": achieved,
+            # every push launches prefilter_kernel + track_batch_kernel
+            "gpu_launches": int(2 * kt_n + kg_n + kn_n),
+            "roofline": {"bound": "fp64", "kernel": "track_batch_kernel (timed with its prefilter_kernel, 1.4 % of it)",
+                         "achieved": achieved,
                          "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
-                         "traffic": None, "peak_source": "measured in this run: dependent-chain DFMA microbenchmark "
+                         "traffic": traffic, "traffic_unit": "DRAM bytes per launch (ncu --set full, profiles/r1_ncu_metrics.json)",
+                         "launches_per_step": launches_step,
+                         "algorithmic_flops_per_launch": flops_step / launches_step if launches_step else None,
+                         "kernel_ms_per_launch": kt_s * 1e3 / launches_step if launches_step else None,
+                         "peak_source": "measured in this run: dependent-chain DFMA microbenchmark "
                          "(ebt_measure_fma_peak); FP32 non-tensor peak measured %.1f TFLOP/s" % fp32_peak,
                          "algorithmic_flops_per_step": flops_step, "kernel_ms_per_step": kt_s * 1e3,
                          "kernel_share_of_step": kt_s / (secs / args.steps)},

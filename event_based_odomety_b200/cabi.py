@@ -64,6 +64,7 @@ EXPORTS = {
     "ebt_timing_get": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "ebt_timing_reset": (C.c_int, [_vp]),
     "ebt_set_prefilter_margin": (C.c_int, [_vp, C.c_double]),
+    "ebt_debug_phase_clocks": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
     "ebt_sizeof_event": (C.c_size_t, []),
     "ebt_sizeof_track": (C.c_size_t, []),
     "ebt_sizeof_opt_record": (C.c_size_t, []),
@@ -257,6 +258,11 @@ class Tracker:
 
     def sync(self):
         self._ck(self.lib.ebt_sync(self.ctx))
+
+    def phase_clocks(self):
+        out = (C.c_uint64 * 8)()
+        self._ck(self.lib.ebt_debug_phase_clocks(self.ctx, out))
+        return [int(v) for v in out]
 
     def set_prefilter_margin(self, pixels):
         self._ck(self.lib.ebt_set_prefilter_margin(self.ctx, float(pixels)))

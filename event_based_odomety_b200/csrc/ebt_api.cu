@@ -516,6 +516,16 @@ size_t ebt_sizeof_solution(void) { return sizeof(ebt_solution); }
 size_t ebt_sizeof_params(void) { return sizeof(ebt_params); }
 int ebt_abi_version(void) { return 1; }
 
+int ebt_debug_phase_clocks(ebt_ctx* ctx, uint64_t* out8)
+{
+	if (!ctx || !out8) return fail(ctx, EBT_E_INVALID, "ebt_debug_phase_clocks: bad argument");
+	CU(cudaSetDevice(ctx->device));
+	unsigned long long v[8];
+	CU(ebt_launch_phase_clocks(v, ctx->stream));
+	for (int i = 0; i < 8; ++i) out8[i] = v[i];
+	return EBT_OK;
+}
+
 int ebt_set_prefilter_margin(ebt_ctx* ctx, double pixels)
 {
 	if (!ctx || !(pixels >= 0.0) || pixels > 4096.0)

@@ -7,8 +7,11 @@
 #include "../../include/ebt_types.h"
 
 #define EBT_MAX_FRAMES 64   // live template frames (FeatureDetector::optimizers_)
-#define EBT_RING 512        // per-feature window ring capacity (>= 300 + one chunk)
+#ifndef EBT_THREADS
 #define EBT_THREADS 128     // threads per feature CTA
+#endif
+// per-feature window ring capacity: a power of two >= 300 + one chunk of EBT_THREADS
+#define EBT_RING (EBT_THREADS <= 128 ? 512 : 1024)
 
 // Device mirror of the scalars of tracker::Patch
 // (/root/reference/implementation/feature_tracker/include/feature_tracker/patch.h:98-130).

@@ -36,6 +36,20 @@
 #define EBT_MIN_CTAS 4  // resident CTAs per SM the register budget is tuned for
 #endif
 
+// Phase clocks of the leader warp (build with -DEBT_PHASE_CLOCKS; read through
+// ebt_launch_phase_clocks): 0 request+handshake, 1 pixel pass, 2 wait for the
+// workers' partials, 3 totals+finalisation, 4 rest of the LM iteration,
+// 5 evaluations counted.
+__device__ unsigned long long g_phase_clocks[8];
+#ifdef EBT_PHASE_CLOCKS
+#define PHASE_T(v) const long long v = clock64()
+#define PHASE_ADD(k, a, b) \
+	if (threadIdx.x == 0) atomicAdd(&g_phase_clocks[k], (unsigned long long)((b) - (a)))
+#else
+#define PHASE_T(v)
+#define PHASE_ADD(k, a, b)
+#endif
+
 namespace
 {
 constexpr int kPixUnroll = EBT_PIX_UNROLL;
@@ -64,6 +78,8 @@ struct __align__(16) FeatShared
 	int req_kind;              // 0 stop, 1 cost-only evaluation, 2 Jacobian evaluation
 	int res_i[5];              // n_successful, n_unsuccessful, termination, n_jac, n_cost
 	EvalCtx ctx;               // written by thread 0 before the solve
+	double tot[20];            // CTA totals of one evaluation (leader warp)
+	long long t_last;          // EBT_PHASE_CLOCKS only
 };
 
 
@@ -182,6 +198,54 @@ __device__ __forceinline__ void cr_weights(double t, double (&w)[4], double (&d)
 // u = gx cos(phi) + gy sin(phi).  Jacobian columns: SE2 local (upsilon_x,
 // upsilon_y, theta) through Dx_this_mul_exp_x_at_0 (sophus/se2.hpp:123-142)
 // and phi.
+// 4x4 neighbourhood of (row, col): INTERIOR = all 16 taps inside the image, so
+// the clamp-to-edge index arithmetic (cubic_interpolation.h:403-421) is skipped
+// and the taps are addressed from one base pointer.
+template <bool JAC, bool INTERIOR>
+__device__ __forceinline__ void sample_taps(const double2* __restrict__ grid, int W, int H, int row,
+											int col, const double (&wr)[4], const double (&dr)[4],
+											const double (&wc)[4], const double (&dc)[4], double& g0,
+											double& g1, double& gr0, double& gr1, double& gc0,
+											double& gc1)
+{
+	int ci[4];
+	const double2* base = grid + ((size_t)(row - 1) * W + (col - 1));
+	if (!INTERIOR)
+	{
+#pragma unroll
+		for (int j = 0; j < 4; ++j) ci[j] = min(max(col - 1 + j, 0), W - 1);
+	}
+	g0 = g1 = gr0 = gr1 = gc0 = gc1 = 0;
+#pragma unroll
+	for (int r = 0; r < 4; ++r)
+	{
+		const double2* rowp =
+			INTERIOR ? base + (size_t)r * W : grid + (size_t)min(max(row - 1 + r, 0), H - 1) * W;
+		double f0 = 0, f1 = 0, d0 = 0, d1 = 0;
+#pragma unroll
+		for (int j = 0; j < 4; ++j)
+		{
+			const double2 p = __ldg(rowp + (INTERIOR ? j : ci[j]));
+			f0 += wc[j] * p.x;
+			f1 += wc[j] * p.y;
+			if (JAC)
+			{
+				d0 += dc[j] * p.x;
+				d1 += dc[j] * p.y;
+			}
+		}
+		g0 += wr[r] * f0;
+		g1 += wr[r] * f1;
+		if (JAC)
+		{
+			gr0 += dr[r] * f0;
+			gr1 += dr[r] * f1;
+			gc0 += wr[r] * d0;
+			gc1 += wr[r] * d1;
+		}
+	}
+}
+
 template <bool JAC>
 __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, int W, int H,
 											 const double (&x)[5], double vx, double vy,
@@ -204,38 +268,11 @@ __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, in
 		double wr[4], dr[4], wc[4], dc[4];
 		cr_weights<JAC>(wy - fr, wr, dr);
 		cr_weights<JAC>(wx - fc, wc, dc);
-		int ci[4];
-#pragma unroll
-		for (int j = 0; j < 4; ++j) ci[j] = min(max(col - 1 + j, 0), W - 1);
-		double g0 = 0, g1 = 0, gr0 = 0, gr1 = 0, gc0 = 0, gc1 = 0;
-#pragma unroll
-		for (int r = 0; r < 4; ++r)
-		{
-			const int ri = min(max(row - 1 + r, 0), H - 1);
-			const double2* rowp = grid + (size_t)ri * W;
-			double f0 = 0, f1 = 0, d0 = 0, d1 = 0;
-#pragma unroll
-			for (int j = 0; j < 4; ++j)
-			{
-				const double2 p = __ldg(rowp + ci[j]);
-				f0 += wc[j] * p.x;
-				f1 += wc[j] * p.y;
-				if (JAC)
-				{
-					d0 += dc[j] * p.x;
-					d1 += dc[j] * p.y;
-				}
-			}
-			g0 += wr[r] * f0;
-			g1 += wr[r] * f1;
-			if (JAC)
-			{
-				gr0 += dr[r] * f0;
-				gr1 += dr[r] * f1;
-				gc0 += wr[r] * d0;
-				gc1 += wr[r] * d1;
-			}
-		}
+		double g0, g1, gr0, gr1, gc0, gc1;
+		if (row >= 1 && row + 2 < H && col >= 1 && col + 2 < W)
+			sample_taps<JAC, true>(grid, W, H, row, col, wr, dr, wc, dc, g0, g1, gr0, gr1, gc0, gc1);
+		else
+			sample_taps<JAC, false>(grid, W, H, row, col, wr, dr, wc, dc, g0, g1, gr0, gr1, gc0, gc1);
 		const double u = g0 * vx + g1 * vy;
 		const double mi = m[i];
 		acc[0] += u * u;
@@ -330,6 +367,42 @@ __device__ __forceinline__ double sqrt_fast(double x)
 	return fma(fma(-s, s, x), 0.5 * y, s);
 }
 
+// sin and cos for the leader's chain: Cody-Waite reduction by pi/2 (three FMA
+// terms, exact products) and the fdlibm kernel polynomials on [-pi/4, pi/4];
+// < 1.5 ulp, no slow-path call for |x| < 1e6 (angles here are a few radians).
+__device__ __forceinline__ void sincos_fast(double x, double* sn, double* cs)
+{
+	if (!(fabs(x) < 1e6))
+	{
+		sincos(x, sn, cs);
+		return;
+	}
+	const double q = rint(x * 0.6366197723675814);
+	double r = fma(-q, 1.5707963267948966, x);
+	r = fma(-q, 6.123233995736766e-17, r);
+	r = fma(-q, -1.4973849048591698e-33, r);
+	const int n = (int)q;
+	const double z = r * r;
+	double ps = 1.58969099521155010221e-10;
+	ps = fma(ps, z, -2.50507602534068634195e-08);
+	ps = fma(ps, z, 2.75573137070700676789e-06);
+	ps = fma(ps, z, -1.98412698298579493134e-04);
+	ps = fma(ps, z, 8.33333333332248946124e-03);
+	ps = fma(ps, z, -1.66666666666666324348e-01);
+	double pc = -1.13596475577881948265e-11;
+	pc = fma(pc, z, 2.08757232129817482790e-09);
+	pc = fma(pc, z, -2.75573143513906633035e-07);
+	pc = fma(pc, z, 2.48015872894767294178e-05);
+	pc = fma(pc, z, -1.38888888888741095749e-03);
+	pc = fma(pc, z, 4.16666666666666019037e-02);
+	const double s0 = fma(r * z, ps, r);
+	const double c0 = fma(z * z, pc, fma(-0.5, z, 1.0));
+	const double sv = (n & 1) ? c0 : s0;
+	const double cv = (n & 1) ? s0 : c0;
+	*sn = (n & 2) ? -sv : sv;
+	*cs = ((n + 1) & 2) ? -cv : cv;
+}
+
 __device__ __forceinline__ void post_request(FeatShared& sh, int kind, const double (&x)[5], double vx,
 											 double vy)
 {
@@ -383,6 +456,19 @@ __device__ void lm_worker(FeatShared& sh)
 	}
 }
 
+// CTA total of reduced value k: pairwise over the per-warp partials
+__device__ __forceinline__ double red_total(const FeatShared& sh, int k)
+{
+	double v[NW];
+#pragma unroll
+	for (int w = 0; w < NW; ++w) v[w] = sh.red[w][k];
+#pragma unroll
+	for (int n = NW; n > 1; n >>= 1)
+#pragma unroll
+		for (int w = 0; w < n / 2; ++w) v[w] = v[2 * w] + v[2 * w + 1];
+	return v[0];
+}
+
 // Leader side of one evaluation at `x`.  kind 2: cost, H = J^T J (upper 4x4) and
 // g = J^T r of the Huber-corrected 625-block; kind 1: cost only.
 //   r_i = u_i/sqrt(N) + m_i, N = 1e-5 + sum u^2   (optimizer_cost.h:29-45)
@@ -395,14 +481,36 @@ __device__ void lm_worker(FeatShared& sh)
 __device__ __forceinline__ bool leader_eval(FeatShared& sh, int kind, const double (&x)[5],
 											double& cost, double (&Hm)[10], double (&g)[4])
 {
+	PHASE_T(t0);
 	double vy, vx;
-	sincos(x[4], &vy, &vx);
+	sincos_fast(x[4], &vy, &vx);
 	post_request(sh, kind, x, vx, vy);
+	PHASE_T(t1);
 	pixel_service(sh);
+	PHASE_T(t2);
 	partials_wait();
+	PHASE_T(t3);
+	PHASE_ADD(0, t0, t1);
+	PHASE_ADD(1, t1, t2);
+	PHASE_ADD(2, t2, t3);
+#ifdef EBT_PHASE_CLOCKS
+	if (threadIdx.x == 0)
+	{
+		atomicAdd(&g_phase_clocks[5], 1ull);
+		if (sh.t_last) atomicAdd(&g_phase_clocks[4], (unsigned long long)(t0 - sh.t_last));
+	}
+#endif
 	const EvalCtx& E = sh.ctx;
-	const double suu = (sh.red[0][0] + sh.red[1][0]) + (sh.red[2][0] + sh.red[3][0]);
-	const double c = (sh.red[0][1] + sh.red[1][1]) + (sh.red[2][1] + sh.red[3][1]);
+	{
+		// every leader lane that owns a reduction slot sums that slot's per-warp
+		// partials; the totals are then shared through sh.tot
+		const int lane = threadIdx.x & 31;
+		const int slot = kind == 2 ? butterfly_slot<20>(lane) : butterfly_slot<2>(lane);
+		if (slot >= 0) sh.tot[slot] = red_total(sh, slot);
+		__syncwarp();
+	}
+	const double suu = sh.tot[0];
+	const double c = sh.tot[1];
 	const double N = 1e-5 + suu;
 	const double iN = rcp_fast(N), isq = rsqrt_fast(N);
 	const double s = suu * iN + 2.0 * c * isq + E.smm;
@@ -423,8 +531,8 @@ __device__ __forceinline__ bool leader_eval(FeatShared& sh, int kind, const doub
 #pragma unroll
 		for (int q = 0; q < 4; ++q)
 		{
-			A[q] = (sh.red[0][2 + q] + sh.red[1][2 + q]) + (sh.red[2][2 + q] + sh.red[3][2 + q]);
-			B[q] = (sh.red[0][6 + q] + sh.red[1][6 + q]) + (sh.red[2][6 + q] + sh.red[3][6 + q]);
+			A[q] = sh.tot[2 + q];
+			B[q] = sh.tot[6 + q];
 		}
 		// g_q = rho' [ A_q/N (1 - suu/N - c/sqrt(N)) + B_q/sqrt(N) ]
 		const double k1 = rho1 * iN * (1.0 - suu * iN - c * isq);
@@ -444,12 +552,19 @@ __device__ __forceinline__ bool leader_eval(FeatShared& sh, int kind, const doub
 #pragma unroll
 			for (int p = q; p < 4; ++p, ++k)
 			{
-				const double G = (sh.red[0][10 + k] + sh.red[1][10 + k]) + (sh.red[2][10 + k] + sh.red[3][10 + k]);
+				const double G = sh.tot[10 + k];
 				Hm[k] = G * kg - A[q] * A[p] * k2;
 				chk += Hm[k];
 			}
 		ok = ok && isfinite(chk);  // any non-finite term poisons the sum
 	}
+#ifdef EBT_PHASE_CLOCKS
+	{
+		const long long t4 = clock64();
+		PHASE_ADD(3, t3, t4);
+		if (threadIdx.x == 0) sh.t_last = t4;
+	}
+#endif
 	return ok;
 }
 
@@ -470,7 +585,7 @@ __device__ __forceinline__ void plus5(const double (&x)[5], const double (&d)[4]
 {
 	const double theta = d[2];
 	double es, ec;
-	sincos(theta, &es, &ec);
+	sincos_fast(theta, &es, &ec);
 	{
 		const double il = inv_len(ec * ec + es * es);
 		ec *= il;
@@ -654,6 +769,9 @@ __device__ void lm_solve(FeatShared& sh, const DevParams& P, double (&params)[5]
 	bool failed = false;
 #pragma unroll
 	for (int k = 0; k < 5; ++k) x[k] = best[k] = params[k];
+#ifdef EBT_PHASE_CLOCKS
+	if (threadIdx.x == 0) sh.t_last = 0;
+#endif
 	S.n_successful = S.n_unsuccessful = S.termination = 0;
 	S.n_jac = 1;
 	S.n_cost = 0;
@@ -1622,4 +1740,14 @@ cudaError_t ebt_launch_grad(const unsigned char* gray, const double* lut, int W,
 	const dim3 grd((W + blk.x - 1) / blk.x, (H + blk.y - 1) / blk.y);
 	grad_kernel<<<grd, blk, 0, stream>>>(gray, lut, W, H, grid);
 	return cudaGetLastError();
+}
+
+cudaError_t ebt_launch_phase_clocks(unsigned long long* out8, cudaStream_t stream)
+{
+	cudaError_t e = cudaStreamSynchronize(stream);
+	if (e != cudaSuccess) return e;
+	e = cudaMemcpyFromSymbol(out8, g_phase_clocks, sizeof(unsigned long long) * 8);
+	if (e != cudaSuccess) return e;
+	unsigned long long zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+	return cudaMemcpyToSymbol(g_phase_clocks, zero, sizeof(zero));
 }

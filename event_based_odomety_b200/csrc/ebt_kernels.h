@@ -26,3 +26,5 @@ cudaError_t ebt_launch_grad(const unsigned char* gray, const double* lut, int W,
 							double2* grid, cudaStream_t stream);
 cudaError_t ebt_launch_fma_peak(int fp64, void* out, int blocks, int threads, int iters,
 								cudaStream_t stream);
+// leader-warp phase clocks (all zero unless built with -DEBT_PHASE_CLOCKS); resets them
+cudaError_t ebt_launch_phase_clocks(unsigned long long* out8, cudaStream_t stream);

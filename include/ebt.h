@@ -148,6 +148,14 @@ int ebt_timing_enable(ebt_ctx* ctx, int on);
 int ebt_timing_get(ebt_ctx* ctx, int kernel, double* ms_total, int64_t* launches);
 int ebt_timing_reset(ebt_ctx* ctx);
 
+/* Profiling aid: cycle counters of the solver's leader warp, summed over all
+ * solves since the last call (reset on read).  out8[0..4] = cycles spent in
+ * request hand-off, the pixel pass, waiting for the other warps' partial sums,
+ * totals + finalisation, and the rest of a trust-region iteration; out8[5] =
+ * evaluations counted.  All zero unless the library was built with
+ * -DEBT_PHASE_CLOCKS (the shipped build is not). */
+int ebt_debug_phase_clocks(ebt_ctx* ctx, uint64_t* out8);
+
 /* Tuning knob of ebt_push_events (not part of the reference's API).  Before the
  * stream kernel runs, a prefilter marks, per feature, the events whose pixel
  * lies within `pixels` of the feature's patch rect as it stands at the push;

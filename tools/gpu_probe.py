@@ -31,3 +31,7 @@ ns, nu = sol["n_successful"].astype(float), sol["n_unsuccessful"].astype(float)
 flops = 625.0 * (400 * (1 + ns) + 230 * (ns + nu))  # SURVEY 8d (reference's evaluation count)
 print(f"problems/launch {len(prob)}  avg ms/launch {ms/nl:.3f}  -> {len(prob)/(ms/nl)*1e3:.0f} opt/s")
 print(f"mean full evals {njac.mean():.2f} cost-only evals {ncost.mean():.2f}; algorithmic TFLOP/s {flops.sum()/(ms/nl*1e-3)/1e12:.3f}")
+pc = tr.phase_clocks()
+if pc[5]:
+    names = ["request", "pixel pass", "wait partials", "totals+final", "LM rest"]
+    print("leader phase clocks per evaluation: " + ", ".join(f"{n} {pc[i]/pc[5]:.0f}" for i, n in enumerate(names)))
