@@ -105,6 +105,12 @@ struct ebt_ctx
 
 	bool timing = false;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	// timing: event pairs are recorded without a host sync and resolved when the
+	// totals are read (every launch is already followed by a stream sync of its own)
+	struct Span { cudaEvent_t a, b; int k; };
+	std::vector<Span> spans;
+	std::vector<cudaEvent_t> event_pool;
+	cudaEvent_t span_begin = nullptr;
 	double ms[K_COUNT] = {0, 0, 0, 0};
 	int64_t launches[K_COUNT] = {0, 0, 0, 0};
 };
@@ -138,19 +144,45 @@ FrameTable frameTable(const ebt_ctx* c)
 	return ft;
 }
 
+cudaEvent_t takeEvent(ebt_ctx* c)
+{
+	if (!c->event_pool.empty())
+	{
+		cudaEvent_t e = c->event_pool.back();
+		c->event_pool.pop_back();
+		return e;
+	}
+	cudaEvent_t e = nullptr;
+	cudaEventCreate(&e);
+	return e;
+}
+void resolveSpans(ebt_ctx* c)
+{
+	for (const auto& s : c->spans)
+	{
+		float ms = 0;
+		if (cudaEventSynchronize(s.b) == cudaSuccess && cudaEventElapsedTime(&ms, s.a, s.b) == cudaSuccess)
+			c->ms[s.k] += ms;
+		c->event_pool.push_back(s.a);
+		c->event_pool.push_back(s.b);
+	}
+	c->spans.clear();
+}
 void tic(ebt_ctx* c)
 {
-	if (c->timing) cudaEventRecord(c->ev0, c->stream);
+	if (!c->timing) return;
+	c->span_begin = takeEvent(c);
+	cudaEventRecord(c->span_begin, c->stream);
 }
 void toc(ebt_ctx* c, int k)
 {
 	c->launches[k]++;
-	if (!c->timing) return;
-	cudaEventRecord(c->ev1, c->stream);
-	cudaEventSynchronize(c->ev1);
-	float ms = 0;
-	cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-	c->ms[k] += ms;
+	if (!c->timing || !c->span_begin) return;
+	cudaEvent_t e = takeEvent(c);
+	cudaEventRecord(e, c->stream);
+	c->spans.push_back({c->span_begin, e, k});
+	c->span_begin = nullptr;
+	if (c->spans.size() >= 4096) resolveSpans(c);
 }
 
 void cornerOf(const DevPatch& p, double& x, double& y)
@@ -312,6 +344,8 @@ int ebt_destroy(ebt_ctx* ctx)
 	cudaFreeHost(ctx->h_stage);
 	cudaFreeHost(ctx->rec_stage);
 	cudaFreeHost(ctx->nrec_stage);
+	resolveSpans(ctx);
+	for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
 	if (ctx->ev0) cudaEventDestroy(ctx->ev0);
 	if (ctx->ev1) cudaEventDestroy(ctx->ev1);
 	if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -493,6 +527,7 @@ int ebt_timing_enable(ebt_ctx* ctx, int on)
 int ebt_timing_reset(ebt_ctx* ctx)
 {
 	if (!ctx) return EBT_E_INVALID;
+	resolveSpans(ctx);
 	for (int k = 0; k < K_COUNT; ++k)
 	{
 		ctx->ms[k] = 0;
@@ -503,6 +538,7 @@ int ebt_timing_reset(ebt_ctx* ctx)
 int ebt_timing_get(ebt_ctx* ctx, int kernel, double* ms_total, int64_t* launches)
 {
 	if (!ctx || kernel < 0 || kernel >= K_COUNT) return EBT_E_INVALID;
+	resolveSpans(ctx);
 	if (ms_total) *ms_total = ctx->ms[kernel];
 	if (launches) *launches = ctx->launches[kernel];
 	return EBT_OK;

@@ -20,8 +20,8 @@ def _angle_diff_deg(a, b):
     return np.rad2deg(np.minimum(d, 2 * np.pi - d))
 
 
-def run_case(n, w, h, seed, n_frames=1):
-    ps = synth.make_problems(n, w, h, seed=seed, n_frames=n_frames)
+def run_case(n, w, h, seed, n_frames=1, **kw):
+    ps = synth.make_problems(n, w, h, seed=seed, n_frames=n_frames, **kw)
     ob = CpuBatch(load_oracle(), w, h)
     tr = Tracker(w, h)
     for f in ps.frames:
@@ -75,3 +75,22 @@ def test_batch_edge_windows():
     assert osol["termination"][0] == 2 and gsol["termination"][0] == 2
     assert gsol["final_cost"][0] == osol["final_cost"][0] == -1.0
     assert np.allclose(osol["x"], gsol["x"], atol=POS_TOL_PX) and np.allclose(osol["y"], gsol["y"], atol=POS_TOL_PX)
+
+
+@pytest.mark.gpu
+def test_batch_border_patches():
+    """Patches hanging over the image border: pixels that warp outside the image
+    contribute u = 0 without derivative (optimizer_cost.h:47-90) and the bicubic
+    taps clamp to the edge (cubic_interpolation.h:403-421)."""
+    ps, osol, onab, gsol, gnab = run_case(256, 240, 180, 3111, 1, border=2)
+    assert np.array_equal(onab.astype(np.int32), gnab)
+    dpos = np.hypot(osol["x"] - gsol["x"], osol["y"] - gsol["y"])
+    same_path = ((osol["n_successful"] == gsol["n_successful"])
+                 & (osol["n_unsuccessful"] == gsol["n_unsuccessful"])
+                 & (osol["termination"] == gsol["termination"]))
+    print(f"\n[border] max dpos {np.nanmax(dpos):.3e} px, same LM path {same_path.mean():.4f}")
+    ok = np.isfinite(osol["x"])
+    assert np.array_equal(ok, np.isfinite(gsol["x"]))
+    assert dpos[ok].max() <= POS_TOL_PX
+    assert _angle_diff_deg(osol["flow_dir"][ok], gsol["flow_dir"][ok]).max() <= ANGLE_TOL_DEG
+    assert same_path.mean() >= 0.99

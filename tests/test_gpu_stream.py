@@ -67,7 +67,8 @@ def compare(stream, max_patches, n_frames=None, split=None, margin=None):
                   "current_ts", "time_last_update", "init_time"):
             assert np.array_equal(tc[k], tg[k]), k
         assert np.array_equal(tc["counter"], tg["counter"])
-        assert np.abs(tc["rect_x"] - tg["rect_x"]).max() <= POS_TOL_PX
+        if len(tc):
+            assert np.abs(tc["rect_x"] - tg["rect_x"]).max() <= POS_TOL_PX
         for tid in tc["track_id"]:
             assert np.array_equal(cpu.patch(tid), gpu.patch(tid)), f"integer patch of track {tid}"
             a, b = cpu.trajectory(tid), gpu.trajectory(tid)
@@ -105,3 +106,41 @@ def test_stream_prefilter_margin(margin):
     nearly every optimisation, 64 px never does on this stream."""
     S = synth.make_stream(240, 180, 0.15, 500e3, seed=1021, max_corners=69)
     compare(S, 100, margin=margin)
+
+
+@pytest.mark.gpu
+def test_stream_c3_shape():
+    """BASELINE.json configs[2] shape: 640x480, 2000 features, ~10 Mev/s (two
+    frame intervals; the CPU oracle needs about a minute for them)."""
+    S = synth.make_stream(640, 480, 0.09, 10e6, seed=1003, max_corners=2000)
+    compare(S, 2000, n_frames=2)
+
+
+@pytest.mark.gpu
+def test_stream_empty_and_tiny_pushes():
+    """Zero-length pushes, single-event pushes and a push before any frame."""
+    S = synth.make_stream(240, 180, 0.10, 500e3, seed=1031, max_corners=40)
+    gpu = Tracker(S.width, S.height, 100)
+    assert gpu.push_events(S.events[:1000]) == 0  # no patches yet: events are consumed, nothing happens
+    assert len(gpu.tracks()) == 0
+    gpu.reset()
+    cpu = CpuTracker(load_oracle(), S.width, S.height, 100)
+
+    class Ragged:
+        def __getattr__(self, k):
+            return getattr(gpu, k)
+
+        def push_events(self, ev):
+            n = gpu.push_events(ev[:0])
+            cuts = [0, 1, 2, 3, 130, 131, len(ev) // 2, len(ev)]
+            for a, b in zip(cuts, cuts[1:]):
+                n += gpu.push_events(ev[a:b])
+            return n + gpu.push_events(ev[:0])
+    n_cpu = synth.run_stream(cpu, S)
+    n_gpu = synth.run_stream(Ragged(), S)
+    assert n_cpu == n_gpu > 0
+    rc, rg = cpu.records(), gpu.records()
+    assert np.array_equal(rc["track_id"], rg["track_id"]) and np.array_equal(rc["event_index"], rg["event_index"])
+    assert np.hypot(rc["x"] - rg["x"], rc["y"] - rg["y"]).max() <= POS_TOL_PX
+    cpu.close()
+    gpu.close()
