@@ -89,8 +89,11 @@ def run_step(tr, S, flows, frame_fn, push_fn, n_frames):
         ids, xy = tr.get_uninit()
         if len(ids):
             found, nxt = flows.get(k, ids, xy)
-            for i in range(len(ids)):
-                tr.set_flow(ids[i], found[i], nxt[i, 0], nxt[i, 1])
+            if hasattr(tr, "set_flows"):
+                tr.set_flows(ids, found, nxt)
+            else:
+                for i in range(len(ids)):
+                    tr.set_flow(ids[i], found[i], nxt[i, 0], nxt[i, 1])
         tr.new_frame_end()
         total += push_fn(k)
     return total

@@ -45,6 +45,7 @@ EXPORTS = {
     "ebt_measure_fma_peak": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "ebt_get_uninit": (C.c_int, [_vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]),
     "ebt_set_flow": (C.c_int, [_vp, C.c_int32, C.c_int, C.c_float, C.c_float]),
+    "ebt_set_flows": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int]),
     "ebt_new_frame_end": (C.c_int, [_vp]),
     "ebt_push_events": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
     "ebt_push_events_device": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
@@ -165,6 +166,14 @@ class Tracker:
 
     def set_flow(self, track_id, found, nx, ny):
         self._ck(self.lib.ebt_set_flow(self.ctx, int(track_id), int(found), float(nx), float(ny)))
+
+    def set_flows(self, track_ids, found, next_xy):
+        ids = np.ascontiguousarray(track_ids, np.int32)
+        fnd = np.ascontiguousarray(found, np.int32)
+        nxt = np.ascontiguousarray(next_xy, np.float32).reshape(-1, 2)
+        assert len(ids) == len(fnd) == len(nxt)
+        self._ck(self.lib.ebt_set_flows(self.ctx, ids.ctypes.data_as(_vp), fnd.ctypes.data_as(_vp),
+                                        nxt.ctypes.data_as(_vp), len(ids)))
 
     def new_frame_end(self):
         self._ck(self.lib.ebt_new_frame_end(self.ctx))

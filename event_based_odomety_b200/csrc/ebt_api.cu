@@ -613,6 +613,9 @@ static int newFrameBegin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us, const
 		for (int j = 0; j < n_corners; ++j)
 		{
 			const double dx = cx - cornersXY[2 * j], dy = cy - cornersXY[2 * j + 1];
+			// |dx| or |dy| >= d implies the norm is >= d: skip the sqrt, same decision
+			if (!(std::fabs(dx) < ctx->prm.association_distance) || !(std::fabs(dy) < ctx->prm.association_distance))
+				continue;
 			if (newIds[j] == -1 && std::sqrt(dx * dx + dy * dy) < ctx->prm.association_distance)
 			{
 				newIds[j] = p.track_id;
@@ -672,32 +675,57 @@ int ebt_get_uninit(ebt_ctx* ctx, int32_t* track_ids, double* cornersXY, int cap,
 }
 
 // Loop body of FlowEstimator::getFlowPatches (flow_estimator.cpp:41-79).
+static void applyFlow(ebt_ctx* ctx, DevPatch& p, int found, float next_x, float next_y)
+{
+	ctx->host_dirty = true;
+	if (!found)
+	{
+		p.lost = 1;
+		return;
+	}
+	double cx, cy;
+	cornerOf(p, cx, cy);
+	const double dx = next_x - cx, dy = next_y - cy;
+	p.warp[0] = 1.0;
+	p.warp[1] = 0.0;
+	p.warp[2] = -dx;
+	p.warp[3] = -dy;
+	p.flow = std::atan2(dy, dx);
+	p.init = 1;
+	p.time_without_update = static_cast<long long>(1e6 / std::fmax(1e-1, std::sqrt(dx * dx + dy * dy)));
+	if (cx <= 5 || cy <= 5 || cx >= ctx->prm.width - 5 || cy >= ctx->prm.height - 5) p.lost = 1;
+}
+
 int ebt_set_flow(ebt_ctx* ctx, int32_t track_id, int found, float next_x, float next_y)
 {
 	if (!ctx) return EBT_E_INVALID;
 	for (DevPatch& p : ctx->h)
 	{
 		if (p.track_id != track_id || p.init) continue;
-		ctx->host_dirty = true;
-		if (!found)
-		{
-			p.lost = 1;
-			return EBT_OK;
-		}
-		double cx, cy;
-		cornerOf(p, cx, cy);
-		const double dx = next_x - cx, dy = next_y - cy;
-		p.warp[0] = 1.0;
-		p.warp[1] = 0.0;
-		p.warp[2] = -dx;
-		p.warp[3] = -dy;
-		p.flow = std::atan2(dy, dx);
-		p.init = 1;
-		p.time_without_update = static_cast<long long>(1e6 / std::fmax(1e-1, std::sqrt(dx * dx + dy * dy)));
-		if (cx <= 5 || cy <= 5 || cx >= ctx->prm.width - 5 || cy >= ctx->prm.height - 5) p.lost = 1;
+		applyFlow(ctx, p, found, next_x, next_y);
 		return EBT_OK;
 	}
 	return fail(ctx, EBT_E_INVALID, "ebt_set_flow: no uninitialised patch with this track id");
+}
+
+// The same for n patches at once (what a caller that runs LK on all the
+// uninitialised patches of a frame has in hand): nextXY holds n (x, y) pairs.
+int ebt_set_flows(ebt_ctx* ctx, const int32_t* track_ids, const int32_t* found, const float* nextXY, int n)
+{
+	if (!ctx || n < 0 || (n > 0 && (!track_ids || !found || !nextXY)))
+		return fail(ctx, EBT_E_INVALID, "ebt_set_flows: bad argument");
+	ctx->pos_of_id.assign(static_cast<size_t>(ctx->next_track_id), -1);
+	for (size_t i = 0; i < ctx->h.size(); ++i)
+		ctx->pos_of_id[static_cast<size_t>(ctx->h[i].track_id)] = static_cast<int>(i);
+	for (int i = 0; i < n; ++i)
+	{
+		const int32_t id = track_ids[i];
+		const int pos = (id >= 0 && id < ctx->next_track_id) ? ctx->pos_of_id[static_cast<size_t>(id)] : -1;
+		if (pos < 0 || ctx->h[static_cast<size_t>(pos)].init)
+			return fail(ctx, EBT_E_INVALID, "ebt_set_flows: no uninitialised patch with this track id");
+		applyFlow(ctx, ctx->h[static_cast<size_t>(pos)], found[i], nextXY[2 * i], nextXY[2 * i + 1]);
+	}
+	return EBT_OK;
 }
 
 // FeatureDetector::newImage, second half (feature_detector.cpp:499-535).

@@ -170,20 +170,23 @@ __device__ __forceinline__ void block_sum(FeatShared& sh, double (&acc)[K])
 // Catmull-Rom weights of ceres::CubicHermiteSpline (ceres/include/ceres/
 // cubic_interpolation.h:64-90) in basis form: f = sum_k w[k] p[k],
 // df/dx = sum_k d[k] p[k].
+// The common factor 0.5 is left out here and applied once to the finished sums
+// (0.25 for a row weight times a column weight): scaling by a power of two is
+// exact, so the results are bit-identical and 10 FP64 multiplies per pixel go.
 template <bool DERIV>
 __device__ __forceinline__ void cr_weights(double t, double (&w)[4], double (&d)[4])
 {
 	const double t2 = t * t, t3 = t2 * t;
-	w[0] = 0.5 * (-t3 + 2.0 * t2 - t);
-	w[1] = 0.5 * (3.0 * t3 - 5.0 * t2 + 2.0);
-	w[2] = 0.5 * (-3.0 * t3 + 4.0 * t2 + t);
-	w[3] = 0.5 * (t3 - t2);
+	w[0] = -t3 + 2.0 * t2 - t;
+	w[1] = 3.0 * t3 - 5.0 * t2 + 2.0;
+	w[2] = -3.0 * t3 + 4.0 * t2 + t;
+	w[3] = t3 - t2;
 	if (DERIV)
 	{
-		d[0] = 0.5 * (-3.0 * t2 + 4.0 * t - 1.0);
-		d[1] = 0.5 * (9.0 * t2 - 10.0 * t);
-		d[2] = 0.5 * (-9.0 * t2 + 8.0 * t + 1.0);
-		d[3] = 0.5 * (3.0 * t2 - 2.0 * t);
+		d[0] = -3.0 * t2 + 4.0 * t - 1.0;
+		d[1] = 9.0 * t2 - 10.0 * t;
+		d[2] = -9.0 * t2 + 8.0 * t + 1.0;
+		d[3] = 3.0 * t2 - 2.0 * t;
 	}
 }
 
@@ -209,7 +212,7 @@ __device__ __forceinline__ void sample_taps(const double2* __restrict__ grid, in
 											double& gc1)
 {
 	int ci[4];
-	const double2* base = grid + ((size_t)(row - 1) * W + (col - 1));
+	const double2* base = grid + ((row - 1) * W + (col - 1));  // 32-bit index: W*H < 2^31
 	if (!INTERIOR)
 	{
 #pragma unroll
@@ -220,7 +223,7 @@ __device__ __forceinline__ void sample_taps(const double2* __restrict__ grid, in
 	for (int r = 0; r < 4; ++r)
 	{
 		const double2* rowp =
-			INTERIOR ? base + (size_t)r * W : grid + (size_t)min(max(row - 1 + r, 0), H - 1) * W;
+			INTERIOR ? base + r * W : grid + min(max(row - 1 + r, 0), H - 1) * W;
 		double f0 = 0, f1 = 0, d0 = 0, d1 = 0;
 #pragma unroll
 		for (int j = 0; j < 4; ++j)
@@ -243,6 +246,16 @@ __device__ __forceinline__ void sample_taps(const double2* __restrict__ grid, in
 			gc0 += wr[r] * d0;
 			gc1 += wr[r] * d1;
 		}
+	}
+	// the two 0.5 factors cr_weights leaves out
+	g0 *= 0.25;
+	g1 *= 0.25;
+	if (JAC)
+	{
+		gr0 *= 0.25;
+		gr1 *= 0.25;
+		gc0 *= 0.25;
+		gc1 *= 0.25;
 	}
 }
 

@@ -80,6 +80,8 @@ int ebt_new_frame_begin_device(ebt_ctx* ctx, const uint8_t* d_gray, int64_t ts_u
 							   const double* cornersXY, int n_corners);
 int ebt_get_uninit(ebt_ctx* ctx, int32_t* track_ids, double* cornersXY, int cap, int* n_out);
 int ebt_set_flow(ebt_ctx* ctx, int32_t track_id, int found, float next_x, float next_y);
+/* ebt_set_flow for n patches in one call; nextXY = n (x, y) float pairs. */
+int ebt_set_flows(ebt_ctx* ctx, const int32_t* track_ids, const int32_t* found, const float* nextXY, int n);
 int ebt_new_frame_end(ebt_ctx* ctx);
 
 /* FeatureDetector::updatePatches (feature_detector.cpp:585-619) for n events in

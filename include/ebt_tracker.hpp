@@ -158,12 +158,16 @@ class FeatureDetector
 		std::vector<int32_t> ids(static_cast<size_t>(n));
 		std::vector<double> pts(static_cast<size_t>(n) * 2);
 		if (n) check(ebt_get_uninit(ctx_, ids.data(), pts.data(), n, &n), "ebt_get_uninit");
+		std::vector<int32_t> found(static_cast<size_t>(n));
+		std::vector<float> next(static_cast<size_t>(n) * 2);
 		for (int i = 0; i < n; ++i)
 		{
 			float nx = 0, ny = 0;
-			const bool found = flow_ && flow_(Corner{pts[2 * i], pts[2 * i + 1]}, nx, ny);
-			check(ebt_set_flow(ctx_, ids[i], found ? 1 : 0, nx, ny), "ebt_set_flow");
+			found[i] = (flow_ && flow_(Corner{pts[2 * i], pts[2 * i + 1]}, nx, ny)) ? 1 : 0;
+			next[2 * i] = nx;
+			next[2 * i + 1] = ny;
 		}
+		if (n) check(ebt_set_flows(ctx_, ids.data(), found.data(), next.data(), n), "ebt_set_flows");
 		check(ebt_new_frame_end(ctx_), "ebt_new_frame_end");
 		dirty_ = true;
 	}
