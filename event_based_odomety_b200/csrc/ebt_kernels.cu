@@ -1612,7 +1612,7 @@ optimize_batch_kernel(const ebt_problem* __restrict__ problems, int n_problems,
 		s.n_successful = S.n_successful;
 		s.n_unsuccessful = S.n_unsuccessful;
 		s.termination = S.termination;
-		s.n_in_rect = S.n_jac * 100 + S.n_cost;  // evaluation counts (jac*100 + cost)
+		s.n_passes = S.n_jac * 100 + S.n_cost;
 		s.ts = st.cur_ts;
 		solutions[b] = s;
 	}

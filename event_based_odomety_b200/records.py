@@ -53,7 +53,7 @@ SOLUTION = np.dtype(
         ("warp", "<f8", (4,)), ("flow_dir", "<f8"), ("final_cost", "<f8"),
         ("x", "<f8"), ("y", "<f8"),
         ("n_successful", "<i4"), ("n_unsuccessful", "<i4"), ("termination", "<i4"),
-        ("n_in_rect", "<i4"), ("ts", "<i8"),
+        ("n_passes", "<i4"), ("ts", "<i8"),
     ],
     align=True,
 )

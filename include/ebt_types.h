@@ -94,7 +94,7 @@ typedef struct ebt_solution
 	int32_t n_successful;
 	int32_t n_unsuccessful;
 	int32_t termination;
-	int32_t n_in_rect;      /* events that landed inside the rect */
+	int32_t n_passes;       /* pixel passes of the solve: 100 * (cost+Jacobian passes) + cost-only passes; -1 = not reported (CPU checkers) */
 	int64_t ts;             /* int32((t_front+t_back)*0.5) */
 } ebt_solution;
 

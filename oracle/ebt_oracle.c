@@ -1254,7 +1254,7 @@ double oracle_optimize_batch(void* f, const ebt_problem* problems, int64_t n,
 			if (nabla) nabla[i * NPIX + k] = p->nabla[k];
 			in += (int)fabs(p->nabla[k]);
 		}
-		s->n_in_rect = -1;
+		s->n_passes = -1;
 		(void)in;
 		if (evals)
 		{

@@ -537,7 +537,7 @@ void solveRange(const RefFrames* F, const ebt_problem* problems,
 				if (nabla) nabla[i * EBT_PATCH_PIXELS + y * EBT_PATCH_SIDE + x] = v;
 				(void)inRect;
 			}
-		s.n_in_rect = -1;
+		s.n_passes = -1;
 	}
 }
 }  // namespace

@@ -25,7 +25,7 @@ for it in range(4):
     print(f"iter {it}: cumulative {ms:.3f} ms over {nl} launches")
 ms, nl = tr.timing_get(K_BATCH)
 sol = ds.cpu().numpy().view(SOLUTION)
-ev = sol["n_in_rect"]
+ev = sol["n_passes"]
 njac, ncost = ev // 100, ev % 100
 ns, nu = sol["n_successful"].astype(float), sol["n_unsuccessful"].astype(float)
 flops = 625.0 * (400 * (1 + ns) + 230 * (ns + nu))  # SURVEY 8d (reference's evaluation count)
