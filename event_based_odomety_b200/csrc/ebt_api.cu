@@ -59,9 +59,16 @@ struct ebt_ctx
 	int latest = 0;
 
 	std::vector<DevPatch> h;        // FeatureDetector::patches_ (list order)
-	std::vector<HostTrack> tracks;  // parallel to h
 	std::vector<DevPatch> arch;     // FeatureDetector::archivedPatches_
-	std::vector<HostTrack> arch_tracks;
+	// Per-track histories (Patch::trajectory_, finalCosts_), indexed by track
+	// id.  They are built lazily: pushes and frames only append to the journal
+	// (counts live in DevPatch::n_costs / n_traj); materialise() replays it in
+	// order when a history is asked for.
+	std::vector<HostTrack> all_tracks;
+	struct ImgSample { int32_t id; double x, y, ts; };
+	struct Pending { int kind; size_t a, b; };  // 0: img_samples[a,b)  1: records[a,b)
+	std::vector<ImgSample> img_samples;
+	std::vector<Pending> journal;
 	std::vector<std::vector<int>> arch_nabla;
 	std::vector<int> free_slots;
 	bool host_dirty = true;  // h holds changes the device has not seen
@@ -191,13 +198,52 @@ void cornerOf(const DevPatch& p, double& x, double& y)
 	y = p.ry + (EBT_PATCH_SIDE - 1) / 2.;
 }
 
-void addTraj(const DevPatch& p, HostTrack& t)
+// Patch::addTrajectoryPosition at image time (feature_detector.cpp:497-506)
+void addTraj(ebt_ctx* c, DevPatch& p)
 {
 	double x, y;
 	cornerOf(p, x, y);
-	t.traj.push_back(x);
-	t.traj.push_back(y);
-	t.traj.push_back(static_cast<double>(p.cur_ts));
+	c->img_samples.push_back({p.track_id, x, y, static_cast<double>(p.cur_ts)});
+	p.n_traj++;
+}
+
+void materialise(ebt_ctx* c)
+{
+	if (c->all_tracks.size() < static_cast<size_t>(c->next_track_id))
+		c->all_tracks.resize(static_cast<size_t>(c->next_track_id));
+	for (const auto& e : c->journal)
+	{
+		if (e.kind == 0)
+		{
+			for (size_t i = e.a; i < e.b; ++i)
+			{
+				const auto& sm = c->img_samples[i];
+				HostTrack& t = c->all_tracks[static_cast<size_t>(sm.id)];
+				t.traj.push_back(sm.x);
+				t.traj.push_back(sm.y);
+				t.traj.push_back(sm.ts);
+			}
+		}
+		else
+		{
+			// a feature's records are in the order it produced them, before and
+			// after sortRecords (which orders by event first)
+			for (size_t i = e.a; i < e.b; ++i)
+			{
+				const ebt_opt_record& r = c->records[i];
+				HostTrack& t = c->all_tracks[static_cast<size_t>(r.track_id)];
+				t.costs.push_back(r.final_cost);  // Patch::addFinalCost
+				if (!(r.lost & 2))                // not dropped by the cost filter (optimizer.cpp:151-156)
+				{
+					t.traj.push_back(r.x);
+					t.traj.push_back(r.y);
+					t.traj.push_back(static_cast<double>(r.ts));
+				}
+			}
+		}
+	}
+	c->journal.clear();
+	c->img_samples.clear();
 }
 
 int findFrame(const ebt_ctx* c, int64_t ts)
@@ -269,7 +315,7 @@ void sortRecords(ebt_ctx* ctx)
 	ctx->record_batches.clear();
 }
 
-void fillTrack(const DevPatch& p, const HostTrack& t, ebt_track& o)
+void fillTrack(const DevPatch& p, ebt_track& o)
 {
 	std::memset(&o, 0, sizeof(o));
 	o.track_id = p.track_id;
@@ -278,15 +324,15 @@ void fillTrack(const DevPatch& p, const HostTrack& t, ebt_track& o)
 	o.num_of_events = p.num_of_events;
 	o.counter = p.counter;
 	o.window_size = p.win_size;
-	o.n_optimizations = static_cast<int32_t>(t.costs.size());
-	o.n_trajectory = static_cast<int32_t>(t.traj.size() / 3);
+	o.n_optimizations = p.n_costs;
+	o.n_trajectory = p.n_traj;
 	o.rect_x = p.rx;
 	o.rect_y = p.ry;
 	o.init_x = p.ix;
 	o.init_y = p.iy;
 	std::memcpy(o.warp, p.warp, sizeof(o.warp));
 	o.flow_dir = p.init ? static_cast<double>(static_cast<float>(p.flow)) : 0.0;
-	o.last_cost = t.costs.empty() ? 0.0 : t.costs.back();
+	o.last_cost = p.n_costs > 0 ? p.costs[(p.n_costs - 1) & (EBT_COST_HISTORY - 1)] : 0.0;
 	o.current_ts = p.cur_ts;
 	o.time_last_update = p.time_last_update;
 	o.time_without_update = p.time_without_update;
@@ -460,9 +506,10 @@ int ebt_reset(ebt_ctx* ctx)
 	}
 	ctx->latest = 0;
 	ctx->h.clear();
-	ctx->tracks.clear();
+	ctx->all_tracks.clear();
+	ctx->img_samples.clear();
+	ctx->journal.clear();
 	ctx->arch.clear();
-	ctx->arch_tracks.clear();
 	ctx->arch_nabla.clear();
 	ctx->records.clear();
 	ctx->records_sorted = 0;
@@ -605,6 +652,7 @@ static int newFrameBegin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us, const
 	ctx->latest = slot;
 
 	std::vector<int> newIds(static_cast<size_t>(n_corners), -1);
+	const size_t first_sample = ctx->img_samples.size();
 	for (size_t i = 0; i < ctx->h.size(); ++i)
 	{
 		DevPatch& p = ctx->h[i];
@@ -623,7 +671,7 @@ static int newFrameBegin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us, const
 			}
 		}
 		p.cur_ts = ts_us;  // Patch::setTs
-		addTraj(p, ctx->tracks[i]);
+		addTraj(ctx, p);
 	}
 	for (int j = 0; j < n_corners; ++j)
 	{
@@ -643,12 +691,12 @@ static int newFrameBegin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us, const
 		p.frame_slot = slot;
 		p.store_slot = ctx->free_slots.back();
 		ctx->free_slots.pop_back();
-		HostTrack t;
-		addTraj(p, t);
+		addTraj(ctx, p);
 		ctx->h.push_back(p);
-		ctx->tracks.push_back(std::move(t));
 		f.users++;
 	}
+	if (ctx->img_samples.size() > first_sample)
+		ctx->journal.push_back({0, first_sample, ctx->img_samples.size()});
 	if (ctx->image_counter < 2) ctx->image_counter++;  // FlowEstimator::addImage
 	ctx->host_dirty = true;
 	return EBT_OK;
@@ -757,7 +805,6 @@ int ebt_new_frame_end(ebt_ctx* ctx)
 			CU(cudaMemset(ctx->d_nablas + static_cast<size_t>(ctx->h[i].store_slot) * EBT_PATCH_PIXELS, 0,
 						  EBT_PATCH_PIXELS * sizeof(int)));
 			ctx->arch.push_back(ctx->h[i]);
-			ctx->arch_tracks.push_back(std::move(ctx->tracks[i]));
 			ctx->arch_nabla.push_back(std::move(nab));
 			ctx->free_slots.push_back(ctx->h[i].store_slot);
 			ctx->frames[ctx->h[i].frame_slot].users--;
@@ -765,16 +812,11 @@ int ebt_new_frame_end(ebt_ctx* ctx)
 		}
 		else
 		{
-			if (k != i)
-			{
-				ctx->h[k] = ctx->h[i];
-				ctx->tracks[k] = std::move(ctx->tracks[i]);
-			}
+			if (k != i) ctx->h[k] = ctx->h[i];
 			++k;
 		}
 	}
 	ctx->h.resize(k);
-	ctx->tracks.resize(k);
 	if (moved) ctx->host_dirty = true;
 	// erase unused optimizers (feature_detector.cpp:525-535)
 	for (auto& f : ctx->frames)
@@ -847,25 +889,13 @@ static int runStream(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t
 						   ctx->stream));
 		CU(cudaStreamSynchronize(ctx->stream));
 		// A feature's records sit in the buffer in the order it produced them,
-		// which is all the per-track histories need; the global reference order
-		// is restored lazily (sortRecords) when the list is asked for.
-		ctx->pos_of_id.assign(static_cast<size_t>(ctx->next_track_id), -1);
-		for (size_t i = 0; i < ctx->h.size(); ++i) ctx->pos_of_id[static_cast<size_t>(ctx->h[i].track_id)] = static_cast<int>(i);
+		// which is all the per-track histories need (built lazily, materialise());
+		// the global reference order is restored lazily too (sortRecords).
 		const ebt_opt_record* recs = ctx->rec_stage;
-		for (unsigned long long k = 0; k < got; ++k)
-		{
-			const ebt_opt_record& r = recs[k];
-			HostTrack& t = ctx->tracks[static_cast<size_t>(ctx->pos_of_id[static_cast<size_t>(r.track_id)])];
-			t.costs.push_back(r.final_cost);  // Patch::addFinalCost
-			if (!(r.lost & 2))                // not dropped by the cost filter (optimizer.cpp:151-156)
-			{
-				t.traj.push_back(r.x);
-				t.traj.push_back(r.y);
-				t.traj.push_back(static_cast<double>(r.ts));
-			}
-		}
+		const size_t first = ctx->records.size();
 		ctx->records.insert(ctx->records.end(), recs, recs + got);
 		ctx->record_batches.push_back(ctx->records.size());
+		ctx->journal.push_back({1, first, ctx->records.size()});
 	}
 	if (nrec > got)
 		return fail(ctx, EBT_E_CAPACITY,
@@ -927,27 +957,27 @@ int ebt_get_tracks(ebt_ctx* ctx, ebt_track* out, int cap, int archived, int* n_o
 {
 	if (!ctx || !n_out) return fail(ctx, EBT_E_INVALID, "ebt_get_tracks: bad argument");
 	const auto& ps = archived ? ctx->arch : ctx->h;
-	const auto& ts = archived ? ctx->arch_tracks : ctx->tracks;
-	for (size_t i = 0; i < ps.size() && static_cast<int>(i) < cap && out; ++i) fillTrack(ps[i], ts[i], out[i]);
+	for (size_t i = 0; i < ps.size() && static_cast<int>(i) < cap && out; ++i) fillTrack(ps[i], out[i]);
 	*n_out = static_cast<int>(ps.size());
 	return EBT_OK;
 }
 
 static const HostTrack* findTrack(ebt_ctx* ctx, int32_t id, const DevPatch** p, int* archIdx)
 {
+	materialise(ctx);
 	for (size_t i = 0; i < ctx->h.size(); ++i)
 		if (ctx->h[i].track_id == id)
 		{
 			*p = &ctx->h[i];
 			*archIdx = -1;
-			return &ctx->tracks[i];
+			return &ctx->all_tracks[static_cast<size_t>(id)];
 		}
 	for (size_t i = 0; i < ctx->arch.size(); ++i)
 		if (ctx->arch[i].track_id == id)
 		{
 			*p = &ctx->arch[i];
 			*archIdx = static_cast<int>(i);
-			return &ctx->arch_tracks[i];
+			return &ctx->all_tracks[static_cast<size_t>(id)];
 		}
 	return nullptr;
 }
@@ -1010,6 +1040,7 @@ int ebt_get_records(ebt_ctx* ctx, ebt_opt_record* out, int64_t cap, int64_t* n_o
 int ebt_clear_records(ebt_ctx* ctx)
 {
 	if (!ctx) return EBT_E_INVALID;
+	materialise(ctx);  // the journal refers to ranges of records
 	ctx->records.clear();
 	ctx->records_sorted = 0;
 	ctx->record_batches.clear();

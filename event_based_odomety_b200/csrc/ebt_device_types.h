@@ -30,7 +30,7 @@ struct DevPatch
 	int counter, win_tail, win_size, n_costs;
 	int frame_slot, store_slot;
 	int last_n_opt;  // optimisations in the previous push (CTA ordering estimate)
-	int pad1;
+	int n_traj;      // Patch::trajectory_.size(): image-time samples (host) + kept optimisations (device)
 };
 
 // Solver constants: the reference's OptimizerParams

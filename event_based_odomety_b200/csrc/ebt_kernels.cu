@@ -705,6 +705,7 @@ struct LmSummary
 	double final_cost;
 	int n_successful, n_unsuccessful, termination;
 	int n_jac, n_cost;
+	int filtered;  // the cost-median filter dropped this solve (optimizer.cpp:151-156)
 };
 
 __device__ __forceinline__ double norm5(const double (&a)[5])
@@ -986,6 +987,7 @@ struct FeatState
 	double flow;
 	long long cur_ts, time_last_update, time_without_update;
 	int init, lost, num_of_events, counter, tail, size, n_costs, frame_slot;
+	int n_traj;  // Patch::trajectory_.size()
 };
 
 __device__ __forceinline__ long long to_i32(double v)
@@ -1043,6 +1045,7 @@ __device__ __forceinline__ void update_rect(FeatState& st)
 __device__ EBT_NOINLINE void optimize_feature(FeatShared& sh, double* costs, FeatState& st,
 								 const FrameTable& ft, const DevParams& P, LmSummary& S)
 {
+	S.filtered = 0;
 	integrate_window(sh, st);
 	double a1[1];
 	a1[0] = 0;
@@ -1129,6 +1132,7 @@ __device__ EBT_NOINLINE void optimize_feature(FeatShared& sh, double* costs, Fea
 		if (v[2] > P.optimizer_threshold)
 		{
 			st.lost = 1;
+			S.filtered = 1;
 			return;
 		}
 	}
@@ -1141,6 +1145,7 @@ __device__ EBT_NOINLINE void optimize_feature(FeatShared& sh, double* costs, Fea
 	const double h = (SIDE - 1) / 2.;  // Patch::toCorner
 	const double dx = (st.rx + h) - (ox + h), dy = (st.ry + h) - (oy + h);
 	st.time_without_update = (long long)(1e6 / fmax(1e-1, sqrt(dx * dx + dy * dy)));
+	st.n_traj++;  // Patch::addTrajectoryPosition (optimizer.cpp:179-181)
 	st.counter = 0;
 }
 
@@ -1207,6 +1212,7 @@ __device__ __forceinline__ void load_state(FeatState& st, const DevPatch& p)
 	st.init = p.init; st.lost = p.lost; st.num_of_events = p.num_of_events;
 	st.counter = p.counter; st.tail = p.win_tail; st.size = p.win_size;
 	st.n_costs = p.n_costs; st.frame_slot = p.frame_slot;
+	st.n_traj = p.n_traj;
 }
 
 __device__ __forceinline__ void store_state(const FeatState& st, DevPatch& p)
@@ -1221,6 +1227,7 @@ __device__ __forceinline__ void store_state(const FeatState& st, DevPatch& p)
 	p.init = st.init; p.lost = st.lost; p.num_of_events = st.num_of_events;
 	p.counter = st.counter; p.win_tail = st.tail; p.win_size = st.size;
 	p.n_costs = st.n_costs;
+	p.n_traj = st.n_traj;
 }
 
 __device__ void write_record(ebt_opt_record* records, unsigned long long* n_records,
@@ -1234,7 +1241,7 @@ __device__ void write_record(ebt_opt_record* records, unsigned long long* n_reco
 	r.n_successful = S.n_successful;
 	r.n_unsuccessful = S.n_unsuccessful;
 	r.termination = S.termination;
-	r.lost = st.lost;
+	r.lost = st.lost | (S.filtered ? 2 : 0);
 	r.num_of_events = st.num_of_events;
 	r.ts = st.cur_ts;
 	r.event_index = event_index;
@@ -1588,6 +1595,7 @@ optimize_batch_kernel(const ebt_problem* __restrict__ problems, int n_problems,
 	st.counter = pr.n_events;
 	st.tail = 0;
 	st.n_costs = 0;
+	st.n_traj = 0;
 	st.frame_slot = pr.frame_slot;
 	st.rx = st.ry = 0;
 	update_rect(st);
