@@ -34,6 +34,11 @@ class Params(C.Structure):
     ]
 
 
+class FrontendParams(C.Structure):
+    _fields_ = [("quality_level", C.c_double), ("min_distance", C.c_double), ("lk_levels", C.c_int32),
+                ("lk_max_count", C.c_int32), ("lk_epsilon", C.c_double)]
+
+
 EXPORTS = {
     "ebt_default_params": (C.c_int, [C.POINTER(Params), C.c_int, C.c_int]),
     "ebt_create": (C.c_int, [C.POINTER(Params), C.c_int, C.POINTER(_vp)]),
@@ -47,6 +52,12 @@ EXPORTS = {
     "ebt_set_flow": (C.c_int, [_vp, C.c_int32, C.c_int, C.c_float, C.c_float]),
     "ebt_set_flows": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int]),
     "ebt_new_frame_end": (C.c_int, [_vp]),
+    "ebt_default_frontend_params": (C.c_int, [C.POINTER(FrontendParams)]),
+    "ebt_set_frontend_params": (C.c_int, [_vp, C.POINTER(FrontendParams)]),
+    "ebt_detect_features": (C.c_int, [_vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]),
+    "ebt_lk_flow": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, _vp, _vp]),
+    "ebt_new_image": (C.c_int, [_vp, _vp, C.c_int64]),
+    "ebt_get_features": (C.c_int, [_vp, _vp, C.c_int, C.POINTER(C.c_int)]),
     "ebt_push_events": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
     "ebt_push_events_device": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
     "ebt_get_tracks": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.POINTER(C.c_int)]),
@@ -72,6 +83,7 @@ EXPORTS = {
     "ebt_sizeof_problem": (C.c_size_t, []),
     "ebt_sizeof_solution": (C.c_size_t, []),
     "ebt_sizeof_params": (C.c_size_t, []),
+    "ebt_sizeof_frontend_params": (C.c_size_t, []),
     "ebt_abi_version": (C.c_int, []),
 }
 
@@ -102,7 +114,7 @@ def _ptr(a):
     return a.ctypes.data_as(_vp)
 
 
-K_TRACK, K_BATCH, K_GRAD, K_NUMEV = 0, 1, 2, 3
+K_TRACK, K_BATCH, K_GRAD, K_NUMEV, K_CORNERS, K_PYRAMID, K_LK = range(7)
 
 
 class Tracker:
@@ -177,6 +189,43 @@ class Tracker:
 
     def new_frame_end(self):
         self._ck(self.lib.ebt_new_frame_end(self.ctx))
+
+    # ---- per-frame re-arm on the device (corner detector, LK) -------------
+    def detect_features(self, gray, cap=8192):
+        gray = np.ascontiguousarray(gray, np.uint8)
+        assert gray.shape == (self.height, self.width)
+        xy = np.zeros((cap, 2))
+        n = C.c_int()
+        self._ck(self.lib.ebt_detect_features(self.ctx, _ptr(gray), _ptr(xy), cap, C.byref(n)))
+        return xy[:min(n.value, cap)].copy()
+
+    def lk_flow(self, prev, cur, pts):
+        prev = np.ascontiguousarray(prev, np.uint8)
+        cur = np.ascontiguousarray(cur, np.uint8)
+        assert prev.shape == cur.shape == (self.height, self.width)
+        pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 2)
+        nxt = np.zeros_like(pts)
+        st = np.zeros(len(pts), np.uint8)
+        self._ck(self.lib.ebt_lk_flow(self.ctx, _ptr(prev), _ptr(cur), _ptr(pts), len(pts), _ptr(nxt), _ptr(st)))
+        return nxt, st
+
+    def new_image(self, gray, ts):
+        gray = np.ascontiguousarray(gray, np.uint8)
+        assert gray.shape == (self.height, self.width)
+        self._ck(self.lib.ebt_new_image(self.ctx, _ptr(gray), int(ts)))
+
+    def features(self, cap=8192):
+        xy = np.zeros((cap, 2))
+        n = C.c_int()
+        self._ck(self.lib.ebt_get_features(self.ctx, _ptr(xy), cap, C.byref(n)))
+        return xy[:min(n.value, cap)].copy()
+
+    def set_frontend_params(self, **kw):
+        p = FrontendParams()
+        self.lib.ebt_default_frontend_params(C.byref(p))
+        for k, v in kw.items():
+            setattr(p, k, v)
+        self._ck(self.lib.ebt_set_frontend_params(self.ctx, C.byref(p)))
 
     # ---- events ---------------------------------------------------------
     def push_events(self, events):

@@ -17,6 +17,7 @@
 
 #include "../../include/ebt.h"
 #include "ebt_device_types.h"
+#include "ebt_frontend.h"
 #include "ebt_kernels.h"
 
 namespace
@@ -43,7 +44,40 @@ enum
 	K_BATCH = 1,
 	K_GRAD = 2,
 	K_NUMEV = 3,
-	K_COUNT = 4
+	K_CORNERS = 4,
+	K_PYRAMID = 5,
+	K_LK = 6,
+	K_COUNT = 7
+};
+
+// Device state of the per-frame re-arm kernels (ebt_frontend.cu): the image
+// pyramids of the previous and the current frame (FlowEstimator::previousImage_
+// / currentImage_), Scharr derivatives of the previous one, Harris scratch.
+struct Frontend
+{
+	bool ready = false;
+	ebt_frontend_params prm;
+	int levels = 0;
+	int w[EBT_LK_MAX_LEVELS], h[EBT_LK_MAX_LEVELS];
+	unsigned char* img[2][EBT_LK_MAX_LEVELS] = {};
+	int built[2] = {0, 0};  // pyramid levels valid beyond level 0
+	bool have[2] = {false, false};
+	int cur = 0;  // img[cur] = currentImage_, img[cur ^ 1] = previousImage_
+	short2* deriv[EBT_LK_MAX_LEVELS] = {};
+	unsigned char* scratch = nullptr;  // image of a stand-alone ebt_detect_features call
+	float* planes = nullptr;  // 3 product planes
+	float* resp = nullptr;
+	unsigned* max_key = nullptr;
+	int* n_cand = nullptr;
+	ebt_corner_candidate* cand = nullptr;
+	int cand_cap = 0;
+	ebt_corner_candidate* h_cand = nullptr;  // pinned
+	int* h_ncand = nullptr;                   // pinned
+	float* d_pts = nullptr;                   // pts | next, lk_cap points each
+	unsigned char* d_status = nullptr;
+	float* h_pts = nullptr;  // pinned, same layout
+	unsigned char* h_status = nullptr;
+	int lk_cap = 0;
 };
 }  // namespace
 
@@ -73,6 +107,7 @@ struct ebt_ctx
 	std::vector<int> free_slots;
 	bool host_dirty = true;  // h holds changes the device has not seen
 	int next_track_id = 0;
+	std::vector<double> corners;  // FeatureDetector::corners_ of the latest frame
 	int image_counter = 0;  // FlowEstimator::imageCounter_
 	int64_t event_index = 0;
 
@@ -118,8 +153,10 @@ struct ebt_ctx
 	std::vector<Span> spans;
 	std::vector<cudaEvent_t> event_pool;
 	cudaEvent_t span_begin = nullptr;
-	double ms[K_COUNT] = {0, 0, 0, 0};
-	int64_t launches[K_COUNT] = {0, 0, 0, 0};
+	double ms[K_COUNT] = {};
+	int64_t launches[K_COUNT] = {};
+
+	Frontend fe;
 };
 
 namespace
@@ -390,6 +427,27 @@ int ebt_destroy(ebt_ctx* ctx)
 	cudaFreeHost(ctx->h_stage);
 	cudaFreeHost(ctx->rec_stage);
 	cudaFreeHost(ctx->nrec_stage);
+	{
+		Frontend& fe = ctx->fe;
+		for (int l = 0; l < EBT_LK_MAX_LEVELS; ++l)
+		{
+			cudaFree(fe.img[0][l]);
+			cudaFree(fe.img[1][l]);
+			cudaFree(fe.deriv[l]);
+		}
+		cudaFree(fe.scratch);
+		cudaFree(fe.planes);
+		cudaFree(fe.resp);
+		cudaFree(fe.max_key);
+		cudaFree(fe.n_cand);
+		cudaFree(fe.cand);
+		cudaFree(fe.d_pts);
+		cudaFree(fe.d_status);
+		cudaFreeHost(fe.h_cand);
+		cudaFreeHost(fe.h_ncand);
+		cudaFreeHost(fe.h_pts);
+		cudaFreeHost(fe.h_status);
+	}
 	resolveSpans(ctx);
 	for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
 	if (ctx->ev0) cudaEventDestroy(ctx->ev0);
@@ -420,6 +478,7 @@ int ebt_create(const ebt_params* params, int device, ebt_ctx** out)
 	ebt_ctx* c = new ebt_ctx();
 	c->prm = *params;
 	c->device = device;
+	ebt_default_frontend_params(&c->fe.prm);
 	DevParams& d = c->dp;
 	d.width = params->width;
 	d.height = params->height;
@@ -520,6 +579,9 @@ int ebt_reset(ebt_ctx* ctx)
 	ctx->next_track_id = 0;
 	ctx->image_counter = 0;
 	ctx->event_index = 0;
+	ctx->corners.clear();
+	ctx->fe.have[0] = ctx->fe.have[1] = false;
+	ctx->fe.built[0] = ctx->fe.built[1] = 0;
 	CU(cudaMemsetAsync(ctx->d_nablas, 0,
 					   static_cast<size_t>(ctx->prm.max_patches) * EBT_PATCH_PIXELS * sizeof(int), ctx->stream));
 	return EBT_OK;
@@ -597,6 +659,7 @@ size_t ebt_sizeof_opt_record(void) { return sizeof(ebt_opt_record); }
 size_t ebt_sizeof_problem(void) { return sizeof(ebt_problem); }
 size_t ebt_sizeof_solution(void) { return sizeof(ebt_solution); }
 size_t ebt_sizeof_params(void) { return sizeof(ebt_params); }
+size_t ebt_sizeof_frontend_params(void) { return sizeof(ebt_frontend_params); }
 int ebt_abi_version(void) { return 1; }
 
 int ebt_debug_phase_clocks(ebt_ctx* ctx, uint64_t* out8)
@@ -651,6 +714,10 @@ static int newFrameBegin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us, const
 	f.alive = true;
 	ctx->latest = slot;
 
+	if (n_corners > 0 && cornersXY != ctx->corners.data())
+		ctx->corners.assign(cornersXY, cornersXY + 2 * static_cast<size_t>(n_corners));
+	else if (n_corners == 0)
+		ctx->corners.clear();
 	std::vector<int> newIds(static_cast<size_t>(n_corners), -1);
 	const size_t first_sample = ctx->img_samples.size();
 	for (size_t i = 0; i < ctx->h.size(); ++i)
@@ -1154,6 +1221,340 @@ int ebt_optimize_batch(ebt_ctx* ctx, const ebt_problem* problems, int64_t n_prob
 						   ctx->stream));
 	CU(cudaStreamSynchronize(ctx->stream));
 	return EBT_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Per-frame re-arm on the device: corner detector and pyramidal
+// LK, kernels in ebt_frontend.cu.
+// ---------------------------------------------------------------------------
+namespace
+{
+int ensureFrontend(ebt_ctx* ctx)
+{
+	Frontend& fe = ctx->fe;
+	if (fe.ready) return EBT_OK;
+	const int W = ctx->prm.width, H = ctx->prm.height;
+	const size_t npx = static_cast<size_t>(W) * H;
+	// buildOpticalFlowPyramid (lkpyramid.cpp): a level is added only while it
+	// stays larger than the window
+	fe.levels = 1;
+	fe.w[0] = W;
+	fe.h[0] = H;
+	for (int l = 1; l <= fe.prm.lk_levels && l < EBT_LK_MAX_LEVELS; ++l)
+	{
+		const int w = (fe.w[l - 1] + 1) / 2, h = (fe.h[l - 1] + 1) / 2;
+		if (w <= EBT_LK_WINDOW || h <= EBT_LK_WINDOW) break;
+		fe.w[l] = w;
+		fe.h[l] = h;
+		fe.levels = l + 1;
+	}
+	for (int l = 0; l < fe.levels; ++l)
+	{
+		const size_t n = static_cast<size_t>(fe.w[l]) * fe.h[l];
+		CU(cudaMalloc(&fe.img[0][l], n));
+		CU(cudaMalloc(&fe.img[1][l], n));
+		CU(cudaMalloc(&fe.deriv[l], n * sizeof(short2)));
+	}
+	CU(cudaMalloc(&fe.scratch, npx));
+	CU(cudaMalloc(&fe.planes, 3 * npx * sizeof(float)));
+	CU(cudaMalloc(&fe.resp, npx * sizeof(float)));
+	CU(cudaMalloc(&fe.max_key, sizeof(unsigned)));
+	CU(cudaMalloc(&fe.n_cand, sizeof(int)));
+	// a 3x3 local maximum excludes its 8 neighbours unless they tie: npx/2 bounds
+	// any checkerboard of ties, npx/4 + slack covers images that are not adversarial
+	fe.cand_cap = static_cast<int>(npx / 4 + 1024);
+	CU(cudaMalloc(&fe.cand, static_cast<size_t>(fe.cand_cap) * sizeof(ebt_corner_candidate)));
+	CU(cudaHostAlloc(&fe.h_cand, static_cast<size_t>(fe.cand_cap) * sizeof(ebt_corner_candidate),
+					 cudaHostAllocDefault));
+	CU(cudaHostAlloc(&fe.h_ncand, sizeof(int), cudaHostAllocDefault));
+	fe.ready = true;
+	return EBT_OK;
+}
+
+int ensureLkPoints(ebt_ctx* ctx, int n)
+{
+	Frontend& fe = ctx->fe;
+	if (n <= fe.lk_cap) return EBT_OK;
+	cudaFree(fe.d_pts);
+	cudaFree(fe.d_status);
+	cudaFreeHost(fe.h_pts);
+	cudaFreeHost(fe.h_status);
+	fe.d_pts = fe.h_pts = nullptr;
+	fe.d_status = fe.h_status = nullptr;
+	fe.lk_cap = 0;
+	const int cap = std::max(n, 1024);
+	CU(cudaMalloc(&fe.d_pts, static_cast<size_t>(cap) * 4 * sizeof(float)));
+	CU(cudaMalloc(&fe.d_status, static_cast<size_t>(cap)));
+	CU(cudaHostAlloc(&fe.h_pts, static_cast<size_t>(cap) * 4 * sizeof(float), cudaHostAllocDefault));
+	CU(cudaHostAlloc(&fe.h_status, static_cast<size_t>(cap), cudaHostAllocDefault));
+	fe.lk_cap = cap;
+	return EBT_OK;
+}
+
+// goodFeaturesToTrack after the response map (featureselect.cpp): candidates
+// (thresholded 3x3 maxima inside the mask, found on the device) sorted by
+// response, equal responses by descending address (greaterThanPtr), then the
+// greedy minimum-distance selection on a grid of minDistance cells.
+void selectCorners(const ebt_corner_candidate* cand, int n, int W, int H, int max_corners,
+				   double min_distance, std::vector<double>& out)
+{
+	std::vector<int> idx(static_cast<size_t>(n));
+	for (int i = 0; i < n; ++i) idx[static_cast<size_t>(i)] = i;
+	std::sort(idx.begin(), idx.end(), [&](int a, int b) {
+		const ebt_corner_candidate &ca = cand[a], &cb = cand[b];
+		if (ca.value != cb.value) return ca.value > cb.value;
+		return ca.y * W + ca.x > cb.y * W + cb.x;
+	});
+	out.clear();
+	if (min_distance >= 1)
+	{
+		const int cell = static_cast<int>(std::lrint(min_distance));  // cvRound
+		const int gw = (W + cell - 1) / cell, gh = (H + cell - 1) / cell;
+		std::vector<std::vector<int>> grid(static_cast<size_t>(gw) * gh);  // indices into out / 2
+		const double md2 = min_distance * min_distance;
+		for (int k : idx)
+		{
+			const int x = cand[k].x, y = cand[k].y;
+			const int xc = x / cell, yc = y / cell;
+			const int x1 = std::max(0, xc - 1), y1 = std::max(0, yc - 1);
+			const int x2 = std::min(gw - 1, xc + 1), y2 = std::min(gh - 1, yc + 1);
+			bool good = true;
+			for (int yy = y1; yy <= y2 && good; ++yy)
+				for (int xx = x1; xx <= x2 && good; ++xx)
+					for (int j : grid[static_cast<size_t>(yy) * gw + xx])
+					{
+						const double dx = x - out[2 * static_cast<size_t>(j)], dy = y - out[2 * static_cast<size_t>(j) + 1];
+						if (dx * dx + dy * dy < md2)
+						{
+							good = false;
+							break;
+						}
+					}
+			if (!good) continue;
+			grid[static_cast<size_t>(yc) * gw + xc].push_back(static_cast<int>(out.size() / 2));
+			out.push_back(x);
+			out.push_back(y);
+			if (max_corners > 0 && static_cast<int>(out.size() / 2) == max_corners) break;
+		}
+	}
+	else
+	{
+		for (int k : idx)
+		{
+			out.push_back(cand[k].x);
+			out.push_back(cand[k].y);
+			if (max_corners > 0 && static_cast<int>(out.size() / 2) == max_corners) break;
+		}
+	}
+}
+
+// detectFeatures on a device image
+int detectOnDevice(ebt_ctx* ctx, const unsigned char* d_img, std::vector<double>& corners)
+{
+	Frontend& fe = ctx->fe;
+	const int W = ctx->prm.width, H = ctx->prm.height;
+	tic(ctx);
+	CU(ebt_launch_harris(d_img, W, H, 0.04f, fe.prm.quality_level, EBT_PATCH_EXTENT, fe.planes,
+						 fe.resp, fe.max_key, fe.cand, fe.cand_cap, fe.n_cand, ctx->stream));
+	toc(ctx, K_CORNERS);
+	CU(cudaMemcpyAsync(fe.h_ncand, fe.n_cand, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	const int n = *fe.h_ncand;
+	if (n > fe.cand_cap)
+		return fail(ctx, EBT_E_CAPACITY, "corner detector: more local maxima than the candidate buffer holds");
+	if (n > 0)
+	{
+		CU(cudaMemcpyAsync(fe.h_cand, fe.cand, static_cast<size_t>(n) * sizeof(ebt_corner_candidate),
+						   cudaMemcpyDeviceToHost, ctx->stream));
+		CU(cudaStreamSynchronize(ctx->stream));
+	}
+	// FeatureDetector::reset (feature_detector.cpp:34-36)
+	const int max_corners = W * H / (EBT_PATCH_SIDE * EBT_PATCH_SIDE);
+	selectCorners(fe.h_cand, n, W, H, max_corners, fe.prm.min_distance, corners);
+	return EBT_OK;
+}
+
+int buildPyramid(ebt_ctx* ctx, int which)
+{
+	Frontend& fe = ctx->fe;
+	if (fe.built[which] == fe.levels) return EBT_OK;
+	tic(ctx);
+	for (int l = 1; l < fe.levels; ++l)
+		CU(ebt_launch_pyr_down(fe.img[which][l - 1], fe.w[l - 1], fe.h[l - 1], fe.img[which][l], ctx->stream));
+	toc(ctx, K_PYRAMID);
+	fe.built[which] = fe.levels;
+	return EBT_OK;
+}
+
+// calcOpticalFlowPyrLK(img[prev], img[cur], h_pts[0..n)) -> h_pts[2n..4n), h_status
+int lkOnDevice(ebt_ctx* ctx, int prev, int cur, int n)
+{
+	Frontend& fe = ctx->fe;
+	int rc = buildPyramid(ctx, prev);
+	if (rc != EBT_OK) return rc;
+	rc = buildPyramid(ctx, cur);
+	if (rc != EBT_OK) return rc;
+	ebt_lk_pyramids pyr;
+	pyr.levels = fe.levels;
+	tic(ctx);
+	for (int l = 0; l < fe.levels; ++l)
+	{
+		pyr.w[l] = fe.w[l];
+		pyr.h[l] = fe.h[l];
+		pyr.prev[l] = fe.img[prev][l];
+		pyr.cur[l] = fe.img[cur][l];
+		pyr.deriv[l] = fe.deriv[l];
+		CU(ebt_launch_scharr(fe.img[prev][l], fe.w[l], fe.h[l], fe.deriv[l], ctx->stream));
+	}
+	toc(ctx, K_PYRAMID);
+	const size_t nb = static_cast<size_t>(n) * 2 * sizeof(float);
+	CU(cudaMemcpyAsync(fe.d_pts, fe.h_pts, nb, cudaMemcpyHostToDevice, ctx->stream));
+	tic(ctx);
+	CU(ebt_launch_lk(pyr, fe.d_pts, n, fe.d_pts + 2 * static_cast<size_t>(n), fe.d_status, fe.prm.lk_max_count,
+					 fe.prm.lk_epsilon, ctx->stream));
+	toc(ctx, K_LK);
+	CU(cudaMemcpyAsync(fe.h_pts + 2 * static_cast<size_t>(n), fe.d_pts + 2 * static_cast<size_t>(n), nb,
+					   cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaMemcpyAsync(fe.h_status, fe.d_status, static_cast<size_t>(n), cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return EBT_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int ebt_default_frontend_params(ebt_frontend_params* p)
+{
+	if (!p) return EBT_E_INVALID;
+	std::memset(p, 0, sizeof(*p));
+	p->quality_level = 0.01;
+	p->min_distance = 10.0;
+	p->lk_levels = 3;
+	p->lk_max_count = 30;
+	p->lk_epsilon = 0.01;
+	return EBT_OK;
+}
+
+int ebt_set_frontend_params(ebt_ctx* ctx, const ebt_frontend_params* p)
+{
+	if (!ctx || !p || !(p->quality_level > 0) || p->min_distance < 0 || p->lk_levels < 0 ||
+		p->lk_levels >= EBT_LK_MAX_LEVELS || p->lk_max_count < 1 || !(p->lk_epsilon >= 0))
+		return fail(ctx, EBT_E_INVALID, "ebt_set_frontend_params: bad argument");
+	if (ctx->fe.ready && p->lk_levels != ctx->fe.prm.lk_levels)
+		return fail(ctx, EBT_E_INVALID, "ebt_set_frontend_params: lk_levels is fixed once a frame has been seen");
+	ctx->fe.prm = *p;
+	return EBT_OK;
+}
+
+int ebt_detect_features(ebt_ctx* ctx, const uint8_t* gray, double* cornersXY, int cap, int* n_out)
+{
+	if (!ctx || !gray || !n_out || cap < 0 || (cap > 0 && !cornersXY))
+		return fail(ctx, EBT_E_INVALID, "ebt_detect_features: bad argument");
+	CU(cudaSetDevice(ctx->device));
+	int rc = ensureFrontend(ctx);
+	if (rc != EBT_OK) return rc;
+	Frontend& fe = ctx->fe;
+	const size_t npx = static_cast<size_t>(ctx->prm.width) * ctx->prm.height;
+	CU(cudaMemcpyAsync(fe.scratch, gray, npx, cudaMemcpyHostToDevice, ctx->stream));
+	std::vector<double> corners;
+	rc = detectOnDevice(ctx, fe.scratch, corners);
+	if (rc != EBT_OK) return rc;
+	const int n = static_cast<int>(corners.size() / 2);
+	*n_out = n;
+	if (cap > 0) std::memcpy(cornersXY, corners.data(), static_cast<size_t>(std::min(n, cap)) * 2 * sizeof(double));
+	return EBT_OK;
+}
+
+int ebt_get_features(ebt_ctx* ctx, double* cornersXY, int cap, int* n_out)
+{
+	if (!ctx || !n_out || cap < 0 || (cap > 0 && !cornersXY))
+		return fail(ctx, EBT_E_INVALID, "ebt_get_features: bad argument");
+	const int n = static_cast<int>(ctx->corners.size() / 2);
+	*n_out = n;
+	if (cap > 0 && n > 0)
+		std::memcpy(cornersXY, ctx->corners.data(), static_cast<size_t>(std::min(n, cap)) * 2 * sizeof(double));
+	return EBT_OK;
+}
+
+int ebt_lk_flow(ebt_ctx* ctx, const uint8_t* prev_gray, const uint8_t* cur_gray, const float* ptsXY, int n,
+				float* nextXY, uint8_t* status)
+{
+	if (!ctx || !prev_gray || !cur_gray || n < 0 || (n > 0 && (!ptsXY || !nextXY || !status)))
+		return fail(ctx, EBT_E_INVALID, "ebt_lk_flow: bad argument");
+	if (n == 0) return EBT_OK;
+	CU(cudaSetDevice(ctx->device));
+	int rc = ensureFrontend(ctx);
+	if (rc != EBT_OK) return rc;
+	Frontend& fe = ctx->fe;
+	if (fe.have[0] || fe.have[1])
+		return fail(ctx, EBT_E_INVALID, "ebt_lk_flow: not available between ebt_new_image calls; use a second context");
+	rc = ensureLkPoints(ctx, n);
+	if (rc != EBT_OK) return rc;
+	const size_t npx = static_cast<size_t>(ctx->prm.width) * ctx->prm.height;
+	CU(cudaMemcpyAsync(fe.img[0][0], prev_gray, npx, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemcpyAsync(fe.img[1][0], cur_gray, npx, cudaMemcpyHostToDevice, ctx->stream));
+	fe.built[0] = fe.built[1] = 0;
+	std::memcpy(fe.h_pts, ptsXY, static_cast<size_t>(n) * 2 * sizeof(float));
+	rc = lkOnDevice(ctx, 0, 1, n);
+	if (rc != EBT_OK) return rc;
+	std::memcpy(nextXY, fe.h_pts + 2 * static_cast<size_t>(n), static_cast<size_t>(n) * 2 * sizeof(float));
+	std::memcpy(status, fe.h_status, static_cast<size_t>(n));
+	return EBT_OK;
+}
+
+int ebt_new_image(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us)
+{
+	if (!ctx || !gray) return fail(ctx, EBT_E_INVALID, "ebt_new_image: bad argument");
+	CU(cudaSetDevice(ctx->device));
+	int rc = ensureFrontend(ctx);
+	if (rc != EBT_OK) return rc;
+	Frontend& fe = ctx->fe;
+	const size_t npx = static_cast<size_t>(ctx->prm.width) * ctx->prm.height;
+	// FlowEstimator::addImage (flow_estimator.cpp:16-25): current becomes previous
+	fe.cur ^= 1;
+	const int cur = fe.cur, prev = cur ^ 1;
+	CU(cudaMemcpyAsync(fe.img[cur][0], gray, npx, cudaMemcpyHostToDevice, ctx->stream));
+	fe.built[cur] = 0;
+	fe.have[cur] = true;
+	// extractPatches: detectFeatures, gradients, associatePatches
+	std::vector<double> corners;
+	rc = detectOnDevice(ctx, fe.img[cur][0], corners);  // synchronises: `gray` may be reused by the caller
+	if (rc != EBT_OK) return rc;
+	rc = newFrameBegin(ctx, fe.img[cur][0], ts_us, corners.data(), static_cast<int>(corners.size() / 2), true);
+	if (rc != EBT_OK) return rc;
+	// getFlowPatches (flow_estimator.cpp:27-82)
+	if (ctx->image_counter == 2 && fe.have[prev])
+	{
+		int n = 0;
+		for (const DevPatch& p : ctx->h) n += p.init ? 0 : 1;
+		if (n > 0)
+		{
+			rc = ensureLkPoints(ctx, n);
+			if (rc != EBT_OK) return rc;
+			int k = 0;
+			for (const DevPatch& p : ctx->h)
+			{
+				if (p.init) continue;
+				double cx, cy;
+				cornerOf(p, cx, cy);
+				fe.h_pts[2 * k] = static_cast<float>(cx);  // getFlow(const cv::Point2f&)
+				fe.h_pts[2 * k + 1] = static_cast<float>(cy);
+				++k;
+			}
+			rc = lkOnDevice(ctx, prev, cur, n);
+			if (rc != EBT_OK) return rc;
+			k = 0;
+			for (DevPatch& p : ctx->h)
+			{
+				if (p.init) continue;
+				applyFlow(ctx, p, fe.h_status[k], fe.h_pts[2 * (n + k)], fe.h_pts[2 * (n + k) + 1]);
+				++k;
+			}
+		}
+	}
+	return ebt_new_frame_end(ctx);
 }
 
 }  // extern "C"

@@ -84,6 +84,50 @@ int ebt_set_flow(ebt_ctx* ctx, int32_t track_id, int found, float next_x, float 
 int ebt_set_flows(ebt_ctx* ctx, const int32_t* track_ids, const int32_t* found, const float* nextXY, int n);
 int ebt_new_frame_end(ebt_ctx* ctx);
 
+/* ---- per-frame re-arm on the device ------------------------
+ * What the reference delegates to OpenCV inside newImage, as sm_100a kernels
+ * (csrc/ebt_frontend.cu); the algorithm is OpenCV 4.x's, pinned by cv2 golden
+ * vectors (tests/golden/frontend_cv2.npz).
+ *
+ * DetectorParams::qualityLevel / minDistance (feature_detector.h:12-13) and
+ * FlowEstimatorParams::numLevels (flow_estimator.h:13); blockSize 3, Harris
+ * k 0.04, patchExtent 12 and the 21x21 LK window are fixed as in the
+ * reference's defaults. */
+typedef struct ebt_frontend_params
+{
+	double quality_level; /* 0.01 */
+	double min_distance;  /* 10 */
+	int32_t lk_levels;    /* maxLevel 3 */
+	int32_t lk_max_count; /* TermCriteria default of calcOpticalFlowPyrLK: 30 */
+	double lk_epsilon;    /* 0.01 */
+} ebt_frontend_params;
+int ebt_default_frontend_params(ebt_frontend_params* p);
+int ebt_set_frontend_params(ebt_ctx* ctx, const ebt_frontend_params* p);
+
+/* FeatureDetector::detectFeatures (feature_detector.cpp:568-583) =
+ * cv::goodFeaturesToTrack(gray, W*H/625, qualityLevel, minDistance, mask_, 3,
+ * true, 0.04) with the mask of reset() (:34-43).  cornersXY receives up to cap
+ * (x, y) pairs in OpenCV's order (strongest first); *n_out = number found. */
+int ebt_detect_features(ebt_ctx* ctx, const uint8_t* gray, double* cornersXY, int cap, int* n_out);
+
+/* FlowEstimator::getFlow (flow_estimator.cpp:84-103) for n points at once =
+ * cv::calcOpticalFlowPyrLK(prev, cur, pts, next, status, err, {21, 21},
+ * numLevels).  ptsXY / nextXY: n (x, y) float pairs; status: n bytes. */
+int ebt_lk_flow(ebt_ctx* ctx, const uint8_t* prev_gray, const uint8_t* cur_gray, const float* ptsXY,
+				int n, float* nextXY, uint8_t* status);
+
+/* FeatureDetector::newImage (feature_detector.cpp:493-541) in one call:
+ * detectFeatures -> extractPatches/associatePatches -> FlowEstimator::addImage
+ * + getFlowPatches on the previous/current frame pair kept on the device ->
+ * updateNumOfEvents -> archive.  Equivalent to ebt_new_frame_begin /
+ * ebt_get_uninit / ebt_set_flows / ebt_new_frame_end with the corners and LK
+ * results computed by the kernels above. */
+int ebt_new_image(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us);
+
+/* FeatureDetector::getFeatures (feature_detector.h:69): corners_ of the latest
+ * frame, (x, y) pairs; *n_out = number available (may exceed cap). */
+int ebt_get_features(ebt_ctx* ctx, double* cornersXY, int cap, int* n_out);
+
 /* FeatureDetector::updatePatches (feature_detector.cpp:585-619) for n events in
  * stream order (the reference takes one event per call).  Host buffer; the
  * call copies it to the device, runs the stream kernel and returns after the
@@ -145,7 +189,8 @@ int ebt_measure_fma_peak(ebt_ctx* ctx, double* fp64_tflops, double* fp32_tflops)
 
 /* Device-time of the kernels launched since ebt_timing_reset, measured with
  * CUDA events on the context stream: milliseconds and launch count per kernel
- * (0 stream kernel, 1 batched kernel, 2 gradient kernel, 3 window-size kernel). */
+ * (0 stream kernel, 1 batched kernel, 2 gradient kernel, 3 window-size kernel,
+ * 4 corner detector, 5 pyramid + Scharr, 6 LK tracker). */
 int ebt_timing_enable(ebt_ctx* ctx, int on);
 int ebt_timing_get(ebt_ctx* ctx, int kernel, double* ms_total, int64_t* launches);
 int ebt_timing_reset(ebt_ctx* ctx);
@@ -174,6 +219,7 @@ size_t ebt_sizeof_opt_record(void);
 size_t ebt_sizeof_problem(void);
 size_t ebt_sizeof_solution(void);
 size_t ebt_sizeof_params(void);
+size_t ebt_sizeof_frontend_params(void);
 int ebt_abi_version(void);
 
 #ifdef __cplusplus

@@ -7,8 +7,9 @@
 // Differences a caller sees (all forced by the missing OpenCV / batching):
 //  * images are `const uint8_t*` (CV_8U, row-major) instead of cv::Mat;
 //  * the Harris detector and the LK tracker the reference calls inside newImage
-//    (feature_detector.cpp:568-583, flow_estimator.cpp:84-103) are std::function
-//    hooks — the host keeps using cv::goodFeaturesToTrack / calcOpticalFlowPyrLK;
+//    (feature_detector.cpp:568-583, flow_estimator.cpp:84-103) run on the device
+//    (ebt_new_image); a host that wants to keep cv::goodFeaturesToTrack /
+//    calcOpticalFlowPyrLK installs them as std::function hooks (both or neither);
 //  * updatePatches(event) buffers; the batch is flushed on newImage, on any
 //    getter, or when `flushThreshold` events are pending.  Results equal the
 //    per-event loop.
@@ -144,6 +145,18 @@ class FeatureDetector
 	void newImage(const uint8_t* gray, int64_t timestampUs)
 	{
 		flush();
+		if (!detect_ && !flow_)
+		{
+			check(ebt_new_image(ctx_, gray, timestampUs), "ebt_new_image");
+			int nc = 0;
+			check(ebt_get_features(ctx_, nullptr, 0, &nc), "ebt_get_features");
+			std::vector<double> cxy(static_cast<size_t>(nc) * 2);
+			if (nc) check(ebt_get_features(ctx_, cxy.data(), nc, &nc), "ebt_get_features");
+			corners_.clear();
+			for (int i = 0; i < nc; ++i) corners_.push_back(Corner{cxy[2 * i], cxy[2 * i + 1]});
+			dirty_ = true;
+			return;
+		}
 		corners_ = detect_ ? detect_(gray, params_.imageWidth, params_.imageHeight) : Corners();
 		std::vector<double> xy;
 		for (const Corner& c : corners_)

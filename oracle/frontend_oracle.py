@@ -56,10 +56,11 @@ def harris_response(gray: np.ndarray, block: int = 3, k: float = 0.04) -> np.nda
 def select_corners(resp: np.ndarray, max_corners: int, quality: float, min_distance: float,
                    mask: np.ndarray) -> np.ndarray:
     """featureselect.cpp: threshold at quality * max, 3x3 non-maximum suppression
-    on the interior, descending sort (ties in memory order), greedy minimum
+    on the interior, descending sort (ties: larger address first, greaterThanPtr
+    in OpenCV 4.x; pinned by the "ties" golden case), greedy minimum
     distance on a grid of min_distance cells.  Returns (n, 2) float32 (x, y)."""
     h, w = resp.shape
-    thr = F32(resp.max() * quality)
+    thr = F32(float(resp.max()) * float(quality))  # double product, cast to float by cv::threshold
     e = np.where(resp > thr, resp, F32(0))
     q = np.pad(e, 1, mode="constant", constant_values=-np.inf)
     d = np.max([q[i:i + h, j:j + w] for i in range(3) for j in range(3)], axis=0)
@@ -68,7 +69,7 @@ def select_corners(resp: np.ndarray, max_corners: int, quality: float, min_dista
     ok[:, 0] = ok[:, -1] = False
     ys, xs = np.nonzero(ok)
     vals = e[ys, xs]
-    order = np.lexsort((xs, ys, -vals))
+    order = np.lexsort((-xs, -ys, -vals))
     ys, xs = ys[order], xs[order]
     cell = int(round(min_distance))
     gw, gh = (w + cell - 1) // cell, (h + cell - 1) // cell

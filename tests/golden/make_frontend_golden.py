@@ -14,6 +14,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from event_based_odomety_b200 import synth  # noqa: E402
+from tests.golden.tie_image import tie_image  # noqa: E402
 
 CASES = [(240, 180, 1001), (346, 260, 1002), (640, 480, 1003)]
 
@@ -25,6 +26,11 @@ def frames_of(w, h, seed):
 
 def main():
     out = {"cv2_version": np.array(cv2.__version__)}
+    img = tie_image()
+    mask = np.zeros(img.shape, np.uint8)
+    cv2.rectangle(mask, (12, 12, 200 - 24, 100 - 24), 1, cv2.FILLED)
+    out["corners_ties"] = cv2.goodFeaturesToTrack(img, 200 * 100 // 625, 0.01, 10, mask=mask, blockSize=3,
+                                                  useHarrisDetector=True, k=0.04).reshape(-1, 2)
     for w, h, seed in CASES:
         fr = frames_of(w, h, seed)
         mask = np.zeros((h, w), np.uint8)

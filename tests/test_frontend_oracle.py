@@ -28,6 +28,11 @@ def test_corners_match_cv2(w, h, seed):
         assert np.array_equal(c, GOLD[f"corners_{w}_{k}"]), f"corner list of frame {k}"
 
 
+def test_equal_responses_are_ordered_as_cv2_orders_them():
+    from tests.golden.tie_image import tie_image
+    assert np.array_equal(fo.detect_corners(tie_image()), GOLD["corners_ties"])
+
+
 @pytest.mark.parametrize("w,h,seed", CASES[:2])
 def test_lk_matches_cv2(w, h, seed):
     fr = frames_of(w, h, seed)
