@@ -62,6 +62,7 @@ EXPORTS = {
     "ebt_push_events_device": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
     "ebt_get_tracks": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "ebt_get_patch": (C.c_int, [_vp, C.c_int32, C.c_int, _vp]),
+    "ebt_set_products": (C.c_int, [_vp, C.c_int]),
     "ebt_get_trajectory": (C.c_int, [_vp, C.c_int32, _vp, C.c_int, C.POINTER(C.c_int)]),
     "ebt_get_final_costs": (C.c_int, [_vp, C.c_int32, _vp, C.c_int, C.POINTER(C.c_int)]),
     "ebt_get_records": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
@@ -267,6 +268,9 @@ class Tracker:
         out = np.zeros(PATCH_PIXELS)
         self._ck(self.lib.ebt_get_patch(self.ctx, int(track_id), which, _ptr(out)))
         return out
+
+    def set_products(self, mode):
+        self._ck(self.lib.ebt_set_products(self.ctx, int(mode)))
 
     def trajectory(self, track_id):
         n = C.c_int()

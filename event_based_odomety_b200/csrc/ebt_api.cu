@@ -104,6 +104,8 @@ struct ebt_ctx
 	std::vector<ImgSample> img_samples;
 	std::vector<Pending> journal;
 	std::vector<std::vector<int>> arch_nabla;
+	std::vector<std::vector<int>> arch_mc;       // products on: motionCompensatedIntegratedNabla_
+	std::vector<std::vector<double>> arch_pred;  // products on: predictedNabla_
 	std::vector<int> free_slots;
 	bool host_dirty = true;  // h holds changes the device has not seen
 	int next_track_id = 0;
@@ -114,6 +116,8 @@ struct ebt_ctx
 	DevPatch* d_patches = nullptr;
 	ebt_event* d_rings = nullptr;
 	int* d_nablas = nullptr;
+	int* d_mc_nablas = nullptr;       // allocated by ebt_set_products
+	double* d_pred_nablas = nullptr;
 	ebt_opt_record* d_records = nullptr;
 	unsigned long long* d_nrec = nullptr;
 	std::vector<ebt_opt_record> records;
@@ -242,6 +246,12 @@ void addTraj(ebt_ctx* c, DevPatch& p)
 	cornerOf(p, x, y);
 	c->img_samples.push_back({p.track_id, x, y, static_cast<double>(p.cur_ts)});
 	p.n_traj++;
+	p.traj_x[0] = p.traj_x[1];
+	p.traj_y[0] = p.traj_y[1];
+	p.traj_ts[0] = p.traj_ts[1];
+	p.traj_x[1] = x;
+	p.traj_y[1] = y;
+	p.traj_ts[1] = p.cur_ts;
 }
 
 void materialise(ebt_ctx* c)
@@ -412,6 +422,8 @@ int ebt_destroy(ebt_ctx* ctx)
 	cudaFree(ctx->d_patches);
 	cudaFree(ctx->d_rings);
 	cudaFree(ctx->d_nablas);
+	cudaFree(ctx->d_mc_nablas);
+	cudaFree(ctx->d_pred_nablas);
 	cudaFree(ctx->d_records);
 	cudaFree(ctx->d_nrec);
 	cudaFree(ctx->d_events);
@@ -502,6 +514,10 @@ int ebt_create(const ebt_params* params, int device, ebt_ctx** out)
 	d.parameter_tolerance = 1e-8;
 	d.max_consecutive_nonmonotonic_steps = 5;
 	d.max_consecutive_invalid_steps = 5;
+	d.products = 0;
+	d.pad_ = 0;
+	d.mc_nablas = nullptr;
+	d.pred_nablas = nullptr;
 
 	ctx = c;
 	const size_t P = static_cast<size_t>(params->max_patches);
@@ -570,6 +586,8 @@ int ebt_reset(ebt_ctx* ctx)
 	ctx->journal.clear();
 	ctx->arch.clear();
 	ctx->arch_nabla.clear();
+	ctx->arch_mc.clear();
+	ctx->arch_pred.clear();
 	ctx->records.clear();
 	ctx->records_sorted = 0;
 	ctx->record_batches.clear();
@@ -584,6 +602,13 @@ int ebt_reset(ebt_ctx* ctx)
 	ctx->fe.built[0] = ctx->fe.built[1] = 0;
 	CU(cudaMemsetAsync(ctx->d_nablas, 0,
 					   static_cast<size_t>(ctx->prm.max_patches) * EBT_PATCH_PIXELS * sizeof(int), ctx->stream));
+	if (ctx->d_mc_nablas)
+	{
+		CU(cudaMemsetAsync(ctx->d_mc_nablas, 0,
+						   static_cast<size_t>(ctx->prm.max_patches) * EBT_PATCH_PIXELS * sizeof(int), ctx->stream));
+		CU(cudaMemsetAsync(ctx->d_pred_nablas, 0,
+						   static_cast<size_t>(ctx->prm.max_patches) * EBT_PATCH_PIXELS * sizeof(double), ctx->stream));
+	}
 	return EBT_OK;
 }
 
@@ -871,6 +896,23 @@ int ebt_new_frame_end(ebt_ctx* ctx)
 						  EBT_PATCH_PIXELS * sizeof(int), cudaMemcpyDeviceToHost));
 			CU(cudaMemset(ctx->d_nablas + static_cast<size_t>(ctx->h[i].store_slot) * EBT_PATCH_PIXELS, 0,
 						  EBT_PATCH_PIXELS * sizeof(int)));
+			if (ctx->dp.products)
+			{
+				const size_t off = static_cast<size_t>(ctx->h[i].store_slot) * EBT_PATCH_PIXELS;
+				std::vector<int> mc(EBT_PATCH_PIXELS);
+				std::vector<double> pr(EBT_PATCH_PIXELS);
+				CU(cudaMemcpy(mc.data(), ctx->d_mc_nablas + off, EBT_PATCH_PIXELS * sizeof(int), cudaMemcpyDeviceToHost));
+				CU(cudaMemcpy(pr.data(), ctx->d_pred_nablas + off, EBT_PATCH_PIXELS * sizeof(double), cudaMemcpyDeviceToHost));
+				CU(cudaMemset(ctx->d_mc_nablas + off, 0, EBT_PATCH_PIXELS * sizeof(int)));
+				CU(cudaMemset(ctx->d_pred_nablas + off, 0, EBT_PATCH_PIXELS * sizeof(double)));
+				ctx->arch_mc.push_back(std::move(mc));
+				ctx->arch_pred.push_back(std::move(pr));
+			}
+			else
+			{
+				ctx->arch_mc.emplace_back();
+				ctx->arch_pred.emplace_back();
+			}
 			ctx->arch.push_back(ctx->h[i]);
 			ctx->arch_nabla.push_back(std::move(nab));
 			ctx->free_slots.push_back(ctx->h[i].store_slot);
@@ -1051,20 +1093,63 @@ static const HostTrack* findTrack(ebt_ctx* ctx, int32_t id, const DevPatch** p, 
 
 int ebt_get_patch(ebt_ctx* ctx, int32_t track_id, int which, double* out625)
 {
-	if (!ctx || !out625 || which != 0) return fail(ctx, EBT_E_INVALID, "ebt_get_patch: bad argument");
+	if (!ctx || !out625 || which < 0 || which > 2) return fail(ctx, EBT_E_INVALID, "ebt_get_patch: bad argument");
+	if (which != 0 && !ctx->dp.products)
+		return fail(ctx, EBT_E_INVALID, "ebt_get_patch: this product is not computed; enable it with ebt_set_products");
 	const DevPatch* p = nullptr;
 	int ai = -1;
 	if (!findTrack(ctx, track_id, &p, &ai)) return fail(ctx, EBT_E_INVALID, "ebt_get_patch: unknown track id");
+	const size_t off = static_cast<size_t>(p->store_slot) * EBT_PATCH_PIXELS;
+	if (which == 2)
+	{
+		if (ai >= 0)
+		{
+			if (ctx->arch_pred[static_cast<size_t>(ai)].empty())
+				return fail(ctx, EBT_E_INVALID, "ebt_get_patch: track was archived before the products were enabled");
+			std::memcpy(out625, ctx->arch_pred[static_cast<size_t>(ai)].data(), EBT_PATCH_PIXELS * sizeof(double));
+		}
+		else
+		{
+			CU(cudaSetDevice(ctx->device));
+			CU(cudaMemcpy(out625, ctx->d_pred_nablas + off, EBT_PATCH_PIXELS * sizeof(double), cudaMemcpyDeviceToHost));
+		}
+		return EBT_OK;
+	}
 	int nab[EBT_PATCH_PIXELS];
 	if (ai >= 0)
-		std::memcpy(nab, ctx->arch_nabla[ai].data(), sizeof(nab));
+	{
+		const std::vector<int>& src = which == 0 ? ctx->arch_nabla[static_cast<size_t>(ai)] : ctx->arch_mc[static_cast<size_t>(ai)];
+		if (src.empty())
+			return fail(ctx, EBT_E_INVALID, "ebt_get_patch: track was archived before the products were enabled");
+		std::memcpy(nab, src.data(), sizeof(nab));
+	}
 	else
 	{
 		CU(cudaSetDevice(ctx->device));
-		CU(cudaMemcpy(nab, ctx->d_nablas + static_cast<size_t>(p->store_slot) * EBT_PATCH_PIXELS, sizeof(nab),
-					  cudaMemcpyDeviceToHost));
+		CU(cudaMemcpy(nab, (which == 0 ? ctx->d_nablas : ctx->d_mc_nablas) + off, sizeof(nab), cudaMemcpyDeviceToHost));
 	}
 	for (int i = 0; i < EBT_PATCH_PIXELS; ++i) out625[i] = static_cast<double>(nab[i]);
+	return EBT_OK;
+}
+
+// DetectorParams::drawImages and the per-optimisation Patch::warpImage /
+// integrateMotionCompensatedEvents calls (feature_detector.cpp:504-510, 615;
+// optimizer.cpp:182): products that only feed getters.
+int ebt_set_products(ebt_ctx* ctx, int mode)
+{
+	if (!ctx || mode < 0 || mode > 2) return fail(ctx, EBT_E_INVALID, "ebt_set_products: mode must be 0, 1 or 2");
+	CU(cudaSetDevice(ctx->device));
+	if (mode && !ctx->d_mc_nablas)
+	{
+		const size_t n = static_cast<size_t>(ctx->prm.max_patches) * EBT_PATCH_PIXELS;
+		CU(cudaMalloc(&ctx->d_mc_nablas, n * sizeof(int)));
+		CU(cudaMalloc(&ctx->d_pred_nablas, n * sizeof(double)));
+		CU(cudaMemset(ctx->d_mc_nablas, 0, n * sizeof(int)));
+		CU(cudaMemset(ctx->d_pred_nablas, 0, n * sizeof(double)));
+	}
+	ctx->dp.products = mode;
+	ctx->dp.mc_nablas = ctx->d_mc_nablas;
+	ctx->dp.pred_nablas = ctx->d_pred_nablas;
 	return EBT_OK;
 }
 

@@ -31,6 +31,10 @@ struct DevPatch
 	int frame_slot, store_slot;
 	int last_n_opt;  // optimisations in the previous push (CTA ordering estimate)
 	int n_traj;      // Patch::trajectory_.size(): image-time samples (host) + kept optimisations (device)
+	// the two newest entries of Patch::trajectory_ (what integrateMotionCompensatedEvents reads,
+	// patch.cpp:91-92): [0] = second newest, [1] = newest
+	double traj_x[2], traj_y[2];
+	long long traj_ts[2];
 };
 
 // Solver constants: the reference's OptimizerParams
@@ -58,6 +62,12 @@ struct DevParams
 	double parameter_tolerance;   // 1e-8
 	int max_consecutive_nonmonotonic_steps;  // 5
 	int max_consecutive_invalid_steps;       // 5
+	// Getter-only products of tracker::Patch (ebt_set_products): 0 none, 1 after every
+	// optimisation (what the reference always does), 2 also at image time (drawImages).
+	int products;
+	int pad_;
+	int* mc_nablas;       // [store_slot][625] Patch::motionCompensatedIntegratedNabla_
+	double* pred_nablas;  // [store_slot][625] Patch::predictedNabla_
 };
 
 // Gradient grids of the live template frames: interleaved (gx, gy) doubles,

@@ -1200,6 +1200,97 @@ __device__ EBT_NOINLINE void update_num_of_events(FeatShared& sh, FeatState& st,
 								(unsigned long long)P.max_num_events);
 }
 
+// Patch::addTrajectoryPosition after an optimisation (optimizer.cpp:179-181): the
+// device keeps the two newest trajectory entries, then — when the products are on —
+// Patch::integrateMotionCompensatedEvents (ft/src/patch.cpp:87-130): every window
+// event is moved along the newest trajectory segment to the window's mid time,
+// rounded half-to-even (static_cast<Point2i>(Point2d)), tested against the moved
+// rect and accumulated.  Integer work, global atomics on the feature's 625 ints.
+struct McArgs
+{
+	double rx, ry;
+	long long cur_ts;
+	int n_traj, size, tail;
+};
+__device__ __noinline__ void motion_compensated(FeatShared& sh, const McArgs st, DevPatch& gp, int products,
+											   int* mc_nablas)
+{
+	if (threadIdx.x == 0)
+	{
+		const double px = gp.traj_x[1], py = gp.traj_y[1];
+		const long long pt = gp.traj_ts[1];
+		const double lx = st.rx + (SIDE - 1) / 2., ly = st.ry + (SIDE - 1) / 2.;
+		gp.traj_x[0] = px; gp.traj_y[0] = py; gp.traj_ts[0] = pt;
+		gp.traj_x[1] = lx; gp.traj_y[1] = ly; gp.traj_ts[1] = st.cur_ts;
+		// midTime = currentTimestamp_ = the newest entry's timestamp
+		const long long half = to_i32((double)(st.cur_ts - pt) * 0.5);
+		const bool run = products && st.n_traj >= 2 && st.size > 0 && st.cur_ts + half >= st.cur_ts &&
+						 pt < st.cur_ts;
+		sh.req[0] = run ? 1.0 : 0.0;
+		sh.req[1] = lx - px;
+		sh.req[2] = ly - py;
+		sh.req[3] = (double)(st.cur_ts - pt);
+	}
+	__syncthreads();
+	const bool run = sh.req[0] != 0.0;
+	const double dirx = sh.req[1], diry = sh.req[2], t_dif = sh.req[3];
+	__syncthreads();
+	if (!run) return;
+	int* mc = mc_nablas + (size_t)gp.store_slot * NPIX;
+	for (int i = threadIdx.x; i < NPIX; i += NT) mc[i] = 0;
+	__syncthreads();
+	const double t = (double)st.cur_ts;
+	for (int k = threadIdx.x; k < st.size; k += NT)
+	{
+		const ebt_event e = sh.ring[(st.tail + k) & RMASK];
+		const double sc = __ddiv_rn(t - (double)e.t_us, t_dif);
+		const double cxd = __dadd_rn((double)e.x, __dmul_rn(dirx, sc));
+		const double cyd = __dadd_rn((double)e.y, __dmul_rn(diry, sc));
+		if (!(fabs(cxd) < 2e9 && fabs(cyd) < 2e9)) continue;
+		const int cx = __double2int_rn(cxd), cy = __double2int_rn(cyd);
+		if (in_rect(st.rx, st.ry, cx, cy))
+		{
+			const int px = (int)(cx - st.rx), py = (int)(cy - st.ry);
+			atomicAdd(&mc[py * SIDE + px], (int)e.polarity);
+		}
+	}
+	__syncthreads();
+}
+
+// Patch::warpImage (ft/src/patch.cpp:132-154): predictedNabla_ = -gx cos(flowDir_)
+// - gy sin(flowDir_) of the patch's own template gradients, sampled as
+// cv::warpAffine(WARP_INVERSE_MAP) does (nearest neighbour, 10-bit fixed point) on
+// Rect(patch_).  Left unchanged when the rect is not strictly inside the image.
+struct PredArgs
+{
+	double rx, ry, c, s, tx, ty, flow;
+};
+__device__ __noinline__ void predicted_nabla(const PredArgs st, const double2* __restrict__ grid, int W, int H,
+											 double* __restrict__ out)
+{
+	if (st.rx < 0 || st.ry < 0 || st.rx + SIDE >= W || st.ry + SIDE >= H) return;
+	const double c = st.c, s = st.s, tx = st.tx, ty = st.ty;
+	const int x0 = __double2int_rn(st.rx), y0 = __double2int_rn(st.ry);
+	const double a = -cos(st.flow), b = -sin(st.flow);
+	for (int i = threadIdx.x; i < NPIX; i += NT)
+	{
+		const int yy = i / SIDE;
+		const int x = x0 + (i - yy * SIDE), y = y0 + yy;
+		const int X0 = __double2int_rn(c * x * 1024) +
+					   __double2int_rn(__dadd_rn(__dmul_rn(-s, y), tx) * 1024) + 512;
+		const int Y0 = __double2int_rn(s * x * 1024) +
+					   __double2int_rn(__dadd_rn(__dmul_rn(c, y), ty) * 1024) + 512;
+		const int xi = X0 >> 10, yi = Y0 >> 10;
+		double v = 0.0;
+		if (xi >= 0 && xi < W && yi >= 0 && yi < H)
+		{
+			const double2 g = __ldg(grid + (size_t)yi * W + xi);
+			v = __dadd_rn(__dmul_rn(g.x, a), __dmul_rn(g.y, b));
+		}
+		out[i] = v;
+	}
+}
+
 __device__ __forceinline__ void load_state(FeatState& st, const DevPatch& p)
 {
 	st.rx = p.rx; st.ry = p.ry; st.ix = p.ix; st.iy = p.iy;
@@ -1423,7 +1514,14 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 	auto optimise_at = [&](long long at) -> bool {
 		LmSummary S;
 		optimize_feature(sh, costs, st, ft, P, S);
+		if (!S.filtered)
+			motion_compensated(sh, McArgs{st.rx, st.ry, st.cur_ts, st.n_traj, st.size, st.tail}, gp, P.products,
+							   P.mc_nablas);
 		update_num_of_events(sh, st, ft, P);
+		if (P.products)  // feature_detector.cpp:615
+			predicted_nabla(PredArgs{st.rx, st.ry, st.warp[0], st.warp[1], st.warp[2], st.warp[3], st.flow},
+							ft.grid[st.frame_slot], P.width, P.height,
+							P.pred_nablas + (size_t)gp.store_slot * NPIX);
 		if (threadIdx.x == 0) write_record(records, n_records, record_cap, st, track_id, S, event_base + at);
 		++n_opt;
 		start = at + 1;
@@ -1637,6 +1735,10 @@ num_events_kernel(DevPatch* __restrict__ patches, int n_patches, FrameTable ft, 
 	FeatState st;
 	load_state(st, patches[f]);
 	update_num_of_events(sh, st, ft, P);
+	if (P.products == 2)  // feature_detector.cpp:504-510
+		predicted_nabla(PredArgs{st.rx, st.ry, st.warp[0], st.warp[1], st.warp[2], st.warp[3], st.flow},
+						ft.grid[st.frame_slot], P.width, P.height,
+						P.pred_nablas + (size_t)patches[f].store_slot * NPIX);
 	if (threadIdx.x == 0)
 	{
 		patches[f].lost = st.lost;

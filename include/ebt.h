@@ -144,9 +144,20 @@ int ebt_push_events_device(ebt_ctx* ctx, const ebt_event* d_events, int64_t n,
  * snapshots in list order.  *n_out = number available (may exceed cap). */
 int ebt_get_tracks(ebt_ctx* ctx, ebt_track* out, int cap, int archived, int* n_out);
 
-/* Patch::getIntegratedNabla (patch.h:49): 625 doubles, row-major at<double>(y,x).
- * which: 0 = integratedNabla_. */
+/* Patch::getIntegratedNabla / getCompenatedIntegratedNabla / getPredictedNabla
+ * (patch.h:49-50, 67): 625 doubles, row-major at<double>(y,x).
+ * which: 0 = integratedNabla_, 1 = motionCompensatedIntegratedNabla_,
+ * 2 = predictedNabla_ (1 and 2 need ebt_set_products). */
 int ebt_get_patch(ebt_ctx* ctx, int32_t track_id, int which, double* out625);
+
+/* The two Patch products that only feed getters: Patch::integrateMotion-
+ * CompensatedEvents (patch.cpp:87-130, called by Optimizer::optimize,
+ * optimizer.cpp:182) and Patch::warpImage (patch.cpp:132-154, called after
+ * every optimisation, feature_detector.cpp:615, and for every patch at image
+ * time when DetectorParams::drawImages is set, :504-510).
+ * mode 0 (default): not computed; 1: after every optimisation (the reference
+ * with drawImages = false); 2: also at image time (drawImages = true). */
+int ebt_set_products(ebt_ctx* ctx, int mode);
 
 /* Patch::getTrajectory (patch.h:58): (x, y, t_us) triples. */
 int ebt_get_trajectory(ebt_ctx* ctx, int32_t track_id, double* out_xyt, int cap, int* n_out);

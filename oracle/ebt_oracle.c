@@ -613,6 +613,8 @@ typedef struct
 	int tail, size;
 	int num_of_events, counter;
 	double nabla[NPIX];
+	double mc_nabla[NPIX];   /* motionCompensatedIntegratedNabla_ */
+	double pred_nabla[NPIX]; /* predictedNabla_ */
 	double flow;    /* flowDir_ (double); read through float getFlow() */
 	double warp[4]; /* cos sin tx ty */
 	double* traj;   /* (x, y, ts) triples */
@@ -750,8 +752,73 @@ static void patch_update_rect(opatch* p)
 	p->ry = ncy - EBT_PATCH_EXTENT;
 }
 
-/* Optimizer::optimize, ft/src/optimizer.cpp:62-206 (drawCostMap off;
- * integrateMotionCompensatedEvents is a getter-only product). */
+static int cv_round(double v) { return (int)nearbyint(v); }
+
+/* Patch::integrateMotionCompensatedEvents, patch.cpp:87-130: the window's
+ * events moved along the last trajectory segment to the window's mid time.
+ * static_cast<Point2i>(Point2d) rounds half-to-even, frameToPatchCoords
+ * truncates, containment is tested against the (already updated) rect. */
+static void patch_integrate_motion_compensated(opatch* p)
+{
+	if (p->n_traj < 2 || p->size == 0) return;
+	const double* last = &p->traj[3 * (p->n_traj - 1)];
+	const double* pre = &p->traj[3 * (p->n_traj - 2)];
+	const int64_t last_ts = (int64_t)last[2], pre_ts = (int64_t)pre[2];
+	const int64_t mid = p->cur_ts;
+	const int64_t half = to_i32((double)(last_ts - pre_ts) * 0.5);
+	if (!(last_ts + half >= mid && pre_ts < mid)) return;
+	for (int i = 0; i < NPIX; ++i) p->mc_nabla[i] = 0;
+	const double dirx = last[0] - pre[0], diry = last[1] - pre[1];
+	const double t_dif = (double)(last_ts - pre_ts);
+	const double t = (double)mid;
+	for (int k = 0; k < p->size; ++k)
+	{
+		const ebt_event* e = &p->ring[(p->tail + p->size - 1 - k) & (RING - 1)];
+		const double sc = (t - (double)e->t_us) / t_dif;
+		const double cxd = (double)e->x + dirx * sc, cyd = (double)e->y + diry * sc;
+		if (!(fabs(cxd) < 2e9 && fabs(cyd) < 2e9)) continue; /* saturate_cast: never inside */
+		const int cx = cv_round(cxd), cy = cv_round(cyd);
+		if (in_rect(p, cx, cy))
+		{
+			const int px = (int)(cx - p->rx), py = (int)(cy - p->ry);
+			p->mc_nabla[py * SIDE + px] += (double)e->polarity;
+		}
+	}
+}
+
+/* Patch::warpImage, patch.cpp:132-154: the patch's own template gradients
+ * (Patch::gradX_/gradY_, set at creation) warped with cv::warpAffine(flags =
+ * WARP_INVERSE_MAP) = nearest neighbour, 10-bit fixed point, cropped to
+ * Rect(patch_) (each field rounded half-to-even);
+ * predictedNabla = -gx cos(flowDir_) - gy sin(flowDir_).  Unchanged when the
+ * rect is not strictly inside the image. */
+static void patch_warp_image(opatch* p, const oframe* f)
+{
+	if (p->rx < 0 || p->ry < 0 || p->rx + SIDE >= f->w || p->ry + SIDE >= f->h) return;
+	const double c = p->warp[0], s = p->warp[1], tx = p->warp[2], ty = p->warp[3];
+	const int x0 = cv_round(p->rx), y0 = cv_round(p->ry);
+	const double a = -cos(p->flow), b = -sin(p->flow);
+	for (int yy = 0; yy < SIDE; ++yy)
+		for (int xx = 0; xx < SIDE; ++xx)
+		{
+			const int x = x0 + xx, y = y0 + yy;
+			double vx = 0, vy = 0;
+			if (x >= 0 && x < f->w && y >= 0 && y < f->h) /* crop of the warped full frame */
+			{
+				const int X0 = cv_round(c * x * 1024) + cv_round((-s * y + tx) * 1024) + 512;
+				const int Y0 = cv_round(s * x * 1024) + cv_round((c * y + ty) * 1024) + 512;
+				const int xi = X0 >> 10, yi = Y0 >> 10;
+				if (xi >= 0 && xi < f->w && yi >= 0 && yi < f->h)
+				{
+					vx = f->g[2 * (yi * f->w + xi)];
+					vy = f->g[2 * (yi * f->w + xi) + 1];
+				}
+			}
+			p->pred_nabla[yy * SIDE + xx] = vx * a + vy * b;
+		}
+}
+
+/* Optimizer::optimize, ft/src/optimizer.cpp:62-206 (drawCostMap off). */
 static void optimize_patch(opatch* p, const oframe* frame, double huber_a,
 						   double threshold, int max_iter, osummary* S)
 {
@@ -806,6 +873,7 @@ static void optimize_patch(opatch* p, const oframe* frame, double huber_a,
 	const double mv = sqrt((nx - ox) * (nx - ox) + (ny - oy) * (ny - oy));
 	p->time_without_update = (int64_t)(1e6 / fmax(1e-1, mv));
 	add_traj(p);
+	patch_integrate_motion_compensated(p);
 	p->counter = 0; /* resetBatch */
 }
 
@@ -831,9 +899,8 @@ typedef struct
 	ebt_opt_record* records;
 	int64_t n_records, cap_records;
 	int64_t event_index;
+	int draw_images; /* DetectorParams::drawImages */
 } otracker;
-
-static int cv_round(double v) { return (int)nearbyint(v); }
 
 /* FeatureDetector::updateNumOfEvents, feature_detector.cpp:666-712, with
  * cv::warpAffine(flags = WARP_INVERSE_MAP) = nearest neighbour, 10-bit fixed
@@ -1020,6 +1087,9 @@ void oracle_new_frame_end(void* h)
 {
 	otracker* T = (otracker*)h;
 	for (int i = 0; i < T->n_patches; ++i) update_num_of_events(T, T->patches[i]);
+	if (T->draw_images) /* feature_detector.cpp:504-510 */
+		for (int i = 0; i < T->n_patches; ++i)
+			patch_warp_image(T->patches[i], &T->frames[T->patches[i]->frame_slot]);
 	int k = 0;
 	for (int i = 0; i < T->n_patches; ++i)
 	{
@@ -1083,6 +1153,7 @@ int64_t oracle_push_events(void* h, const ebt_event* ev, int64_t n)
 				optimize_patch(p, &T->frames[p->frame_slot], T->huber_a, T->threshold,
 							   T->max_iter, &S);
 				update_num_of_events(T, p);
+				patch_warp_image(p, &T->frames[p->frame_slot]); /* feature_detector.cpp:615 */
 				push_record(T, p, &S);
 				++n_opt;
 			}
@@ -1146,10 +1217,12 @@ static opatch* find_patch(otracker* T, int32_t id)
 int oracle_get_patch(void* h, int32_t id, int which, double* out625)
 {
 	opatch* p = find_patch((otracker*)h, id);
-	if (!p || which != 0) return -1;
-	memcpy(out625, p->nabla, sizeof(p->nabla));
+	/* which: 0 integratedNabla_, 1 motionCompensatedIntegratedNabla_, 2 predictedNabla_ */
+	if (!p || which < 0 || which > 2) return -1;
+	memcpy(out625, which == 0 ? p->nabla : which == 1 ? p->mc_nabla : p->pred_nabla, sizeof(p->nabla));
 	return NPIX;
 }
+void oracle_set_draw_images(void* h, int on) { ((otracker*)h)->draw_images = on; }
 int oracle_get_trajectory(void* h, int32_t id, double* out, int cap)
 {
 	opatch* p = find_patch((otracker*)h, id);

@@ -113,6 +113,7 @@ struct RefTracker
 	size_t nextTrackId = 0;
 	int imageCounter = 0;  // FlowEstimator::imageCounter_
 	bool callWarpImage = false;
+	bool drawImages = false;  // DetectorParams::drawImages (feature_detector.cpp:504-510)
 	std::vector<ebt_opt_record> records;
 	int64_t eventIndex = 0;
 };
@@ -210,6 +211,7 @@ void* ref_create(int width, int height, int maxPatches, int callWarpImage)
 }
 
 void ref_destroy(void* h) { delete static_cast<RefTracker*>(h); }
+void ref_set_draw_images(void* h, int on) { static_cast<RefTracker*>(h)->drawImages = on != 0; }
 
 // FeatureDetector::newImage part 1 = extractPatches (feature_detector.cpp:
 // 543-566) with the Harris corners injected, then associatePatches (:630-664).
@@ -324,6 +326,8 @@ void ref_new_frame_end(void* h)
 {
 	auto& T = *static_cast<RefTracker*>(h);
 	for (auto& patch : T.patches) updateNumOfEvents(T, patch);
+	if (T.drawImages)
+		for (auto& patch : T.patches) patch.warpImage();
 	for (auto it = T.patches.begin(); it != T.patches.end();)
 	{
 		if (it->isLost())

@@ -68,6 +68,7 @@ def _declare(dll, prefix):
     else:
         fn("create", _vp, C.c_int, C.c_int, C.c_int)
     fn("destroy", None, _vp)
+    fn("set_draw_images", None, _vp, C.c_int)
     fn("new_frame_begin", C.c_int if prefix != "ref_" else None, _vp, _vp, C.c_int64, _vp, C.c_int)
     fn("get_uninit", C.c_int, _vp, _vp, _vp, C.c_int)
     fn("set_flow", None, _vp, C.c_int32, C.c_int, C.c_float, C.c_float)
@@ -105,13 +106,17 @@ def _declare(dll, prefix):
 class CpuTracker:
     """Stream-mode CPU tracker (reference harness or C restatement)."""
 
-    def __init__(self, lib, width, height, max_patches=100):
+    def __init__(self, lib, width, height, max_patches=100, warp_image=False, draw_images=False):
         self.L = lib
         self.w, self.h = width, height
         if lib.prefix == "ref_":
-            self.h_ = lib.create(width, height, max_patches, 0)
+            # warp_image: also run Patch::warpImage after every optimisation as the reference
+            # does (two full-frame warps; off by default because it only feeds a getter)
+            self.h_ = lib.create(width, height, max_patches, int(warp_image or draw_images))
         else:
             self.h_ = lib.create(width, height, max_patches)
+        if draw_images:
+            lib.set_draw_images(self.h_, 1)
 
     def close(self):
         if self.h_:

@@ -72,10 +72,14 @@ def main():
             super().new_frame_begin(gray, ts, corners)
 
     frames_seen = []
-    t = Rec(ref, 240, 180, 100)
+    t = Rec(ref, 240, 180, 100, warp_image=True)  # Patch::warpImage after every optimisation, as the reference does
     n = synth.run_stream(t, S)
     tracks = np.concatenate([t.tracks(False), t.tracks(True)])
     patches = np.stack([t.patch(i) for i in tracks["track_id"]]).astype(np.int16)
+    # getter-only products of the same run: motionCompensatedIntegratedNabla_ (integer valued), predictedNabla_
+    np.savez_compressed(os.path.join(HERE, "products_ref.npz"),
+                        mc=np.stack([t.patch(i, 1) for i in tracks["track_id"]]).astype(np.int16),
+                        pred=np.stack([t.patch(i, 2) for i in tracks["track_id"]]))
     cmax = max(len(c) for c in S.corners)
     corners = np.full((len(S.corners), cmax, 2), np.nan)
     for i, c in enumerate(S.corners):

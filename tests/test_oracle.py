@@ -123,6 +123,20 @@ def test_stream_against_reference_golden(ora):
         assert np.array_equal(t.patch(tid).astype(np.int16), g["patches"][i])
 
 
+def test_products_against_reference_golden(ora):
+    """Patch::integrateMotionCompensatedEvents (patch.cpp:87-130) and Patch::warpImage
+    (patch.cpp:132-154) of the same reference run (tests/golden/products_ref.npz)"""
+    g = np.load(os.path.join(G, "stream_ref.npz"))
+    pr = np.load(os.path.join(G, "products_ref.npz"))
+    t = CpuTracker(ora, 240, 180, 100)
+    _replay(t, g)
+    tracks = np.concatenate([t.tracks(False), t.tracks(True)])
+    assert len(tracks) == len(pr["mc"]) and np.abs(pr["mc"]).sum() > 0 and np.abs(pr["pred"]).sum() > 0
+    for i, tid in enumerate(tracks["track_id"]):
+        assert np.array_equal(t.patch(tid, 1).astype(np.int16), pr["mc"][i]), f"track {tid}"
+        assert np.abs(t.patch(tid, 2) - pr["pred"][i]).max() < 1e-14, f"track {tid}"
+
+
 def test_warp_affine_nearest_rule_against_cv2(ora):
     """cv::warpAffine(flags=WARP_INVERSE_MAP) = nearest neighbour with 10-bit
     fixed-point coordinates (feature_detector.cpp:695-698)."""
