@@ -39,6 +39,11 @@ class FrontendParams(C.Structure):
                 ("lk_max_count", C.c_int32), ("lk_epsilon", C.c_double)]
 
 
+class Camera(C.Structure):
+    """common::CameraModelParams<double>"""
+    _fields_ = [(k, C.c_double) for k in ("fx", "fy", "cx", "cy", "k1", "k2", "k3", "p1", "p2")]
+
+
 EXPORTS = {
     "ebt_default_params": (C.c_int, [C.POINTER(Params), C.c_int, C.c_int]),
     "ebt_create": (C.c_int, [C.POINTER(Params), C.c_int, C.POINTER(_vp)]),
@@ -60,9 +65,14 @@ EXPORTS = {
     "ebt_get_features": (C.c_int, [_vp, _vp, C.c_int, C.POINTER(C.c_int)]),
     "ebt_push_events": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
     "ebt_push_events_device": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
+    "ebt_parse_events_text": (C.c_int, [_vp, C.c_char_p, C.c_size_t, C.c_int, _vp, C.c_int64,
+                                        C.POINTER(C.c_int64), C.POINTER(C.c_size_t)]),
+    "ebt_replay": (C.c_int, [_vp, _vp, C.c_int64, _vp, _vp, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "ebt_get_tracks": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "ebt_get_patch": (C.c_int, [_vp, C.c_int32, C.c_int, _vp]),
     "ebt_set_products": (C.c_int, [_vp, C.c_int]),
+    "ebt_get_landmarks": (C.c_int, [_vp, C.POINTER(Camera), _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]),
+    "ebt_unproject": (C.c_int, [_vp, C.POINTER(Camera), _vp, C.c_int, _vp]),
     "ebt_get_trajectory": (C.c_int, [_vp, C.c_int32, _vp, C.c_int, C.POINTER(C.c_int)]),
     "ebt_get_final_costs": (C.c_int, [_vp, C.c_int32, _vp, C.c_int, C.POINTER(C.c_int)]),
     "ebt_get_records": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
@@ -85,6 +95,7 @@ EXPORTS = {
     "ebt_sizeof_solution": (C.c_size_t, []),
     "ebt_sizeof_params": (C.c_size_t, []),
     "ebt_sizeof_frontend_params": (C.c_size_t, []),
+    "ebt_sizeof_camera": (C.c_size_t, []),
     "ebt_abi_version": (C.c_int, []),
 }
 
@@ -115,7 +126,7 @@ def _ptr(a):
     return a.ctypes.data_as(_vp)
 
 
-K_TRACK, K_BATCH, K_GRAD, K_NUMEV, K_CORNERS, K_PYRAMID, K_LK = range(7)
+K_TRACK, K_BATCH, K_GRAD, K_NUMEV, K_CORNERS, K_PYRAMID, K_LK, K_PARSE = range(8)
 
 
 class Tracker:
@@ -246,6 +257,30 @@ class Tracker:
         self._ck(self.lib.ebt_push_events_device(self.ctx, _vp(dev_ptr), n_events, C.byref(n)))
         return n.value
 
+    # ---- ingestion ------------------------------------------------------
+    def parse_events_text(self, text: bytes, final=True, cap=None):
+        """(events, bytes consumed) of a buffer of "t_sec x y p" lines."""
+        if cap is None:
+            cap = text.count(b"\n") + 1
+        out = np.zeros(max(cap, 1), EVENT)
+        n = C.c_int64()
+        used = C.c_size_t()
+        self._ck(self.lib.ebt_parse_events_text(self.ctx, text, len(text), int(final), _ptr(out), cap,
+                                                C.byref(n), C.byref(used)))
+        return out[:n.value].copy(), used.value
+
+    def replay(self, events, frames, frame_ts):
+        """Replayer order over in-memory samples; returns (events delivered, optimisations)."""
+        events = np.ascontiguousarray(events)
+        assert events.dtype == EVENT
+        frames = np.ascontiguousarray(np.stack(frames), np.uint8)
+        ts = np.ascontiguousarray(frame_ts, np.int64)
+        assert frames.shape == (len(ts), self.height, self.width)
+        nd, no = C.c_int64(), C.c_int64()
+        self._ck(self.lib.ebt_replay(self.ctx, _ptr(events), len(events), _ptr(frames), _ptr(ts), len(ts),
+                                     C.byref(nd), C.byref(no)))
+        return nd.value, no.value
+
     # ---- getters --------------------------------------------------------
     def tracks(self, archived=False):
         n = C.c_int()
@@ -267,6 +302,24 @@ class Tracker:
     def patch(self, track_id, which=0):
         out = np.zeros(PATCH_PIXELS)
         self._ck(self.lib.ebt_get_patch(self.ctx, int(track_id), which, _ptr(out)))
+        return out
+
+    # ---- tracker -> VO hand-off ---------------------------------------------
+    def landmarks(self, camera=None, cap=8192):
+        """(track ids, corners (n,2), bearings (n,3) or None) of the live patches."""
+        ids = np.zeros(cap, np.int32)
+        xy = np.zeros((cap, 2))
+        b = np.zeros((cap, 3)) if camera is not None else None
+        n = C.c_int()
+        self._ck(self.lib.ebt_get_landmarks(self.ctx, C.byref(camera) if camera is not None else None,
+                                            _ptr(ids), _ptr(xy), _ptr(b), cap, C.byref(n)))
+        m = min(n.value, cap)
+        return ids[:m].copy(), xy[:m].copy(), (b[:m].copy() if b is not None else None)
+
+    def unproject(self, camera, pts):
+        pts = np.ascontiguousarray(pts, np.float64).reshape(-1, 2)
+        out = np.zeros((len(pts), 3))
+        self._ck(self.lib.ebt_unproject(self.ctx, C.byref(camera), _ptr(pts), len(pts), _ptr(out)))
         return out
 
     def set_products(self, mode):

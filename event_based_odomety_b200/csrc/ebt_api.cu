@@ -18,6 +18,7 @@
 #include "../../include/ebt.h"
 #include "ebt_device_types.h"
 #include "ebt_frontend.h"
+#include "ebt_ingest.h"
 #include "ebt_kernels.h"
 
 namespace
@@ -47,7 +48,8 @@ enum
 	K_CORNERS = 4,
 	K_PYRAMID = 5,
 	K_LK = 6,
-	K_COUNT = 7
+	K_PARSE = 7,
+	K_COUNT = 8
 };
 
 // Device state of the per-frame re-arm kernels (ebt_frontend.cu): the image
@@ -76,6 +78,8 @@ struct Frontend
 	float* d_pts = nullptr;                   // pts | next, lk_cap points each
 	unsigned char* d_status = nullptr;
 	float* h_pts = nullptr;  // pinned, same layout
+	double* d_land = nullptr;  // hand-off scratch: n x (2 in | 2 corner + 3 bearing) doubles + n ids
+	size_t land_cap = 0;
 	unsigned char* h_status = nullptr;
 	int lk_cap = 0;
 };
@@ -161,6 +165,16 @@ struct ebt_ctx
 	int64_t launches[K_COUNT] = {};
 
 	Frontend fe;
+
+	// event-text parser scratch (ebt_ingest.cu)
+	char* d_text = nullptr;
+	size_t text_cap = 0;
+	int* d_tile_counts = nullptr;
+	size_t tiles_cap = 0;
+	long long* d_total = nullptr;          // + error word behind it
+	long long* h_total = nullptr;          // pinned, 2 words
+	ebt_event* d_parsed = nullptr;
+	size_t parsed_cap = 0;
 };
 
 namespace
@@ -439,6 +453,11 @@ int ebt_destroy(ebt_ctx* ctx)
 	cudaFreeHost(ctx->h_stage);
 	cudaFreeHost(ctx->rec_stage);
 	cudaFreeHost(ctx->nrec_stage);
+	cudaFree(ctx->d_text);
+	cudaFree(ctx->d_tile_counts);
+	cudaFree(ctx->d_total);
+	cudaFreeHost(ctx->h_total);
+	cudaFree(ctx->d_parsed);
 	{
 		Frontend& fe = ctx->fe;
 		for (int l = 0; l < EBT_LK_MAX_LEVELS; ++l)
@@ -455,6 +474,7 @@ int ebt_destroy(ebt_ctx* ctx)
 		cudaFree(fe.cand);
 		cudaFree(fe.d_pts);
 		cudaFree(fe.d_status);
+		cudaFree(fe.d_land);
 		cudaFreeHost(fe.h_cand);
 		cudaFreeHost(fe.h_ncand);
 		cudaFreeHost(fe.h_pts);
@@ -685,6 +705,7 @@ size_t ebt_sizeof_problem(void) { return sizeof(ebt_problem); }
 size_t ebt_sizeof_solution(void) { return sizeof(ebt_solution); }
 size_t ebt_sizeof_params(void) { return sizeof(ebt_params); }
 size_t ebt_sizeof_frontend_params(void) { return sizeof(ebt_frontend_params); }
+size_t ebt_sizeof_camera(void) { return sizeof(ebt_camera); }
 int ebt_abi_version(void) { return 1; }
 
 int ebt_debug_phase_clocks(ebt_ctx* ctx, uint64_t* out8)
@@ -1640,6 +1661,217 @@ int ebt_new_image(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us)
 		}
 	}
 	return ebt_new_frame_end(ctx);
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Tracker -> VO hand-off
+// ---------------------------------------------------------------------------
+static int landScratch(ebt_ctx* ctx, size_t n)
+{
+	Frontend& fe = ctx->fe;
+	if (n <= fe.land_cap) return EBT_OK;
+	cudaFree(fe.d_land);
+	fe.d_land = nullptr;
+	fe.land_cap = 0;
+	const size_t cap = std::max<size_t>(n, 1024);
+	CU(cudaMalloc(&fe.d_land, cap * 8 * sizeof(double)));  // 2 in + 2 corner + 3 bearing + 1 (id)
+	fe.land_cap = cap;
+	return EBT_OK;
+}
+
+extern "C" {
+
+int ebt_get_landmarks(ebt_ctx* ctx, const ebt_camera* cam, int32_t* track_ids, double* cornersXY,
+					  double* bearingsXYZ, int cap, int* n_out)
+{
+	if (!ctx || !n_out || cap < 0 || (cap > 0 && (!track_ids || !cornersXY)) || (bearingsXYZ && !cam))
+		return fail(ctx, EBT_E_INVALID, "ebt_get_landmarks: bad argument");
+	const int n = static_cast<int>(ctx->h.size());
+	*n_out = n;
+	const int m = std::min(n, cap);
+	if (m == 0) return EBT_OK;
+	CU(cudaSetDevice(ctx->device));
+	int rc = uploadPatches(ctx);  // the device copy is the source
+	if (rc != EBT_OK) return rc;
+	rc = landScratch(ctx, static_cast<size_t>(m));
+	if (rc != EBT_OK) return rc;
+	double* d = ctx->fe.d_land;
+	const size_t M = static_cast<size_t>(m);
+	double* d_corner = d + 2 * ctx->fe.land_cap;
+	double* d_bear = d + 4 * ctx->fe.land_cap;
+	int* d_ids = reinterpret_cast<int*>(d + 7 * ctx->fe.land_cap);
+	ebt_camera c{};
+	if (cam) c = *cam;
+	CU(ebt_launch_unproject(ctx->d_patches, nullptr, m, c, bearingsXYZ ? 1 : 0, d_ids, d_corner, d_bear, ctx->stream));
+	CU(cudaMemcpyAsync(track_ids, d_ids, M * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaMemcpyAsync(cornersXY, d_corner, M * 2 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	if (bearingsXYZ) CU(cudaMemcpyAsync(bearingsXYZ, d_bear, M * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return EBT_OK;
+}
+
+int ebt_unproject(ebt_ctx* ctx, const ebt_camera* cam, const double* pointsXY, int n, double* bearingsXYZ)
+{
+	if (!ctx || !cam || n < 0 || (n > 0 && (!pointsXY || !bearingsXYZ)))
+		return fail(ctx, EBT_E_INVALID, "ebt_unproject: bad argument");
+	if (n == 0) return EBT_OK;
+	CU(cudaSetDevice(ctx->device));
+	const int rc = landScratch(ctx, static_cast<size_t>(n));
+	if (rc != EBT_OK) return rc;
+	double* d = ctx->fe.d_land;
+	double* d_bear = d + 4 * ctx->fe.land_cap;
+	const size_t N = static_cast<size_t>(n);
+	CU(cudaMemcpyAsync(d, pointsXY, N * 2 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	CU(ebt_launch_unproject(nullptr, d, n, *cam, 1, nullptr, nullptr, d_bear, ctx->stream));
+	CU(cudaMemcpyAsync(bearingsXYZ, d_bear, N * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return EBT_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Event ingestion: text parser on the device, Replayer order
+// ---------------------------------------------------------------------------
+extern "C" {
+
+int ebt_parse_events_text(ebt_ctx* ctx, const char* text, size_t len, int final_chunk, ebt_event* out,
+						  int64_t cap, int64_t* n_out, size_t* consumed)
+{
+	if (!ctx || !n_out || cap < 0 || (len > 0 && !text) || (cap > 0 && !out))
+		return fail(ctx, EBT_E_INVALID, "ebt_parse_events_text: bad argument");
+	*n_out = 0;
+	if (consumed) *consumed = 0;
+	if (len == 0) return EBT_OK;
+	if (len > (size_t(1) << 33))
+		return fail(ctx, EBT_E_INVALID, "ebt_parse_events_text: pass the text in chunks of at most 8 GiB");
+	CU(cudaSetDevice(ctx->device));
+	const size_t n_tiles = static_cast<size_t>(ebt_ingest_tiles(len));
+	if (len + 16 > ctx->text_cap)
+	{
+		cudaFree(ctx->d_text);
+		ctx->d_text = nullptr;
+		ctx->text_cap = 0;
+		CU(cudaMalloc(&ctx->d_text, len + len / 4 + 4096));
+		ctx->text_cap = len + len / 4 + 4096;
+	}
+	if (n_tiles > ctx->tiles_cap)
+	{
+		cudaFree(ctx->d_tile_counts);
+		ctx->d_tile_counts = nullptr;
+		ctx->tiles_cap = 0;
+		CU(cudaMalloc(&ctx->d_tile_counts, (n_tiles + n_tiles / 4 + 64) * sizeof(int)));
+		ctx->tiles_cap = n_tiles + n_tiles / 4 + 64;
+	}
+	if (!ctx->d_total)
+	{
+		CU(cudaMalloc(&ctx->d_total, 2 * sizeof(long long)));
+		CU(cudaHostAlloc(&ctx->h_total, 2 * sizeof(long long), cudaHostAllocDefault));
+	}
+	CU(cudaMemcpyAsync(ctx->d_text, text, len, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemsetAsync(ctx->d_total + 1, 0xff, sizeof(long long), ctx->stream));
+	tic(ctx);
+	CU(ebt_launch_count_lines(ctx->d_text, len, ctx->d_tile_counts, ctx->d_total, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->h_total, ctx->d_total, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	const long long newlines = ctx->h_total[0];
+	// a final chunk's last line needs no newline (std::getline); a non-final chunk's
+	// unterminated tail is left to the caller (*consumed)
+	const bool tail = final_chunk && text[len - 1] != '\n';
+	const long long n_lines = newlines + (tail ? 1 : 0);
+	*n_out = n_lines;
+	if (n_lines > cap)
+	{
+		toc(ctx, K_PARSE);
+		return fail(ctx, EBT_E_CAPACITY, "ebt_parse_events_text: " + std::to_string(n_lines) + " lines, output holds " +
+											 std::to_string(cap));
+	}
+	if (n_lines > 0)
+	{
+		if (static_cast<size_t>(n_lines) > ctx->parsed_cap)
+		{
+			cudaFree(ctx->d_parsed);
+			ctx->d_parsed = nullptr;
+			ctx->parsed_cap = 0;
+			const size_t c = static_cast<size_t>(n_lines) + static_cast<size_t>(n_lines) / 4 + 1024;
+			CU(cudaMalloc(&ctx->d_parsed, c * sizeof(ebt_event)));
+			ctx->parsed_cap = c;
+		}
+		CU(ebt_launch_parse_lines(ctx->d_text, len, ctx->d_tile_counts, n_lines, final_chunk ? 1 : 0, ctx->d_parsed,
+								  reinterpret_cast<unsigned long long*>(ctx->d_total + 1), ctx->stream));
+		toc(ctx, K_PARSE);
+		CU(cudaMemcpyAsync(ctx->h_total + 1, ctx->d_total + 1, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+		CU(cudaMemcpyAsync(out, ctx->d_parsed, static_cast<size_t>(n_lines) * sizeof(ebt_event), cudaMemcpyDeviceToHost,
+						   ctx->stream));
+		CU(cudaStreamSynchronize(ctx->stream));
+		const unsigned long long e = static_cast<unsigned long long>(ctx->h_total[1]);
+		if (e != ~0ull)
+		{
+			const unsigned code = static_cast<unsigned>(e & 0xff);
+			const char* why = code == 2   ? "timestamp has too many digits for an exact conversion (mantissa >= 2^53)"
+							  : code == 3 ? "line longer than 128 bytes"
+										  : "malformed line (expected \"t_sec x y p\" with p 0 or 1)";
+			*n_out = 0;
+			return fail(ctx, EBT_E_INVALID, "ebt_parse_events_text: line " + std::to_string(e >> 8) + ": " + why);
+		}
+	}
+	else
+		toc(ctx, K_PARSE);
+	if (consumed)
+	{
+		if (final_chunk)
+			*consumed = len;
+		else
+		{
+			size_t k = len;
+			while (k > 0 && text[k - 1] != '\n') --k;
+			*consumed = k;
+		}
+	}
+	return EBT_OK;
+}
+
+// tools::Replayer::next (tools/replayer/src/replayer.cpp:56-98) over in-memory
+// samples: an event is delivered while its timestamp is < the next image's,
+// otherwise the image; replay ends when either runs out (finished(), :40-43).
+int ebt_replay(ebt_ctx* ctx, const ebt_event* events, int64_t n_events, const uint8_t* frames,
+			   const int64_t* frame_ts, int n_frames, int64_t* n_events_delivered, int64_t* n_optimizations)
+{
+	if (!ctx || n_events < 0 || n_frames < 0 || (n_events > 0 && !events) || (n_frames > 0 && (!frames || !frame_ts)))
+		return fail(ctx, EBT_E_INVALID, "ebt_replay: bad argument");
+	if (n_events_delivered) *n_events_delivered = 0;
+	if (n_optimizations) *n_optimizations = 0;
+	const size_t npx = static_cast<size_t>(ctx->prm.width) * ctx->prm.height;
+	int64_t pos = 0, n_opt = 0;
+	for (int k = 0; k < n_frames && pos < n_events; ++k)
+	{
+		// events strictly older than image k
+		int64_t lo = pos, hi = n_events;
+		while (lo < hi)
+		{
+			const int64_t mid = lo + (hi - lo) / 2;
+			if (events[mid].t_us < frame_ts[k])
+				lo = mid + 1;
+			else
+				hi = mid;
+		}
+		if (lo > pos)
+		{
+			int64_t m = 0;
+			const int rc = ebt_push_events(ctx, events + pos, lo - pos, &m);
+			n_opt += m;
+			if (rc != EBT_OK) return rc;
+			pos = lo;
+		}
+		if (pos >= n_events) break;  // hasEvents_ is false before the image is reached
+		const int rc = ebt_new_image(ctx, frames + static_cast<size_t>(k) * npx, frame_ts[k]);
+		if (rc != EBT_OK) return rc;
+	}
+	if (n_events_delivered) *n_events_delivered = pos;
+	if (n_optimizations) *n_optimizations = n_opt;
+	return EBT_OK;
 }
 
 }  // extern "C"

@@ -17,6 +17,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "ebt_device_types.h"
 #include "ebt_frontend.h"
 
 namespace
@@ -339,6 +340,57 @@ lk_track_kernel(ebt_lk_pyramids pyr, const float* __restrict__ pts, int n_pts,
 		status[p] = ok ? 1 : 0;
 	}
 }
+// ---------------------------------------------------------------------------
+// Tracker -> VO hand-off: Keyframe landmarks (vo/src/keyframe.cpp:5-14) and
+// CameraModel::unproject (common/include/common/camera_model.h:79-114), one
+// thread per landmark, FP64, the reference's operation order without FMA
+// contraction.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ double tangential(double p1, double p2, double x, double y, double r2)
+{
+	// Scalar(2) * p1 * x * y + p2 * (r2 + Scalar(2) * x * x)
+	return __dadd_rn(__dmul_rn(__dmul_rn(__dmul_rn(2.0, p1), x), y),
+					 __dmul_rn(p2, __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, x), x))));
+}
+
+__global__ void unproject_kernel(const DevPatch* __restrict__ patches, const double* __restrict__ pts, int n,
+								 ebt_camera cam, int do_bearings, int* __restrict__ ids,
+								 double* __restrict__ corners, double* __restrict__ bearings)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	double x, y;
+	if (patches)
+	{
+		x = patches[i].rx + (EBT_PATCH_SIDE - 1) / 2.;  // Patch::toCorner
+		y = patches[i].ry + (EBT_PATCH_SIDE - 1) / 2.;
+		ids[i] = patches[i].track_id;
+		corners[2 * i] = x;
+		corners[2 * i + 1] = y;
+	}
+	else
+	{
+		x = pts[2 * i];
+		y = pts[2 * i + 1];
+	}
+	if (!do_bearings) return;
+	const double xd = __ddiv_rn(x - cam.cx, cam.fx), yd = __ddiv_rn(y - cam.cy, cam.fy);
+	double xo = xd, yo = yd;
+	for (int it = 0; it < 10; ++it)
+	{
+		const double r2 = __dadd_rn(__dmul_rn(xo, xo), __dmul_rn(yo, yo));
+		// 1 + k1 r2 + k2 r2 r2
+		const double radial = __dadd_rn(__dadd_rn(1.0, __dmul_rn(cam.k1, r2)), __dmul_rn(__dmul_rn(cam.k2, r2), r2));
+		const double dx = tangential(cam.p1, cam.p2, xo, yo, r2);
+		const double dy = tangential(cam.p2, cam.p1, yo, xo, r2);
+		xo = __ddiv_rn(xd - dx, radial);
+		yo = __ddiv_rn(yd - dy, radial);
+	}
+	const double norm = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(xo, xo), __dmul_rn(yo, yo)), 1.0));
+	bearings[3 * i] = __ddiv_rn(xo, norm);
+	bearings[3 * i + 1] = __ddiv_rn(yo, norm);
+	bearings[3 * i + 2] = __ddiv_rn(1.0, norm);
+}
 }  // namespace
 
 // ---------------------------------------------------------------------------
@@ -383,5 +435,14 @@ cudaError_t ebt_launch_lk(const ebt_lk_pyramids& pyr, const float* pts, int n, f
 {
 	if (n <= 0) return cudaSuccess;
 	lk_track_kernel<<<n, LK_THREADS, 0, stream>>>(pyr, pts, n, next_pts, status, max_count, eps * eps);
+	return cudaGetLastError();
+}
+
+cudaError_t ebt_launch_unproject(const DevPatch* patches, const double* pts, int n, const ebt_camera& cam,
+								 int do_bearings, int* ids, double* corners, double* bearings,
+								 cudaStream_t stream)
+{
+	if (n <= 0) return cudaSuccess;
+	unproject_kernel<<<(n + 127) / 128, 128, 0, stream>>>(patches, pts, n, cam, do_bearings, ids, corners, bearings);
 	return cudaGetLastError();
 }

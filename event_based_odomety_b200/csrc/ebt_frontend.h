@@ -31,3 +31,12 @@ cudaError_t ebt_launch_pyr_down(const unsigned char* src, int W, int H, unsigned
 cudaError_t ebt_launch_scharr(const unsigned char* src, int W, int H, short2* dst, cudaStream_t stream);
 cudaError_t ebt_launch_lk(const ebt_lk_pyramids& pyr, const float* pts, int n, float* next_pts,
 						  unsigned char* status, int max_count, double eps, cudaStream_t stream);
+
+// CameraModel::unproject (common/include/common/camera_model.h:79-114) for n points.
+// If patches != nullptr the points are the corners of patches[0..n) (Patch::toCorner) and
+// ids / corners receive the Keyframe landmarks; otherwise points come from pts.
+struct DevPatch;
+struct ebt_camera;
+cudaError_t ebt_launch_unproject(const DevPatch* patches, const double* pts, int n, const ebt_camera& cam,
+								 int do_bearings, int* ids, double* corners, double* bearings,
+								 cudaStream_t stream);

@@ -159,6 +159,20 @@ int ebt_get_patch(ebt_ctx* ctx, int32_t track_id, int which, double* out625);
  * with drawImages = false); 2: also at image time (drawImages = true). */
 int ebt_set_products(ebt_ctx* ctx, int mode);
 
+/* Tracker -> visual odometry hand-off.  For every live patch,
+ * in list order: the landmark visual_odometry::Keyframe::Keyframe stores
+ * (vo/src/keyframe.cpp:5-14: trackId -> Patch::toCorner()) and, when cam is
+ * not NULL, its bearing vector common::CameraModel::unproject(corner)
+ * (common/include/common/camera_model.h:79-114: 10 fixed-point iterations of the
+ * radial/tangential model, then normalisation), as the VO front end computes
+ * it per landmark (vo/src/visual_odometry.cpp:234, 367-369, 516-518).  Computed
+ * on the device from the resident patch state.  cornersXY: 2 doubles per patch,
+ * bearingsXYZ: 3 doubles per patch (may be NULL); *n_out = patches available. */
+int ebt_get_landmarks(ebt_ctx* ctx, const ebt_camera* cam, int32_t* track_ids, double* cornersXY,
+					  double* bearingsXYZ, int cap, int* n_out);
+/* CameraModel::unproject for n arbitrary pixel positions (same kernel). */
+int ebt_unproject(ebt_ctx* ctx, const ebt_camera* cam, const double* pointsXY, int n, double* bearingsXYZ);
+
 /* Patch::getTrajectory (patch.h:58): (x, y, t_us) triples. */
 int ebt_get_trajectory(ebt_ctx* ctx, int32_t track_id, double* out_xyt, int cap, int* n_out);
 
@@ -173,6 +187,28 @@ int ebt_clear_records(ebt_ctx* ctx);
 
 /* Latest frame's gradients (FeatureDetector::gradX_/gradY_), width*height each. */
 int ebt_get_gradients(ebt_ctx* ctx, double* gx, double* gy);
+
+/* ---- event ingestion ----------------------------------------
+ * tools::Davis240cReader::getEventSample (tools/dataset_reader/src/
+ * davis240c_reader.cpp:60-92) for a whole text buffer on the device: lines
+ * "t_sec x y p" -> ebt_event {t_us = (int64)(stod(t_sec) * 1e6), x, y,
+ * polarity = p ? +1 : -1}.  final_chunk = 0: an unterminated last line is
+ * left unparsed and *consumed (may be NULL) tells how many bytes were used, so
+ * a file can be streamed in chunks (the reference reads 1e6 lines at a time,
+ * :14); final_chunk = 1: the last line needs no newline (std::getline).
+ * *n_out = lines found (EBT_E_CAPACITY if > cap).  A malformed line, a sign
+ * other than 0/1 (the reference throws, :85-88) or a timestamp whose decimal
+ * mantissa is >= 2^53 is EBT_E_INVALID naming the line. */
+int ebt_parse_events_text(ebt_ctx* ctx, const char* text, size_t len, int final_chunk, ebt_event* out,
+						  int64_t cap, int64_t* n_out, size_t* consumed);
+
+/* tools::Replayer::next loop (tools/replayer/src/replayer.cpp:56-98) over
+ * in-memory samples: events older than the next image are delivered first
+ * (FeatureDetector::updatePatches), then the image (FeatureDetector::newImage,
+ * detector and LK on the device); ends when the events or the images run out.
+ * frames: n_frames x height x width uint8.  Events must be in time order. */
+int ebt_replay(ebt_ctx* ctx, const ebt_event* events, int64_t n_events, const uint8_t* frames,
+			   const int64_t* frame_ts, int n_frames, int64_t* n_events_delivered, int64_t* n_optimizations);
 
 /* ---- batched entry: F independent feature-patch problems ----------------
  * One Optimizer::optimize(Patch&) (optimizer.cpp:62-206) per problem.
@@ -201,7 +237,7 @@ int ebt_measure_fma_peak(ebt_ctx* ctx, double* fp64_tflops, double* fp32_tflops)
 /* Device-time of the kernels launched since ebt_timing_reset, measured with
  * CUDA events on the context stream: milliseconds and launch count per kernel
  * (0 stream kernel, 1 batched kernel, 2 gradient kernel, 3 window-size kernel,
- * 4 corner detector, 5 pyramid + Scharr, 6 LK tracker). */
+ * 4 corner detector, 5 pyramid + Scharr, 6 LK tracker, 7 event-text parser). */
 int ebt_timing_enable(ebt_ctx* ctx, int on);
 int ebt_timing_get(ebt_ctx* ctx, int kernel, double* ms_total, int64_t* launches);
 int ebt_timing_reset(ebt_ctx* ctx);
@@ -231,6 +267,7 @@ size_t ebt_sizeof_problem(void);
 size_t ebt_sizeof_solution(void);
 size_t ebt_sizeof_params(void);
 size_t ebt_sizeof_frontend_params(void);
+size_t ebt_sizeof_camera(void);
 int ebt_abi_version(void);
 
 #ifdef __cplusplus

@@ -98,6 +98,13 @@ typedef struct ebt_solution
 	int64_t ts;             /* int32((t_front+t_back)*0.5) */
 } ebt_solution;
 
+/* common::CameraModelParams<double> (common/include/common/camera_model.h:12-24),
+ * same field order (CameraModel::fromData reinterprets a double[9]). */
+typedef struct ebt_camera
+{
+	double fx, fy, cx, cy, k1, k2, k3, p1, p2;
+} ebt_camera;
+
 #ifdef __cplusplus
 }
 #endif

@@ -1398,3 +1398,48 @@ void oracle_cosf_sinf(const float* in, int n, float* c, float* s)
 		s[i] = sinf(in[i]);
 	}
 }
+
+/* ------------------------------------------------------------------------ */
+/* Tracker -> VO hand-off: common::CameraModel<double>::unproject            */
+/* (common/include/common/camera_model.h:79-114; getRadialDistortion :42-47, */
+/* getTangentialDistortion :35-40), built with -ffp-contract=off.            */
+/* ------------------------------------------------------------------------ */
+static double cam_tangential(double p1, double p2, double x, double y, double r2)
+{
+	return 2.0 * p1 * x * y + p2 * (r2 + 2.0 * x * x);
+}
+void oracle_unproject(const ebt_camera* cam, const double* xy, int n, double* out3)
+{
+	for (int i = 0; i < n; ++i)
+	{
+		const double xd = (xy[2 * i] - cam->cx) / cam->fx, yd = (xy[2 * i + 1] - cam->cy) / cam->fy;
+		double xo = xd, yo = yd;
+		for (int it = 0; it < 10; ++it)
+		{
+			const double r2 = xo * xo + yo * yo;
+			const double radial = 1.0 + cam->k1 * r2 + cam->k2 * r2 * r2;
+			const double dx = cam_tangential(cam->p1, cam->p2, xo, yo, r2);
+			const double dy = cam_tangential(cam->p2, cam->p1, yo, xo, r2);
+			xo = (xd - dx) / radial;
+			yo = (yd - dy) / radial;
+		}
+		const double norm = sqrt(xo * xo + yo * yo + 1.0);
+		out3[3 * i] = xo / norm;
+		out3[3 * i + 1] = yo / norm;
+		out3[3 * i + 2] = 1.0 / norm;
+	}
+}
+/* CameraModel::project (camera_model.h:49-77), for the reference's round-trip test */
+void oracle_project(const ebt_camera* cam, const double* xyz, int n, double* out2)
+{
+	for (int i = 0; i < n; ++i)
+	{
+		const double xp = xyz[3 * i] / xyz[3 * i + 2], yp = xyz[3 * i + 1] / xyz[3 * i + 2];
+		const double r2 = xp * xp + yp * yp;
+		const double radial = 1.0 + cam->k1 * r2 + cam->k2 * r2 * r2;
+		const double xD = xp * radial + cam_tangential(cam->p1, cam->p2, xp, yp, r2);
+		const double yD = yp * radial + cam_tangential(cam->p2, cam->p1, yp, xp, r2);
+		out2[2 * i] = cam->fx * xD + cam->cx;
+		out2[2 * i + 1] = cam->fy * yD + cam->cy;
+	}
+}

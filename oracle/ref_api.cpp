@@ -690,3 +690,31 @@ extern "C" int ref_patch_integrate(double cx, double cy, int extent,
 	}
 	return m.rows * m.cols;
 }
+
+// common::CameraModel<double> (common/include/common/camera_model.h), the
+// reference's own header: unproject / project for n points.
+#include <common/camera_model.h>
+extern "C" void ref_unproject(const ebt_camera* cam, const double* xy, int n, double* out3)
+{
+	common::CameraModelParams<double> p;
+	p.fx = cam->fx; p.fy = cam->fy; p.cx = cam->cx; p.cy = cam->cy;
+	p.k1 = cam->k1; p.k2 = cam->k2; p.k3 = cam->k3; p.p1 = cam->p1; p.p2 = cam->p2;
+	common::CameraModel<double> m(p);
+	for (int i = 0; i < n; ++i)
+	{
+		const Eigen::Vector3d b = m.unproject(Eigen::Vector2d(xy[2 * i], xy[2 * i + 1]));
+		out3[3 * i] = b[0]; out3[3 * i + 1] = b[1]; out3[3 * i + 2] = b[2];
+	}
+}
+extern "C" void ref_project(const ebt_camera* cam, const double* xyz, int n, double* out2)
+{
+	common::CameraModelParams<double> p;
+	p.fx = cam->fx; p.fy = cam->fy; p.cx = cam->cx; p.cy = cam->cy;
+	p.k1 = cam->k1; p.k2 = cam->k2; p.k3 = cam->k3; p.p1 = cam->p1; p.p2 = cam->p2;
+	common::CameraModel<double> m(p);
+	for (int i = 0; i < n; ++i)
+	{
+		const Eigen::Vector2d r = m.project(Eigen::Vector3d(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]));
+		out2[2 * i] = r[0]; out2[2 * i + 1] = r[1];
+	}
+}

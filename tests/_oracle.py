@@ -69,6 +69,8 @@ def _declare(dll, prefix):
         fn("create", _vp, C.c_int, C.c_int, C.c_int)
     fn("destroy", None, _vp)
     fn("set_draw_images", None, _vp, C.c_int)
+    fn("unproject", None, _vp, _vp, C.c_int, _vp)
+    fn("project", None, _vp, _vp, C.c_int, _vp)
     fn("new_frame_begin", C.c_int if prefix != "ref_" else None, _vp, _vp, C.c_int64, _vp, C.c_int)
     fn("get_uninit", C.c_int, _vp, _vp, _vp, C.c_int)
     fn("set_flow", None, _vp, C.c_int32, C.c_int, C.c_float, C.c_float)
@@ -219,3 +221,18 @@ class CpuBatch:
             secs = self.L.optimize_batch(self.f_, _ptr(problems), n, _ptr(events), _ptr(sol),
                                          _ptr(nabla), _ptr(evals))
         return sol, nabla, evals, secs
+
+
+def cpu_unproject(lib, camera, pts):
+    """CameraModel::unproject on the CPU checker; camera = cabi.Camera."""
+    pts = np.ascontiguousarray(pts, np.float64).reshape(-1, 2)
+    out = np.zeros((len(pts), 3))
+    lib.unproject(C.byref(camera), _ptr(pts), len(pts), _ptr(out))
+    return out
+
+
+def cpu_project(lib, camera, xyz):
+    xyz = np.ascontiguousarray(xyz, np.float64).reshape(-1, 3)
+    out = np.zeros((len(xyz), 2))
+    lib.project(C.byref(camera), _ptr(xyz), len(xyz), _ptr(out))
+    return out
