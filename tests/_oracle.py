@@ -236,3 +236,23 @@ def cpu_project(lib, camera, xyz):
     out = np.zeros((len(xyz), 2))
     lib.project(C.byref(camera), _ptr(xyz), len(xyz), _ptr(out))
     return out
+
+
+def load_ingest():
+    """oracle/libebt_ingest.so: C++ restatement of the reference's text event reader."""
+    so = os.path.join(ORACLE_DIR, "libebt_ingest.so")
+    src = os.path.join(ORACLE_DIR, "ingest_baseline.cpp")
+    if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", ORACLE_DIR, "oracle"], stdout=subprocess.DEVNULL)
+    dll = C.CDLL(so)
+    dll.ingest_parse_text.restype = C.c_int64
+    dll.ingest_parse_text.argtypes = [C.c_char_p, C.c_size_t, _vp, C.c_int64]
+    return dll
+
+
+def cpu_parse_text(dll, text: bytes):
+    out = np.zeros(text.count(b"\n") + 1, EVENT)
+    n = dll.ingest_parse_text(text, len(text), _ptr(out), len(out))
+    if n < 0:
+        raise ValueError("malformed event text")
+    return out[:n]

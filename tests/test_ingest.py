@@ -57,6 +57,18 @@ def test_restatement_on_reference_known_answer():
         io.parse_events_text(b"0.1 1 2 2\n")
 
 
+def test_cpp_restatement_equals_python_restatement():
+    from tests._oracle import cpu_parse_text, load_ingest
+    dll = load_ingest()
+    _check_reference_answer(cpu_parse_text(dll, REF_TEXT))
+    text = tricky_text(20_000, seed=5)
+    a, b = cpu_parse_text(dll, text), io.parse_events_text(text)
+    for k in ("t_us", "x", "y", "polarity"):
+        assert np.array_equal(a[k], b[k]), k
+    with pytest.raises(ValueError):
+        cpu_parse_text(dll, b"0.1 1 2 2\n")
+
+
 def test_replay_order_restatement():
     # event before image while t_ev < t_img; image first on a tie; stop when either runs out
     seq = io.replay_order([1, 2, 5, 5, 9, 12], [5, 9, 20, 30])
