@@ -57,6 +57,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--duration", type=float, default=0.30, help="stream seconds per step")
+    ap.add_argument("--streams", type=int, default=1,
+                    help="independent streams tracked concurrently per GPU (configs[3] throughput mode)")
     ap.add_argument("--cpu-frames", type=int, default=2, help="frames of the stream in the CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -215,6 +217,46 @@ def main_reference(args):
 # ---------------------------------------------------------------------------
 # Our arm
 # ---------------------------------------------------------------------------
+class Lane:
+    """One event stream of this rank: its tracker context (own CUDA stream), its
+    frames and events resident in HBM and in pinned host memory."""
+
+    def __init__(self, torch, Tracker, wl, duration, seed, device):
+        w, h, feat, rate, _ = wl
+        self.S = S = synth.make_stream(w, h, duration, rate, seed, max_corners=feat)
+        self.nF = len(S.frames)
+        t = S.events["t_us"]
+        self.bounds = [(int(np.searchsorted(t, S.frame_ts[k], "left")),
+                        int(np.searchsorted(t, S.frame_ts[k + 1], "left")) if k + 1 < self.nF else len(S.events))
+                       for k in range(self.nF)]
+        self.n_events = self.bounds[-1][1] - self.bounds[0][0]
+        self.tr = Tracker(w, h, feat, device=device, record_capacity=1 << 20)
+        self.flows = FlowCache(S)
+        ev_bytes = torch.from_numpy(S.events.view(np.uint8).reshape(-1).copy())
+        self.d_events = ev_bytes.cuda()
+        self.h_events = ev_bytes.pin_memory()
+        self.d_frames = [torch.from_numpy(f.copy()).cuda() for f in S.frames]
+
+    def frame_dev(self, k):
+        self.tr.new_frame_begin_device(self.d_frames[k].data_ptr(), self.S.frame_ts[k], self.S.corners[k])
+
+    def frame_host(self, k):
+        self.tr.new_frame_begin(self.S.frames[k], self.S.frame_ts[k], self.S.corners[k])
+
+    def push_dev(self, k):
+        lo, hi = self.bounds[k]
+        return self.tr.push_events_device(self.d_events.data_ptr() + lo * 16, hi - lo)
+
+    def push_host(self, k):
+        lo, hi = self.bounds[k]
+        return self.tr.push_events_ptr(self.h_events.data_ptr() + lo * 16, hi - lo)
+
+    def step(self, host):
+        self.tr.reset()
+        return run_step(self.tr, self.S, self.flows, self.frame_host if host else self.frame_dev,
+                        self.push_host if host else self.push_dev, self.nF)
+
+
 def main_ours(args):
     import torch
     import torch.distributed as dist
@@ -229,58 +271,59 @@ def main_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    w, h, feat, rate, seed = WORKLOADS[args.workload]
-    # rank 0 tracks the named stream; further ranks track independent streams
-    # of the same shape (configs[3], seeds 2000 + rank)
-    S = synth.make_stream(w, h, args.duration, rate, multi.stream_seed(seed, rank), max_corners=feat)
-    nF = len(S.frames)
-    bounds = [(int(np.searchsorted(S.events["t_us"], S.frame_ts[k], "left")),
-               int(np.searchsorted(S.events["t_us"], S.frame_ts[k + 1], "left")) if k + 1 < nF else len(S.events))
-              for k in range(nF)]
-    n_events = bounds[-1][1] - bounds[0][0]
-    tr = Tracker(w, h, feat, device=local, record_capacity=1 << 20)
+    wl = WORKLOADS[args.workload]
+    w, h, feat, rate, seed = wl
+    # global stream g = rank * streams + lane; stream 0 is the named stream, every
+    # further one an independent stream of the same shape (configs[3], seeds 2000 + g)
+    nS = max(1, args.streams)
+    lanes = [Lane(torch, Tracker, wl, args.duration, multi.stream_seed(seed, rank * nS + s), local)
+             for s in range(nS)]
+    L0 = lanes[0]
+    S, nF, tr = L0.S, L0.nF, L0.tr
+    n_events = sum(L.n_events for L in lanes)
     fp64_peak, fp32_peak = tr.measure_fma_peak()
-    flows = FlowCache(S)
-
-    ev_bytes = torch.from_numpy(S.events.view(np.uint8).reshape(-1).copy())
-    d_events = ev_bytes.cuda()
-    h_events = ev_bytes.pin_memory()
-    d_frames = [torch.from_numpy(f.copy()).cuda() for f in S.frames]
+    # L2 flush between steps: 256 MB (> the 126 MB L2) rewritten at the start of
+    # every step, inside the timed region (~0.05 ms)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     torch.cuda.synchronize()
-
-    def frame_dev(k):
-        tr.new_frame_begin_device(d_frames[k].data_ptr(), S.frame_ts[k], S.corners[k])
-
-    def frame_host(k):
-        tr.new_frame_begin(S.frames[k], S.frame_ts[k], S.corners[k])
-
-    def push_dev(k):
-        lo, hi = bounds[k]
-        return tr.push_events_device(d_events.data_ptr() + lo * 16, hi - lo)
-
-    def push_host(k):
-        lo, hi = bounds[k]
-        return tr.push_events_ptr(h_events.data_ptr() + lo * 16, hi - lo)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(frame_fn, push_fn, steps, with_timing):
+    def all_lanes(host):
+        """One step of every stream of this rank; streams run concurrently, one
+        host thread and one CUDA stream each (ctypes releases the GIL)."""
+        if nS == 1:
+            return L0.step(host)
+        out = [0] * nS
+
+        def work(i):
+            out[i] = lanes[i].step(host)
+        th = [threading.Thread(target=work, args=(i,)) for i in range(nS)]
+        [x.start() for x in th]
+        [x.join() for x in th]
+        return sum(out)
+
+    def timed(host, steps, with_timing):
         """K steps bracketed by barrier + synchronize; device time by CUDA events
         (the library syncs its own stream inside every call, so the events on
         the current stream bracket all of its work)."""
         barrier()
-        if with_timing:
+        if with_timing and nS == 1:
+            # per-kernel CUDA events on the library stream; with several streams per
+            # GPU the kernels overlap and the events would serialise them, so the
+            # launch counts are then taken from one extra untimed step below
             tr.timing(True)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         t0 = time.perf_counter()
         opts = 0
         for _ in range(steps):
-            tr.reset()
-            opts += run_step(tr, S, flows, frame_fn, push_fn, nF)
+            flush.zero_()
+            torch.cuda.current_stream().synchronize()
+            opts += all_lanes(host)
         e1.record()
         barrier()
         wall = time.perf_counter() - t0
@@ -288,21 +331,29 @@ def main_ours(args):
         return opts, max(ms * 1e-3, wall if ms <= 0 else 0.0), wall
 
     for _ in range(max(args.warmup, 0)):
-        tr.reset()
-        run_step(tr, S, flows, frame_dev, push_dev, nF)
+        flush.zero_()  # also loads torch's fill kernel outside the timed region
+        all_lanes(False)
     sampler = ClockSampler(local)
     sampler.start()
-    opts, secs, wall = timed(frame_dev, push_dev, args.steps, True)
-    kt_ms, kt_n = tr.timing_get(K_TRACK)
-    kg_ms, kg_n = tr.timing_get(K_GRAD)
-    kn_ms, kn_n = tr.timing_get(K_NUMEV)
-    rec = tr.records()  # records of the last step
-    tr.timing(False)
-    tr.reset()
-    run_step(tr, S, flows, frame_host, push_host, nF)  # e2e warm-up
-    e_opts, e_secs, _ = timed(frame_host, push_host, args.steps, False)
+    opts, secs, wall = timed(False, args.steps, True)
+    kt_ms = kt_n = kg_ms = kg_n = kn_ms = kn_n = 0
+    for L in lanes:
+        a, b = L.tr.timing_get(K_TRACK); kt_ms += a; kt_n += b
+        a, b = L.tr.timing_get(K_GRAD); kg_ms += a; kg_n += b
+        a, b = L.tr.timing_get(K_NUMEV); kn_ms += a; kn_n += b
+    flops_step = sum(lm_flops(L.tr.records()) for L in lanes)  # records of the last step
+    if nS > 1:
+        for L in lanes:
+            L.tr.timing(True)
+        all_lanes(False)
+        kt_n, kg_n, kn_n = (args.steps * sum(L.tr.timing_get(k)[1] for L in lanes) for k in (K_TRACK, K_GRAD, K_NUMEV))
+        kg_ms, kn_ms = (args.steps * sum(L.tr.timing_get(k)[0] for L in lanes) for k in (K_GRAD, K_NUMEV))
+    for L in lanes:
+        L.tr.timing(False)
+    all_lanes(True)  # e2e warm-up
+    e_opts, e_secs, _ = timed(True, args.steps, False)
     clocks = sampler.result()
-    n_tracks = len(tr.tracks()) + len(tr.tracks(True))
+    n_tracks = sum(len(L.tr.tracks()) + len(L.tr.tracks(True)) for L in lanes)
 
     # whole-job aggregate: sum of units over ranks / max time over ranks
     def agg(units, seconds):
@@ -314,8 +365,9 @@ def main_ours(args):
 
     if rank == 0:
         opts_step = opts / args.steps
-        flops_step = lm_flops(rec)
-        kt_s = kt_ms * 1e-3 / args.steps  # stream-kernel time per step
+        # stream-kernel time per step; with several streams per GPU their kernels
+        # overlap, so the kernel's time is the step itself
+        kt_s = kt_ms * 1e-3 / args.steps if nS == 1 else secs / args.steps
         achieved = flops_step / kt_s / 1e12 if kt_s > 0 else 0.0
         hbm_bytes = 16.0 * n_events + (2500.0 + 128.0) * opts_step
         peaks = {}
@@ -331,6 +383,11 @@ def main_ours(args):
         except Exception:
             pass
         launches_step = kt_n / args.steps
+        if world > 1 or nS > 1:
+            sharding = (f"{nS} independent stream(s) per GPU (one context + CUDA stream + host thread each), "
+                        f"{world} GPU(s), no collective")
+        else:
+            sharding = "single stream"
         line = {
             "metric": METRIC, "value": g_opts / g_secs, "unit": "optimisations/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -339,18 +396,22 @@ def main_ours(args):
             "config": {
                 "workload": workload_name(args.workload),
                 "segment": f"{args.duration:g} s = {nF} frames, {n_events} events, {int(opts_step)} optimisations, "
-                           f"{n_tracks} tracks per step",
-                "sharding": "one independent stream per GPU, no collective" if world > 1 else "single stream",
-                "l2": "each step re-reads its whole event stream (%.1f MB) and all template grids; inputs are "
-                      "not larger than L2, the kernel is FP64-pipe bound (see roofline)" % (n_events * 16 / 1e6),
+                           f"{n_tracks} tracks per step" + (f" over {nS} streams" if nS > 1 else ""),
+                "sharding": sharding,
+                "l2": "flushed: a 256 MB buffer (> 126 MB L2) is rewritten at the start of every step, inside the "
+                      "timed region; a step then reads its event stream (%.1f MB) and template grids from HBM once, "
+                      "the kernel is FP64-pipe bound (see roofline)" % (n_events * 16 / 1e6),
             },
             "events_per_s": g_events / g_secs,
             "e2e": {"value": ge_opts / ge_secs, "unit": "optimisations/s",
-                    "h2d_bytes_per_step": int(n_events * 16 + nF * w * h + 8 * sum(len(c) * 2 for c in S.corners)),
-                    "d2h_bytes_per_step": int(opts_step * OPT_RECORD.itemsize + 2 * nF * feat * 216)},
+                    "h2d_bytes_per_step": int(n_events * 16 + sum(
+                        L.nF * w * h + 8 * sum(len(c) * 2 for c in L.S.corners) for L in lanes)),
+                    "d2h_bytes_per_step": int(opts_step * OPT_RECORD.itemsize + 2 * nF * feat * 216 * nS)},
             # every push launches prefilter_kernel + track_batch_kernel
             "gpu_launches": int(2 * kt_n + kg_n + kn_n),
-            "roofline": {"bound": "fp64", "kernel": "track_batch_kernel (timed with its prefilter_kernel, 1.4 % of it)",
+            "roofline": {"bound": "fp64",
+                         "kernel": "track_batch_kernel (timed with its prefilter_kernel, 1.4 % of it)" if nS == 1 else
+                         f"track_batch_kernel of {nS} concurrent streams (kernels overlap: time = the step)",
                          "achieved": achieved,
                          "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
                          "traffic": traffic, "traffic_unit": "DRAM bytes per launch (ncu --set full, profiles/r1_ncu_metrics.json)",
@@ -378,7 +439,8 @@ def main_ours(args):
                 "sample": f"first {cf} frames + event batches of the same stream ({ne} events, {n} optimisations, "
                           f"{dt:.1f} s), single thread as the reference runs it"}
         print(json.dumps(line))
-    tr.close()
+    for L in lanes:
+        L.tr.close()
     if world > 1:
         dist.destroy_process_group()
 

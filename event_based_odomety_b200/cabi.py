@@ -71,6 +71,9 @@ EXPORTS = {
     "ebt_get_tracks": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "ebt_get_patch": (C.c_int, [_vp, C.c_int32, C.c_int, _vp]),
     "ebt_set_products": (C.c_int, [_vp, C.c_int]),
+    "ebt_set_cost_map": (C.c_int, [_vp, C.c_int]),
+    "ebt_get_cost_map": (C.c_int, [_vp, C.c_int32, _vp]),
+    "ebt_get_batch_cost_maps": (C.c_int, [_vp, _vp, C.c_int64]),
     "ebt_get_landmarks": (C.c_int, [_vp, C.POINTER(Camera), _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]),
     "ebt_unproject": (C.c_int, [_vp, C.POINTER(Camera), _vp, C.c_int, _vp]),
     "ebt_get_trajectory": (C.c_int, [_vp, C.c_int32, _vp, C.c_int, C.POINTER(C.c_int)]),
@@ -324,6 +327,21 @@ class Tracker:
 
     def set_products(self, mode):
         self._ck(self.lib.ebt_set_products(self.ctx, int(mode)))
+
+    def set_cost_map(self, on=True):
+        """OptimizerParams::drawCostMap."""
+        self._ck(self.lib.ebt_set_cost_map(self.ctx, int(on)))
+
+    def cost_map(self, track_id):
+        """Patch::getCostMap(): 11x11."""
+        out = np.zeros((11, 11), np.float64)
+        self._ck(self.lib.ebt_get_cost_map(self.ctx, int(track_id), _ptr(out)))
+        return out
+
+    def batch_cost_maps(self, n):
+        out = np.zeros((int(n), 11, 11), np.float64)
+        self._ck(self.lib.ebt_get_batch_cost_maps(self.ctx, _ptr(out), int(n)))
+        return out
 
     def trajectory(self, track_id):
         n = C.c_int()

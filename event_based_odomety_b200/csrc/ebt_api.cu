@@ -110,6 +110,7 @@ struct ebt_ctx
 	std::vector<std::vector<int>> arch_nabla;
 	std::vector<std::vector<int>> arch_mc;       // products on: motionCompensatedIntegratedNabla_
 	std::vector<std::vector<double>> arch_pred;  // products on: predictedNabla_
+	std::vector<std::vector<double>> arch_cost;  // cost map on: costMap_ (121)
 	std::vector<int> free_slots;
 	bool host_dirty = true;  // h holds changes the device has not seen
 	int next_track_id = 0;
@@ -122,6 +123,9 @@ struct ebt_ctx
 	int* d_nablas = nullptr;
 	int* d_mc_nablas = nullptr;       // allocated by ebt_set_products
 	double* d_pred_nablas = nullptr;
+	double* d_cost_maps = nullptr;    // allocated by ebt_set_cost_map: [store_slot][121]
+	double* d_bcost = nullptr;        // cost maps of the last batched solve: [problem][121]
+	size_t cap_bcost = 0, n_bcost = 0;
 	ebt_opt_record* d_records = nullptr;
 	unsigned long long* d_nrec = nullptr;
 	std::vector<ebt_opt_record> records;
@@ -438,6 +442,8 @@ int ebt_destroy(ebt_ctx* ctx)
 	cudaFree(ctx->d_nablas);
 	cudaFree(ctx->d_mc_nablas);
 	cudaFree(ctx->d_pred_nablas);
+	cudaFree(ctx->d_cost_maps);
+	cudaFree(ctx->d_bcost);
 	cudaFree(ctx->d_records);
 	cudaFree(ctx->d_nrec);
 	cudaFree(ctx->d_events);
@@ -538,6 +544,7 @@ int ebt_create(const ebt_params* params, int device, ebt_ctx** out)
 	d.pad_ = 0;
 	d.mc_nablas = nullptr;
 	d.pred_nablas = nullptr;
+	d.cost_maps = nullptr;
 
 	ctx = c;
 	const size_t P = static_cast<size_t>(params->max_patches);
@@ -608,6 +615,7 @@ int ebt_reset(ebt_ctx* ctx)
 	ctx->arch_nabla.clear();
 	ctx->arch_mc.clear();
 	ctx->arch_pred.clear();
+	ctx->arch_cost.clear();
 	ctx->records.clear();
 	ctx->records_sorted = 0;
 	ctx->record_batches.clear();
@@ -622,6 +630,9 @@ int ebt_reset(ebt_ctx* ctx)
 	ctx->fe.built[0] = ctx->fe.built[1] = 0;
 	CU(cudaMemsetAsync(ctx->d_nablas, 0,
 					   static_cast<size_t>(ctx->prm.max_patches) * EBT_PATCH_PIXELS * sizeof(int), ctx->stream));
+	if (ctx->d_cost_maps)
+		CU(cudaMemsetAsync(ctx->d_cost_maps, 0, static_cast<size_t>(ctx->prm.max_patches) * 121 * sizeof(double),
+						   ctx->stream));
 	if (ctx->d_mc_nablas)
 	{
 		CU(cudaMemsetAsync(ctx->d_mc_nablas, 0,
@@ -934,6 +945,16 @@ int ebt_new_frame_end(ebt_ctx* ctx)
 				ctx->arch_mc.emplace_back();
 				ctx->arch_pred.emplace_back();
 			}
+			if (ctx->dp.cost_maps)
+			{
+				const size_t off = static_cast<size_t>(ctx->h[i].store_slot) * 121;
+				std::vector<double> cm(121);
+				CU(cudaMemcpy(cm.data(), ctx->d_cost_maps + off, 121 * sizeof(double), cudaMemcpyDeviceToHost));
+				CU(cudaMemset(ctx->d_cost_maps + off, 0, 121 * sizeof(double)));
+				ctx->arch_cost.push_back(std::move(cm));
+			}
+			else
+				ctx->arch_cost.emplace_back();
 			ctx->arch.push_back(ctx->h[i]);
 			ctx->arch_nabla.push_back(std::move(nab));
 			ctx->free_slots.push_back(ctx->h[i].store_slot);
@@ -1174,6 +1195,62 @@ int ebt_set_products(ebt_ctx* ctx, int mode)
 	return EBT_OK;
 }
 
+// OptimizerParams::drawCostMap (optimizer.h:18): Optimizer::drawCostMap
+// (optimizer.cpp:32-60) after every optimisation that follows.
+int ebt_set_cost_map(ebt_ctx* ctx, int on)
+{
+	if (!ctx) return fail(ctx, EBT_E_INVALID, "ebt_set_cost_map: bad argument");
+	CU(cudaSetDevice(ctx->device));
+	if (on && !ctx->d_cost_maps)
+	{
+		const size_t n = static_cast<size_t>(ctx->prm.max_patches) * 121;
+		CU(cudaMalloc(&ctx->d_cost_maps, n * sizeof(double)));
+		CU(cudaMemset(ctx->d_cost_maps, 0, n * sizeof(double)));
+	}
+	ctx->dp.cost_maps = on ? ctx->d_cost_maps : nullptr;
+	return EBT_OK;
+}
+
+// Patch::getCostMap (patch.h:56): 11x11 row-major, map(y + 5, x + 5); zeros
+// until the patch was optimised with the cost map on (the reference holds
+// zeros(1, 1) then, patch.cpp:29).
+int ebt_get_cost_map(ebt_ctx* ctx, int32_t track_id, double* out121)
+{
+	if (!ctx || !out121) return fail(ctx, EBT_E_INVALID, "ebt_get_cost_map: bad argument");
+	if (!ctx->d_cost_maps)
+		return fail(ctx, EBT_E_INVALID, "ebt_get_cost_map: not computed; enable it with ebt_set_cost_map");
+	const DevPatch* p = nullptr;
+	int ai = -1;
+	if (!findTrack(ctx, track_id, &p, &ai)) return fail(ctx, EBT_E_INVALID, "ebt_get_cost_map: unknown track id");
+	if (ai >= 0)
+	{
+		const std::vector<double>& src = ctx->arch_cost[static_cast<size_t>(ai)];
+		if (src.empty())
+			std::memset(out121, 0, 121 * sizeof(double));
+		else
+			std::memcpy(out121, src.data(), 121 * sizeof(double));
+		return EBT_OK;
+	}
+	CU(cudaSetDevice(ctx->device));
+	CU(cudaStreamSynchronize(ctx->stream));
+	CU(cudaMemcpy(out121, ctx->d_cost_maps + static_cast<size_t>(p->store_slot) * 121, 121 * sizeof(double),
+				  cudaMemcpyDeviceToHost));
+	return EBT_OK;
+}
+
+// Cost maps of the problems of the last ebt_optimize_batch / _device call made
+// with the cost map on: n x 121 doubles.
+int ebt_get_batch_cost_maps(ebt_ctx* ctx, double* out, int64_t n)
+{
+	if (!ctx || !out || n < 0) return fail(ctx, EBT_E_INVALID, "ebt_get_batch_cost_maps: bad argument");
+	if (static_cast<size_t>(n) > ctx->n_bcost)
+		return fail(ctx, EBT_E_INVALID, "ebt_get_batch_cost_maps: the last batched solve produced fewer cost maps");
+	CU(cudaSetDevice(ctx->device));
+	CU(cudaStreamSynchronize(ctx->stream));
+	CU(cudaMemcpy(out, ctx->d_bcost, static_cast<size_t>(n) * 121 * sizeof(double), cudaMemcpyDeviceToHost));
+	return EBT_OK;
+}
+
 int ebt_get_trajectory(ebt_ctx* ctx, int32_t track_id, double* out_xyt, int cap, int* n_out)
 {
 	if (!ctx || !n_out) return fail(ctx, EBT_E_INVALID, "ebt_get_trajectory: bad argument");
@@ -1271,9 +1348,28 @@ int ebt_optimize_batch_device(ebt_ctx* ctx, const ebt_problem* d_problems, int64
 	if (!ctx || n_problems < 0 || n_problems > INT32_MAX || (n_problems > 0 && (!d_problems || !d_events || !d_solutions)))
 		return fail(ctx, EBT_E_INVALID, "ebt_optimize_batch_device: bad argument");
 	CU(cudaSetDevice(ctx->device));
+	DevParams dp = ctx->dp;
+	ctx->n_bcost = 0;
+	if (dp.cost_maps)
+	{
+		// the batched kernel indexes its cost maps by problem, not by store slot
+		const size_t need = static_cast<size_t>(n_problems) * 121;
+		if (need > ctx->cap_bcost)
+		{
+			CU(cudaStreamSynchronize(ctx->stream));
+			cudaFree(ctx->d_bcost);
+			ctx->d_bcost = nullptr;
+			ctx->cap_bcost = 0;
+			CU(cudaMalloc(&ctx->d_bcost, need * sizeof(double)));
+			ctx->cap_bcost = need;
+		}
+		CU(cudaMemsetAsync(ctx->d_bcost, 0, need * sizeof(double), ctx->stream));
+		dp.cost_maps = ctx->d_bcost;
+		ctx->n_bcost = static_cast<size_t>(n_problems);
+	}
 	tic(ctx);
 	CU(ebt_launch_optimize_batch(d_problems, static_cast<int>(n_problems), d_events, frameTable(ctx),
-								 ctx->dp, d_solutions, d_nabla, ctx->stream));
+								 dp, d_solutions, d_nabla, ctx->stream));
 	toc(ctx, K_BATCH);
 	return EBT_OK;
 }

@@ -68,6 +68,9 @@ struct DevParams
 	int pad_;
 	int* mc_nablas;       // [store_slot][625] Patch::motionCompensatedIntegratedNabla_
 	double* pred_nablas;  // [store_slot][625] Patch::predictedNabla_
+	// OptimizerParams::drawCostMap (ebt_set_cost_map): null = off; stream kernel
+	// [store_slot][121], batched kernel [problem][121] = Patch::costMap_ (11x11)
+	double* cost_maps;
 };
 
 // Gradient grids of the live template frames: interleaved (gx, gy) doubles,

@@ -259,6 +259,76 @@ __device__ __forceinline__ void sample_taps(const double2* __restrict__ grid, in
 	}
 }
 
+#ifndef EBT_PIX_ILP
+#define EBT_PIX_ILP 1  // pixels evaluated side by side per loop trip (1 or 2)
+#endif
+
+// Per-pixel terms of one evaluation, straight-line (no branches): the taps are
+// always addressed through clamped indices, so an out-of-image pixel computes
+// harmless values and is dropped by `valid`.  Same arithmetic, in the same
+// order, as the branching form below => bit-identical sums.
+template <bool JAC>
+struct PixTerms
+{
+	double u, mi, du[4];
+	bool valid;
+};
+
+template <bool JAC>
+__device__ __forceinline__ void pixel_terms(const double2* __restrict__ grid, int W, int H, double cs,
+											 double sn, double tx, double ty, double vx, double vy,
+											 double tlx, double tly, const double* m, int i,
+											 PixTerms<JAC>& T)
+{
+	const int yy = i / SIDE, xx = i - yy * SIDE;
+	const double px = xx + tlx, py = yy + tly;
+	const double wx = cs * px + -sn * py + tx;
+	const double wy = sn * px + cs * py + ty;
+	T.valid = !(wx >= W || wy >= H || wx < 0.0 || wy < 0.0);
+	// keep the index arithmetic in range for pixels that are dropped anyway
+	const double wxc = fmin(fmax(wx, -4.0), (double)W + 4.0), wyc = fmin(fmax(wy, -4.0), (double)H + 4.0);
+	const double fr = floor(wyc), fc = floor(wxc);
+	const int row = (int)fr, col = (int)fc;
+	double wr[4], dr[4], wc[4], dc[4];
+	cr_weights<JAC>(wy - fr, wr, dr);
+	cr_weights<JAC>(wx - fc, wc, dc);
+	double g0, g1, gr0, gr1, gc0, gc1;
+	sample_taps<JAC, false>(grid, W, H, row, col, wr, dr, wc, dc, g0, g1, gr0, gr1, gc0, gc1);
+	T.u = g0 * vx + g1 * vy;
+	T.mi = m[i];
+	if (JAC)
+	{
+		const double ux = gc0 * vx + gc1 * vy;  // du/dW.x
+		const double uy = gr0 * vx + gr1 * vy;  // du/dW.y
+		T.du[0] = ux * cs + uy * sn;
+		T.du[1] = -ux * sn + uy * cs;
+		T.du[2] = ux * (-cs * py - sn * px) + uy * (-sn * py + cs * px);
+		T.du[3] = -g0 * vy + g1 * vx;
+	}
+}
+
+template <bool JAC>
+__device__ __forceinline__ void pixel_accumulate(const PixTerms<JAC>& T, double (&acc)[JAC ? 20 : 2])
+{
+	if (!T.valid) return;
+	acc[0] += T.u * T.u;
+	acc[1] += T.u * T.mi;
+	if (JAC)
+	{
+#pragma unroll
+		for (int q = 0; q < 4; ++q)
+		{
+			acc[2 + q] += T.u * T.du[q];
+			acc[6 + q] += T.du[q] * T.mi;
+		}
+		int k = 10;
+#pragma unroll
+		for (int q = 0; q < 4; ++q)
+#pragma unroll
+			for (int p = q; p < 4; ++p) acc[k++] += T.du[q] * T.du[p];
+	}
+}
+
 template <bool JAC>
 __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, int W, int H,
 											 const double (&x)[5], double vx, double vy,
@@ -268,6 +338,21 @@ __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, in
 	const double cs = x[0], sn = x[1], tx = x[2], ty = x[3];
 #pragma unroll
 	for (int k = 0; k < (JAC ? 20 : 2); ++k) acc[k] = 0.0;
+#if EBT_PIX_ILP == 2
+	// two pixels per trip, evaluated side by side (independent dependency
+	// chains for the FP64 pipe), accumulated in pixel order
+#pragma unroll 1
+	for (int i = threadIdx.x; i < NPIX; i += 2 * NT)
+	{
+		PixTerms<JAC> A, B;
+		const int iB = i + NT;
+		pixel_terms<JAC>(grid, W, H, cs, sn, tx, ty, vx, vy, tlx, tly, m, i, A);
+		pixel_terms<JAC>(grid, W, H, cs, sn, tx, ty, vx, vy, tlx, tly, m, min(iB, NPIX - 1), B);
+		B.valid = B.valid && iB < NPIX;
+		pixel_accumulate<JAC>(A, acc);
+		pixel_accumulate<JAC>(B, acc);
+	}
+#else
 #pragma unroll kPixUnroll
 	for (int i = threadIdx.x; i < NPIX; i += NT)
 	{
@@ -312,6 +397,7 @@ __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, in
 				for (int p = q; p < 4; ++p) acc[k++] += du[q] * du[p];
 		}
 	}
+#endif
 }
 
 // HuberLoss::Evaluate (ceres/internal/ceres/loss_function.cc:48-62) on the
@@ -1040,10 +1126,46 @@ __device__ __forceinline__ void update_rect(FeatState& st)
 	st.ry = ncy - EBT_PATCH_EXTENT;
 }
 
+// Optimizer::drawCostMap (ft/src/optimizer.cpp:32-60), run at the end of
+// optimize() when OptimizerParams::drawCostMap is set: the solve's functor (old
+// rect, normalised patch: still in sh.ctx / sh.m) on the 11x11 grid of integer
+// translation offsets around the solved warp.  The pose is rebuilt from its
+// angle (Pose2d(pose.log().z(), t): SO2::log = atan2, SO2(theta) = (cos, sin)),
+// the flow is the float getFlow(); map(y + 5, x + 5) = cv::norm(residuals, L2)
+// = sqrt(sum (u_i / sqrt(N) + m_i)^2), N = 1e-5 + sum u^2, from the two reduced
+// sums of a cost-only pixel pass.  121 passes: a diagnostic, off by default.
+__device__ __noinline__ void cost_map(FeatShared& sh, double w0, double w1, double w2, double w3, double flow,
+									   double* __restrict__ out)
+{
+	const EvalCtx E = sh.ctx;
+	const double theta = atan2(w1, w0);
+	double x[5];
+	sincos(theta, &x[1], &x[0]);
+	x[4] = (double)__double2float_rn(flow);
+	double vx, vy;
+	sincos(x[4], &vy, &vx);
+	for (int k = 0; k < 121; ++k)
+	{
+		const int ox = k / 11 - 5, oy = k % 11 - 5;
+		x[2] = (double)ox + w2;
+		x[3] = (double)oy + w3;
+		double acc[2];
+		eval_pixels<false>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, acc);
+		block_sum<2>(sh, acc);
+		if (threadIdx.x == 0)
+		{
+			const double N = 1e-5 + acc[0];
+			const double s = acc[0] / N + 2.0 * acc[1] / sqrt(N) + E.smm;
+			out[(oy + 5) * 11 + (ox + 5)] = sqrt(fmax(s, 0.0));
+		}
+	}
+}
+
 // One Optimizer::optimize (ft/src/optimizer.cpp:62-206): integrate, normalise,
-// LM solve, cost filter, state update.
+// LM solve, cost filter, state update; cm_out != null: the cost map.
 __device__ EBT_NOINLINE void optimize_feature(FeatShared& sh, double* costs, FeatState& st,
-								 const FrameTable& ft, const DevParams& P, LmSummary& S)
+								 const FrameTable& ft, const DevParams& P, LmSummary& S,
+								 double* cm_out = nullptr)
 {
 	S.filtered = 0;
 	integrate_window(sh, st);
@@ -1147,6 +1269,7 @@ __device__ EBT_NOINLINE void optimize_feature(FeatShared& sh, double* costs, Fea
 	st.time_without_update = (long long)(1e6 / fmax(1e-1, sqrt(dx * dx + dy * dy)));
 	st.n_traj++;  // Patch::addTrajectoryPosition (optimizer.cpp:179-181)
 	st.counter = 0;
+	if (cm_out) cost_map(sh, st.warp[0], st.warp[1], st.warp[2], st.warp[3], st.flow, cm_out);  // optimizer.cpp:191-197
 }
 
 // Job (2b): FeatureDetector::updateNumOfEvents (ft/src/feature_detector.cpp:
@@ -1513,7 +1636,8 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 	// Returns true when the mask row was rebuilt (the caller re-expands).
 	auto optimise_at = [&](long long at) -> bool {
 		LmSummary S;
-		optimize_feature(sh, costs, st, ft, P, S);
+		optimize_feature(sh, costs, st, ft, P, S,
+						 P.cost_maps ? P.cost_maps + (size_t)gp.store_slot * 121 : nullptr);
 		if (!S.filtered)
 			motion_compensated(sh, McArgs{st.rx, st.ry, st.cur_ts, st.n_traj, st.size, st.tail}, gp, P.products,
 							   P.mc_nablas);
@@ -1703,7 +1827,7 @@ optimize_batch_kernel(const ebt_problem* __restrict__ problems, int n_problems,
 		*reinterpret_cast<uint4*>(&sh.ring[k]) = __ldg(ev4 + (st.size - 1 - k));
 	__syncthreads();
 	LmSummary S;
-	optimize_feature(sh, costs, st, ft, P, S);
+	optimize_feature(sh, costs, st, ft, P, S, P.cost_maps ? P.cost_maps + (size_t)b * 121 : nullptr);
 	if (nablas)
 		for (int i = threadIdx.x; i < NPIX; i += NT) nablas[(size_t)b * NPIX + i] = sh.nabla[i];
 	if (threadIdx.x == 0)

@@ -159,6 +159,20 @@ int ebt_get_patch(ebt_ctx* ctx, int32_t track_id, int which, double* out625);
  * with drawImages = false); 2: also at image time (drawImages = true). */
 int ebt_set_products(ebt_ctx* ctx, int mode);
 
+/* OptimizerParams::drawCostMap (feature_tracker/optimizer.h:18) and
+ * Optimizer::drawCostMap (ft/src/optimizer.cpp:32-60, called at :191-197): after
+ * every optimisation the solve's functor is evaluated on the 11x11 grid of
+ * integer translation offsets around the solved warp; the map holds the L2 norm
+ * of the 625 residuals.  121 extra pixel passes per optimisation ("it is too
+ * slow", optimizer.cpp:194): off by default, as in the reference.
+ * ebt_get_cost_map replaces Patch::getCostMap (patch.h:56): out121 row-major,
+ * map(y + 5, x + 5); zeros until the patch was optimised with the map on.
+ * ebt_get_batch_cost_maps: the maps of the last ebt_optimize_batch(_device)
+ * call made with the map on, n x 121. */
+int ebt_set_cost_map(ebt_ctx* ctx, int on);
+int ebt_get_cost_map(ebt_ctx* ctx, int32_t track_id, double* out121);
+int ebt_get_batch_cost_maps(ebt_ctx* ctx, double* out, int64_t n);
+
 /* Tracker -> visual odometry hand-off.  For every live patch,
  * in list order: the landmark visual_odometry::Keyframe::Keyframe stores
  * (vo/src/keyframe.cpp:5-14: trackId -> Patch::toCorner()) and, when cam is

@@ -56,6 +56,7 @@ struct EventSample
 
 struct OptimizerParams  // feature_tracker/optimizer.h:16-27
 {
+	bool drawCostMap = false;  // 121 extra pixel passes per optimisation (optimizer.cpp:191-197)
 	int maxNumIterations = 10;
 	double optimizerThreshold = 0.6;
 	double huberLoss = 0.3;
@@ -100,6 +101,8 @@ class Patch
 	const std::vector<TrajectorySample>& getTrajectory() const { return trajectory_; }
 	const std::vector<double>& getFinalCosts() const { return finalCosts_; }
 	const std::vector<double>& getIntegratedNabla() const { return nabla_; }  // 25x25 row-major
+	// 11x11 row-major once optimised with OptimizerParams::drawCostMap, else a single 0 (patch.cpp:29)
+	const std::vector<double>& getCostMap() const { return costMap_; }
 
    private:
 	friend class FeatureDetector;
@@ -107,6 +110,7 @@ class Patch
 	std::vector<TrajectorySample> trajectory_;
 	std::vector<double> finalCosts_;
 	std::vector<double> nabla_;
+	std::vector<double> costMap_ = std::vector<double>(1, 0.0);
 };
 using Patches = std::list<Patch>;
 
@@ -130,6 +134,7 @@ class FeatureDetector
 		p.optimizer_threshold = params.optimizerParams.optimizerThreshold;
 		if (ebt_create(&p, device, &ctx_) != EBT_OK)
 			throw std::runtime_error(std::string("ebt_create: ") + ebt_last_error(nullptr));
+		if (params.optimizerParams.drawCostMap) check(ebt_set_cost_map(ctx_, 1), "ebt_set_cost_map");
 	}
 	~FeatureDetector()
 	{
@@ -274,6 +279,11 @@ class FeatureDetector
 				  "ebt_get_final_costs");
 			p.nabla_.resize(EBT_PATCH_PIXELS);
 			check(ebt_get_patch(ctx_, k.track_id, 0, p.nabla_.data()), "ebt_get_patch");
+			if (params_.optimizerParams.drawCostMap && k.n_optimizations > 0)
+			{
+				p.costMap_.resize(121);
+				check(ebt_get_cost_map(ctx_, k.track_id, p.costMap_.data()), "ebt_get_cost_map");
+			}
 			dst.push_back(std::move(p));
 		}
 	}

@@ -615,6 +615,7 @@ typedef struct
 	double nabla[NPIX];
 	double mc_nabla[NPIX];   /* motionCompensatedIntegratedNabla_ */
 	double pred_nabla[NPIX]; /* predictedNabla_ */
+	double cost_map[121];    /* costMap_ (11x11 once Optimizer::drawCostMap ran, zeros before) */
 	double flow;    /* flowDir_ (double); read through float getFlow() */
 	double warp[4]; /* cos sin tx ty */
 	double* traj;   /* (x, y, ts) triples */
@@ -818,7 +819,55 @@ static void patch_warp_image(opatch* p, const oframe* f)
 		}
 }
 
-/* Optimizer::optimize, ft/src/optimizer.cpp:62-206 (drawCostMap off). */
+/* OptimizerParams::drawCostMap (ft/include/feature_tracker/optimizer.h:18) for
+ * every optimisation that follows. */
+static int g_draw_cost_map = 0;
+void oracle_set_draw_cost_map(int on) { g_draw_cost_map = on; }
+
+/* Optimizer::drawCostMap, ft/src/optimizer.cpp:32-60: the functor of the solve
+ * (old rect, normalised patch) evaluated on an 11x11 grid of integer translation
+ * offsets around the SOLVED warp; the pose is rebuilt from its angle
+ * (Pose2d(pose.log().z(), t): SO2::log = atan2, SO2(theta) = (cos, sin)); the
+ * flow is the float getFlow(); the map holds cv::norm(residuals, NORM_L2) of the
+ * uncorrected residuals r_i = u_i / sqrt(N) + m_i (optimizer_cost.h:29-45). */
+static void draw_cost_map(opatch* p, const oproblem* P)
+{
+	const double theta = atan2(p->warp[1], p->warp[0]);
+	const double cs = cos(theta), sn = sin(theta);
+	const double phi = (double)(float)p->flow;
+	const double vx = cos(phi), vy = sin(phi);
+	const int W = P->frame->w, H = P->frame->h;
+	for (int ox = -5; ox <= 5; ++ox)
+		for (int oy = -5; oy <= 5; ++oy)
+		{
+			const double tx = (double)(float)ox + p->warp[2], ty = (double)(float)oy + p->warp[3];
+			double u[NPIX], N = 1e-5;
+			for (int y = 0; y < SIDE; ++y)
+				for (int xx = 0; xx < SIDE; ++xx)
+				{
+					const int i = xx + SIDE * y;
+					const double px = xx + P->tlx, py = y + P->tly;
+					const double wx = cs * px + -sn * py + tx;
+					const double wy = sn * px + cs * py + ty;
+					u[i] = 0;
+					if (wx >= W || wy >= H || wx < 0.0 || wy < 0.0) continue;
+					double g[2];
+					bicubic(P->frame, wy, wx, g, NULL, NULL);
+					u[i] = g[0] * vx + g[1] * vy;
+					N += u[i] * u[i];
+				}
+			const double sq = sqrt(N);
+			double s = 0;
+			for (int i = 0; i < NPIX; ++i)
+			{
+				const double r = u[i] / sq + P->m[i];
+				s += r * r;
+			}
+			p->cost_map[(oy + 5) * 11 + (ox + 5)] = sqrt(s);
+		}
+}
+
+/* Optimizer::optimize, ft/src/optimizer.cpp:62-206. */
 static void optimize_patch(opatch* p, const oframe* frame, double huber_a,
 						   double threshold, int max_iter, osummary* S)
 {
@@ -875,6 +924,7 @@ static void optimize_patch(opatch* p, const oframe* frame, double huber_a,
 	add_traj(p);
 	patch_integrate_motion_compensated(p);
 	p->counter = 0; /* resetBatch */
+	if (g_draw_cost_map) draw_cost_map(p, &P); /* optimizer.cpp:191-197 */
 }
 
 /* ------------------------------------------------------------------------ */
@@ -1217,8 +1267,13 @@ static opatch* find_patch(otracker* T, int32_t id)
 int oracle_get_patch(void* h, int32_t id, int which, double* out625)
 {
 	opatch* p = find_patch((otracker*)h, id);
-	/* which: 0 integratedNabla_, 1 motionCompensatedIntegratedNabla_, 2 predictedNabla_ */
-	if (!p || which < 0 || which > 2) return -1;
+	/* which: 0 integratedNabla_, 1 motionCompensatedIntegratedNabla_, 2 predictedNabla_, 3 costMap_ */
+	if (!p || which < 0 || which > 3) return -1;
+	if (which == 3)
+	{
+		memcpy(out625, p->cost_map, sizeof(p->cost_map));
+		return 121;
+	}
 	memcpy(out625, which == 0 ? p->nabla : which == 1 ? p->mc_nabla : p->pred_nabla, sizeof(p->nabla));
 	return NPIX;
 }
@@ -1300,6 +1355,23 @@ static void problem_to_patch(opatch* p, const ebt_problem* pr, const ebt_event* 
 
 /* nabla (optional): n x 625 doubles.  iters (optional): n x 2 ints
  * (jacobian evaluations, cost-only evaluations). */
+static double* g_cost_maps_out = NULL;
+double oracle_optimize_batch(void* f, const ebt_problem* problems, int64_t n, const ebt_event* events,
+							 ebt_solution* out, double* nabla, int32_t* evals);
+/* oracle_optimize_batch with drawCostMap on: cost_maps = n x 121 doubles. */
+double oracle_optimize_batch_cm(void* f, const ebt_problem* problems, int64_t n,
+								const ebt_event* events, ebt_solution* out,
+								double* nabla, double* cost_maps)
+{
+	const int was = g_draw_cost_map;
+	g_draw_cost_map = 1;
+	g_cost_maps_out = cost_maps;
+	oracle_optimize_batch(f, problems, n, events, out, nabla, NULL);
+	g_cost_maps_out = NULL;
+	g_draw_cost_map = was;
+	return 0;
+}
+
 double oracle_optimize_batch(void* f, const ebt_problem* problems, int64_t n,
 							 const ebt_event* events, ebt_solution* out,
 							 double* nabla, int32_t* evals)
@@ -1329,6 +1401,7 @@ double oracle_optimize_batch(void* f, const ebt_problem* problems, int64_t n,
 		}
 		s->n_passes = -1;
 		(void)in;
+		if (g_cost_maps_out) memcpy(g_cost_maps_out + i * 121, p->cost_map, sizeof(p->cost_map));
 		if (evals)
 		{
 			evals[2 * i] = S.n_jac_evals;

@@ -91,6 +91,12 @@ void logSobel(const uint8_t* gray, int w, int h, cv::Mat& gx, cv::Mat& gy)
 		}
 }
 
+// OptimizerParams::drawCostMap (optimizer.h:18) for every Optimizer created
+// after the call: Optimizer::drawCostMap (optimizer.cpp:32-60) then runs inside
+// optimize() and Patch::getCostMap() returns the 11x11 map.
+bool g_drawCostMap = false;
+double* g_costMapsOut = nullptr;  // ref_optimize_batch_cm: n x 121 doubles
+
 struct RefTracker
 {
 	// mirrors of FeatureDetector members (feature_detector.h:94-118)
@@ -229,6 +235,7 @@ void ref_new_frame_begin(void* h, const uint8_t* gray, int64_t ts,
 	}
 	logSobel(gray, T.params.imageSize.width, T.params.imageSize.height, T.gradX,
 			 T.gradY);
+	T.params.optimizerParams.drawCostMap = g_drawCostMap;
 	T.optimizers[ts] = std::make_unique<tracker::Optimizer>(
 		tracker::Optimizer(T.params.optimizerParams, T.params.imageSize));
 	T.optimizers[ts]->setGrad(T.gradX, T.gradY);
@@ -430,14 +437,15 @@ static tracker::Patch* findPatch(RefTracker& T, int32_t id)
 		if (p.getTrackId() == id) return &p;
 	return nullptr;
 }
-// which: 0 integratedNabla, 1 motion-compensated, 2 predictedNabla
+// which: 0 integratedNabla, 1 motion-compensated, 2 predictedNabla, 3 costMap
 int ref_get_patch(void* h, int32_t id, int which, double* out625)
 {
 	auto* p = findPatch(*static_cast<RefTracker*>(h), id);
 	if (!p) return -1;
 	const cv::Mat& m = which == 0   ? p->getIntegratedNabla()
 					   : which == 1 ? p->getCompenatedIntegratedNabla()
-									: p->getPredictedNabla();
+					   : which == 2 ? p->getPredictedNabla()
+									: p->getCostMap();
 	for (int y = 0; y < m.rows; ++y)
 		for (int x = 0; x < m.cols; ++x) out625[y * m.cols + x] = m.at<double>(y, x);
 	return m.rows * m.cols;
@@ -517,8 +525,9 @@ void solveRange(const RefFrames* F, const ebt_problem* problems,
 		auto& opt = opts[pr.frame_slot];
 		if (!opt)
 		{
-			opt.reset(new tracker::Optimizer(tracker::OptimizerParams(),
-											 cv::Size(F->width, F->height)));
+			tracker::OptimizerParams op;
+			op.drawCostMap = g_drawCostMap;
+			opt.reset(new tracker::Optimizer(op, cv::Size(F->width, F->height)));
 			opt->setGrad(F->gx[pr.frame_slot], F->gy[pr.frame_slot]);
 		}
 		tracker::Patch patch = makePatch(pr, events);
@@ -542,6 +551,14 @@ void solveRange(const RefFrames* F, const ebt_problem* problems,
 				(void)inRect;
 			}
 		s.n_passes = -1;
+		if (g_costMapsOut)
+		{
+			// zeros(1, 1) until drawCostMap ran (patch.cpp:29)
+			const cv::Mat& cm = patch.getCostMap();
+			for (int k = 0; k < 121; ++k)
+				g_costMapsOut[i * 121 + k] =
+					(cm.rows == 11 && cm.cols == 11) ? cm.at<double>(k / 11, k % 11) : 0.0;
+		}
 	}
 }
 }  // namespace
@@ -601,6 +618,22 @@ double ref_optimize_batch(void* f, const ebt_problem* problems, int64_t n,
 	}
 	return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0)
 		.count();
+}
+
+void ref_set_draw_cost_map(int on) { g_drawCostMap = on != 0; }
+// ref_optimize_batch with OptimizerParams::drawCostMap on: cost_maps = n x 121
+// doubles, row-major costMap.at<double>(y + 5, x + 5).
+double ref_optimize_batch_cm(void* f, const ebt_problem* problems, int64_t n,
+							 const ebt_event* events, ebt_solution* out,
+							 double* nabla, double* cost_maps)
+{
+	const bool was = g_drawCostMap;
+	g_drawCostMap = true;
+	g_costMapsOut = cost_maps;
+	const double t = ref_optimize_batch(f, problems, n, events, out, nabla, 1);
+	g_costMapsOut = nullptr;
+	g_drawCostMap = was;
+	return t;
 }
 
 // Residuals (625) and Ceres-autodiff Jacobians of the reference functor

@@ -89,6 +89,8 @@ def _declare(dll, prefix):
     fn("frames_destroy", None, _vp)
     fn("frames_add", C.c_int, _vp, _vp)
     fn("frames_get", C.c_int, _vp, C.c_int, _vp, _vp)
+    fn("set_draw_cost_map", None, C.c_int)
+    fn("optimize_batch_cm", C.c_double, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp)
     if prefix == "ref_":
         fn("optimize_batch", C.c_double, _vp, _vp, C.c_int64, _vp, _vp, _vp, C.c_int)
         fn("eval_functor", C.c_int, _vp, C.c_int, _vp, C.c_double, C.c_double, _vp, C.c_double,
@@ -167,6 +169,12 @@ class CpuTracker:
         n = self.L.get_patch(self.h_, int(track_id), which, _ptr(out))
         return out if n == PATCH_PIXELS else None
 
+    def cost_map(self, track_id):
+        """Patch::getCostMap(): 11x11 after Optimizer::drawCostMap ran, else zeros."""
+        out = np.zeros(PATCH_PIXELS, np.float64)
+        n = self.L.get_patch(self.h_, int(track_id), 3, _ptr(out))
+        return out[:121].reshape(11, 11).copy() if n == 121 else np.zeros((11, 11))
+
     def trajectory(self, track_id, cap=1 << 16):
         out = np.zeros((cap, 3), np.float64)
         n = self.L.get_trajectory(self.h_, int(track_id), _ptr(out), cap)
@@ -221,6 +229,16 @@ class CpuBatch:
             secs = self.L.optimize_batch(self.f_, _ptr(problems), n, _ptr(events), _ptr(sol),
                                          _ptr(nabla), _ptr(evals))
         return sol, nabla, evals, secs
+
+    def optimize_cost_maps(self, problems, events):
+        """Optimizer::optimize with OptimizerParams::drawCostMap on -> (solutions, n x 11 x 11 cost maps)."""
+        problems = np.ascontiguousarray(problems)
+        events = np.ascontiguousarray(events)
+        n = len(problems)
+        sol = np.zeros(n, SOLUTION)
+        cm = np.zeros((n, 11, 11))
+        self.L.optimize_batch_cm(self.f_, _ptr(problems), n, _ptr(events), _ptr(sol), None, _ptr(cm))
+        return sol, cm
 
 
 def cpu_unproject(lib, camera, pts):

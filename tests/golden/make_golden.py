@@ -7,6 +7,8 @@ Patch/Optimizer/Ceres build, `make -C oracle ref`) and Python cv2.
 Fixtures (all inputs + the reference's outputs, so tests need neither
 /root/reference nor cv2):
   problems_ref.npz   24 independent feature-patch problems -> Optimizer::optimize
+  costmap_ref.npz    the same 24 problems with OptimizerParams::drawCostMap on ->
+                     Patch::getCostMap() (11x11) of Optimizer::drawCostMap
   functor_ref.npz    residuals + Ceres-autodiff Jacobians of OptimizerCostFunctor
   stream_ref.npz     a 240x180 stream driven per event through the reference
                      harness (records, tracks, patches)
@@ -40,6 +42,10 @@ def main():
     np.savez_compressed(os.path.join(HERE, "problems_ref.npz"), frame=ps.frames[0], problems=ps.problems,
                         events=ps.events, solutions=sol, nabla=nab.astype(np.int16),
                         grad_probe=np.stack([gx[::17, ::13], gy[::17, ::13]]))
+
+    # ---- Optimizer::drawCostMap on the same problems ----------------------
+    _, cm = b.optimize_cost_maps(ps.problems, ps.events)
+    np.savez_compressed(os.path.join(HERE, "costmap_ref.npz"), cost_maps=cm)
 
     # ---- functor residuals / autodiff Jacobians --------------------------
     rng = np.random.Generator(np.random.PCG64(9))

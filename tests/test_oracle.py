@@ -65,6 +65,22 @@ def test_problems_against_reference_golden(ora):
     assert np.abs(sol["final_cost"] - ref["final_cost"]).max() < 1e-12
 
 
+def test_cost_map_against_reference_golden(ora):
+    """Optimizer::drawCostMap (optimizer.cpp:32-60) with OptimizerParams::drawCostMap on:
+    Patch::getCostMap() of the reference build on the 24 golden problems."""
+    g = np.load(os.path.join(G, "problems_ref.npz"))
+    cm_ref = np.load(os.path.join(G, "costmap_ref.npz"))["cost_maps"]
+    b = CpuBatch(ora, 240, 180)
+    b.add_frame(g["frame"])
+    sol, cm = b.optimize_cost_maps(g["problems"], g["events"])
+    assert cm_ref.shape == cm.shape == (24, 11, 11) and cm_ref.min() > 0.5
+    assert np.abs(cm - cm_ref).max() <= 1e-12
+    # the map does not change the solve
+    assert np.abs(sol["x"] - g["solutions"]["x"]).max() <= 1e-9
+    # off by default: zeros (the reference holds zeros(1, 1) then)
+    ora.set_draw_cost_map(0)
+
+
 def test_functor_jacobian_against_ceres_autodiff(ora):
     g = np.load(os.path.join(G, "functor_ref.npz"))
     b = CpuBatch(ora, 240, 180)
