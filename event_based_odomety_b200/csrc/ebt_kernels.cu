@@ -259,76 +259,6 @@ __device__ __forceinline__ void sample_taps(const double2* __restrict__ grid, in
 	}
 }
 
-#ifndef EBT_PIX_ILP
-#define EBT_PIX_ILP 1  // pixels evaluated side by side per loop trip (1 or 2)
-#endif
-
-// Per-pixel terms of one evaluation, straight-line (no branches): the taps are
-// always addressed through clamped indices, so an out-of-image pixel computes
-// harmless values and is dropped by `valid`.  Same arithmetic, in the same
-// order, as the branching form below => bit-identical sums.
-template <bool JAC>
-struct PixTerms
-{
-	double u, mi, du[4];
-	bool valid;
-};
-
-template <bool JAC>
-__device__ __forceinline__ void pixel_terms(const double2* __restrict__ grid, int W, int H, double cs,
-											 double sn, double tx, double ty, double vx, double vy,
-											 double tlx, double tly, const double* m, int i,
-											 PixTerms<JAC>& T)
-{
-	const int yy = i / SIDE, xx = i - yy * SIDE;
-	const double px = xx + tlx, py = yy + tly;
-	const double wx = cs * px + -sn * py + tx;
-	const double wy = sn * px + cs * py + ty;
-	T.valid = !(wx >= W || wy >= H || wx < 0.0 || wy < 0.0);
-	// keep the index arithmetic in range for pixels that are dropped anyway
-	const double wxc = fmin(fmax(wx, -4.0), (double)W + 4.0), wyc = fmin(fmax(wy, -4.0), (double)H + 4.0);
-	const double fr = floor(wyc), fc = floor(wxc);
-	const int row = (int)fr, col = (int)fc;
-	double wr[4], dr[4], wc[4], dc[4];
-	cr_weights<JAC>(wy - fr, wr, dr);
-	cr_weights<JAC>(wx - fc, wc, dc);
-	double g0, g1, gr0, gr1, gc0, gc1;
-	sample_taps<JAC, false>(grid, W, H, row, col, wr, dr, wc, dc, g0, g1, gr0, gr1, gc0, gc1);
-	T.u = g0 * vx + g1 * vy;
-	T.mi = m[i];
-	if (JAC)
-	{
-		const double ux = gc0 * vx + gc1 * vy;  // du/dW.x
-		const double uy = gr0 * vx + gr1 * vy;  // du/dW.y
-		T.du[0] = ux * cs + uy * sn;
-		T.du[1] = -ux * sn + uy * cs;
-		T.du[2] = ux * (-cs * py - sn * px) + uy * (-sn * py + cs * px);
-		T.du[3] = -g0 * vy + g1 * vx;
-	}
-}
-
-template <bool JAC>
-__device__ __forceinline__ void pixel_accumulate(const PixTerms<JAC>& T, double (&acc)[JAC ? 20 : 2])
-{
-	if (!T.valid) return;
-	acc[0] += T.u * T.u;
-	acc[1] += T.u * T.mi;
-	if (JAC)
-	{
-#pragma unroll
-		for (int q = 0; q < 4; ++q)
-		{
-			acc[2 + q] += T.u * T.du[q];
-			acc[6 + q] += T.du[q] * T.mi;
-		}
-		int k = 10;
-#pragma unroll
-		for (int q = 0; q < 4; ++q)
-#pragma unroll
-			for (int p = q; p < 4; ++p) acc[k++] += T.du[q] * T.du[p];
-	}
-}
-
 template <bool JAC>
 __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, int W, int H,
 											 const double (&x)[5], double vx, double vy,
@@ -338,21 +268,6 @@ __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, in
 	const double cs = x[0], sn = x[1], tx = x[2], ty = x[3];
 #pragma unroll
 	for (int k = 0; k < (JAC ? 20 : 2); ++k) acc[k] = 0.0;
-#if EBT_PIX_ILP == 2
-	// two pixels per trip, evaluated side by side (independent dependency
-	// chains for the FP64 pipe), accumulated in pixel order
-#pragma unroll 1
-	for (int i = threadIdx.x; i < NPIX; i += 2 * NT)
-	{
-		PixTerms<JAC> A, B;
-		const int iB = i + NT;
-		pixel_terms<JAC>(grid, W, H, cs, sn, tx, ty, vx, vy, tlx, tly, m, i, A);
-		pixel_terms<JAC>(grid, W, H, cs, sn, tx, ty, vx, vy, tlx, tly, m, min(iB, NPIX - 1), B);
-		B.valid = B.valid && iB < NPIX;
-		pixel_accumulate<JAC>(A, acc);
-		pixel_accumulate<JAC>(B, acc);
-	}
-#else
 #pragma unroll kPixUnroll
 	for (int i = threadIdx.x; i < NPIX; i += NT)
 	{
@@ -397,7 +312,6 @@ __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, in
 				for (int p = q; p < 4; ++p) acc[k++] += du[q] * du[p];
 		}
 	}
-#endif
 }
 
 // HuberLoss::Evaluate (ceres/internal/ceres/loss_function.cc:48-62) on the
