@@ -406,7 +406,7 @@ def main_ours(args):
             "e2e": {"value": ge_opts / ge_secs, "unit": "optimisations/s",
                     "h2d_bytes_per_step": int(n_events * 16 + sum(
                         L.nF * w * h + 8 * sum(len(c) * 2 for c in L.S.corners) for L in lanes)),
-                    "d2h_bytes_per_step": int(opts_step * OPT_RECORD.itemsize + 2 * nF * feat * 216 * nS)},
+                    "d2h_bytes_per_step": int(opts_step * OPT_RECORD.itemsize + 2 * nF * feat * 288 * nS)},
             # every push launches prefilter_kernel + track_batch_kernel
             "gpu_launches": int(2 * kt_n + kg_n + kn_n),
             "roofline": {"bound": "fp64",

@@ -71,6 +71,7 @@ EXPORTS = {
     "ebt_get_tracks": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "ebt_get_patch": (C.c_int, [_vp, C.c_int32, C.c_int, _vp]),
     "ebt_set_products": (C.c_int, [_vp, C.c_int]),
+    "ebt_debug_feature_load": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int, _vp]),
     "ebt_set_cost_map": (C.c_int, [_vp, C.c_int]),
     "ebt_get_cost_map": (C.c_int, [_vp, C.c_int32, _vp]),
     "ebt_get_batch_cost_maps": (C.c_int, [_vp, _vp, C.c_int64]),
@@ -327,6 +328,16 @@ class Tracker:
 
     def set_products(self, mode):
         self._ck(self.lib.ebt_set_products(self.ctx, int(mode)))
+
+    def feature_load(self, cap=8192):
+        """(track ids, optimisations, t0 ns, t1 ns, sm) of every live patch's CTA in the previous push."""
+        ids, nopt, sm = (np.zeros(cap, np.int32) for _ in range(3))
+        t0, t1 = np.zeros(cap, np.uint64), np.zeros(cap, np.uint64)
+        n = C.c_int(0)
+        self._ck(self.lib.ebt_debug_feature_load(self.ctx, _ptr(ids), _ptr(nopt), _ptr(t0), _ptr(t1), _ptr(sm),
+                                                 cap, C.byref(n)))
+        k = min(n.value, cap)
+        return ids[:k], nopt[:k], t0[:k], t1[:k], sm[:k]
 
     def set_cost_map(self, on=True):
         """OptimizerParams::drawCostMap."""

@@ -112,6 +112,7 @@ struct ebt_ctx
 	std::vector<std::vector<double>> arch_pred;  // products on: predictedNabla_
 	std::vector<std::vector<double>> arch_cost;  // cost map on: costMap_ (121)
 	std::vector<int> free_slots;
+	std::vector<int> assoc_start, assoc_items, assoc_fill;  // corner buckets of associatePatches
 	bool host_dirty = true;  // h holds changes the device has not seen
 	int next_track_id = 0;
 	std::vector<double> corners;  // FeatureDetector::corners_ of the latest frame
@@ -138,6 +139,7 @@ struct ebt_ctx
 	size_t rec_stage_cap = 0;
 	unsigned long long* nrec_stage = nullptr;
 	std::vector<int> pos_of_id;  // track id -> index in h, rebuilt per push
+	std::vector<int> load_est;   // per patch: expected optimisations in the next push (CTA order)
 
 	// stream-kernel scratch: prefilter mask (P rows), CTA order
 	unsigned* d_mask = nullptr;
@@ -729,6 +731,27 @@ int ebt_debug_phase_clocks(ebt_ctx* ctx, uint64_t* out8)
 	return EBT_OK;
 }
 
+int ebt_debug_feature_load(ebt_ctx* ctx, int32_t* track_ids, int32_t* n_opt, uint64_t* t0_ns, uint64_t* t1_ns,
+						   int32_t* sm, int cap, int* n_out)
+{
+	if (!ctx || !n_out || cap < 0) return fail(ctx, EBT_E_INVALID, "ebt_debug_feature_load: bad argument");
+	int n = 0;
+	for (const DevPatch& p : ctx->h)
+	{
+		if (n < cap)
+		{
+			if (track_ids) track_ids[n] = p.track_id;
+			if (n_opt) n_opt[n] = p.last_n_opt;
+			if (t0_ns) t0_ns[n] = p.last_t0_ns;
+			if (t1_ns) t1_ns[n] = p.last_t1_ns;
+			if (sm) sm[n] = p.last_sm;
+		}
+		++n;
+	}
+	*n_out = n;
+	return EBT_OK;
+}
+
 int ebt_set_prefilter_margin(ebt_ctx* ctx, double pixels)
 {
 	if (!ctx || !(pixels >= 0.0) || pixels > 4096.0)
@@ -777,23 +800,75 @@ static int newFrameBegin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us, const
 		ctx->corners.clear();
 	std::vector<int> newIds(static_cast<size_t>(n_corners), -1);
 	const size_t first_sample = ctx->img_samples.size();
+	// associatePatches (feature_detector.cpp:630-664): every patch, in list
+	// order, takes the FIRST corner (in corner order) that is still free and
+	// closer than associationDistance.  The corners are bucketed on a uniform
+	// grid of cell size d, so a patch only looks at the 3x3 cells around its
+	// centre; each bucket keeps corner order, so "first" is the smallest index
+	// over the nine buckets — the same decisions as the reference's double loop.
+	const double d = ctx->prm.association_distance;
+	bool use_grid = d > 0.0 && static_cast<size_t>(n_corners) * ctx->h.size() > 4096;
+	for (int j = 0; j < 2 * n_corners && use_grid; ++j) use_grid = std::isfinite(cornersXY[j]);
+	const int gw = use_grid ? static_cast<int>(std::min(4096.0, std::ceil(ctx->prm.width / d) + 2.0)) : 0;
+	const int gh = use_grid ? static_cast<int>(std::min(4096.0, std::ceil(ctx->prm.height / d) + 2.0)) : 0;
+	auto cellOf = [&](double v, int n) {
+		const double c = std::floor(v / d) + 1.0;  // monotone in v, then clamped: neighbours stay neighbours
+		return c < 0.0 ? 0 : (c > n - 1 ? n - 1 : static_cast<int>(c));
+	};
+	std::vector<int>& cellStart = ctx->assoc_start;
+	std::vector<int>& cellItems = ctx->assoc_items;
+	if (use_grid)
+	{
+		cellStart.assign(static_cast<size_t>(gw) * gh + 1, 0);
+		cellItems.resize(static_cast<size_t>(n_corners));
+		for (int j = 0; j < n_corners; ++j)
+			cellStart[static_cast<size_t>(cellOf(cornersXY[2 * j + 1], gh)) * gw + cellOf(cornersXY[2 * j], gw) + 1]++;
+		for (size_t c = 1; c < cellStart.size(); ++c) cellStart[c] += cellStart[c - 1];
+		std::vector<int>& fill = ctx->assoc_fill;
+		fill.assign(cellStart.begin(), cellStart.end() - 1);
+		for (int j = 0; j < n_corners; ++j)
+			cellItems[static_cast<size_t>(
+				fill[static_cast<size_t>(cellOf(cornersXY[2 * j + 1], gh)) * gw + cellOf(cornersXY[2 * j], gw)]++)] = j;
+	}
+	auto matches = [&](double cx, double cy, int j) {
+		const double dx = cx - cornersXY[2 * j], dy = cy - cornersXY[2 * j + 1];
+		// |dx| or |dy| >= d implies the norm is >= d: skip the sqrt, same decision
+		if (!(std::fabs(dx) < d) || !(std::fabs(dy) < d)) return false;
+		return newIds[static_cast<size_t>(j)] == -1 && std::sqrt(dx * dx + dy * dy) < d;
+	};
 	for (size_t i = 0; i < ctx->h.size(); ++i)
 	{
 		DevPatch& p = ctx->h[i];
 		double cx, cy;
 		cornerOf(p, cx, cy);
-		for (int j = 0; j < n_corners; ++j)
+		if (use_grid && std::isfinite(cx) && std::isfinite(cy))
 		{
-			const double dx = cx - cornersXY[2 * j], dy = cy - cornersXY[2 * j + 1];
-			// |dx| or |dy| >= d implies the norm is >= d: skip the sqrt, same decision
-			if (!(std::fabs(dx) < ctx->prm.association_distance) || !(std::fabs(dy) < ctx->prm.association_distance))
-				continue;
-			if (newIds[j] == -1 && std::sqrt(dx * dx + dy * dy) < ctx->prm.association_distance)
-			{
-				newIds[j] = p.track_id;
-				break;
-			}
+			int best = n_corners;
+			const int gx = cellOf(cx, gw), gy = cellOf(cy, gh);
+			for (int yy = std::max(gy - 1, 0); yy <= std::min(gy + 1, gh - 1); ++yy)
+				for (int xx = std::max(gx - 1, 0); xx <= std::min(gx + 1, gw - 1); ++xx)
+				{
+					const size_t c = static_cast<size_t>(yy) * gw + xx;
+					for (int k = cellStart[c]; k < cellStart[c + 1]; ++k)
+					{
+						const int j = cellItems[static_cast<size_t>(k)];
+						if (j >= best) break;  // buckets are in corner order
+						if (matches(cx, cy, j))
+						{
+							best = j;
+							break;
+						}
+					}
+				}
+			if (best < n_corners) newIds[static_cast<size_t>(best)] = p.track_id;
 		}
+		else
+			for (int j = 0; j < n_corners; ++j)
+				if (matches(cx, cy, j))
+				{
+					newIds[static_cast<size_t>(j)] = p.track_id;
+					break;
+				}
 		p.cur_ts = ts_us;  // Patch::setTs
 		addTraj(ctx, p);
 	}
@@ -1002,9 +1077,33 @@ static int runStream(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t
 	}
 	// CTA order: features with the most optimisations in the previous push first
 	// (longest-processing-time-first keeps the kernel's tail short)
+	// Load estimate = optimisations in the previous push; a patch that has its flow
+	// but has never been optimised (it was created at the previous image, so its
+	// previous push only collected events) is expected to carry the mean load —
+	// rating it 0 would start a full-weight CTA in the last wave.
+	{
+		long long sum = 0, cnt = 0;
+		for (int i = 0; i < P; ++i)
+		{
+			const DevPatch& p = ctx->h[static_cast<size_t>(i)];
+			if (!p.lost && p.init && p.n_costs > 0)
+			{
+				sum += p.last_n_opt;
+				++cnt;
+			}
+		}
+		const int mean = cnt ? static_cast<int>((sum + cnt - 1) / cnt) : 1;
+		ctx->load_est.resize(static_cast<size_t>(P));
+		for (int i = 0; i < P; ++i)
+		{
+			const DevPatch& p = ctx->h[static_cast<size_t>(i)];
+			ctx->load_est[static_cast<size_t>(i)] =
+				p.lost ? -1 : (!p.init ? 0 : (p.n_costs == 0 ? mean : p.last_n_opt));
+		}
+	}
 	for (int i = 0; i < P; ++i) ctx->h_order[i] = i;
 	std::stable_sort(ctx->h_order, ctx->h_order + P,
-					 [&](int a, int b) { return ctx->h[static_cast<size_t>(a)].last_n_opt > ctx->h[static_cast<size_t>(b)].last_n_opt; });
+					 [&](int a, int b) { return ctx->load_est[static_cast<size_t>(a)] > ctx->load_est[static_cast<size_t>(b)]; });
 	CU(cudaMemcpyAsync(ctx->d_order, ctx->h_order, static_cast<size_t>(P) * sizeof(int), cudaMemcpyHostToDevice,
 					   ctx->stream));
 	CU(cudaMemsetAsync(ctx->d_nrec, 0, sizeof(unsigned long long), ctx->stream));

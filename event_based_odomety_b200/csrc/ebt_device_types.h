@@ -11,7 +11,7 @@
 #define EBT_THREADS 128     // threads per feature CTA
 #endif
 // per-feature window ring capacity: a power of two >= 300 + one chunk of EBT_THREADS
-#define EBT_RING (EBT_THREADS <= 128 ? 512 : 1024)
+#define EBT_RING (EBT_THREADS <= 212 ? 512 : 1024)
 
 // Device mirror of the scalars of tracker::Patch
 // (/root/reference/implementation/feature_tracker/include/feature_tracker/patch.h:98-130).
@@ -35,6 +35,10 @@ struct DevPatch
 	// patch.cpp:91-92): [0] = second newest, [1] = newest
 	double traj_x[2], traj_y[2];
 	long long traj_ts[2];
+	// load diagnostics of the previous push (ebt_debug_feature_load): %globaltimer at the
+	// CTA's entry and exit, and the SM it ran on
+	unsigned long long last_t0_ns, last_t1_ns;
+	int last_sm, pad_;
 };
 
 // Solver constants: the reference's OptimizerParams

@@ -23,6 +23,17 @@
 #define SIDE EBT_PATCH_SIDE
 #define NT EBT_THREADS
 #define NW (EBT_THREADS / 32)
+// EBT_DEDICATED_LEADER: warp 0 runs the scalar trust-region chain only and the
+// pixel passes of the solve are shared by warps 1.. (PIX_NT threads), so the
+// leader's LM state never has to survive a pixel pass in registers (or be
+// spilled around it) and the kernel's register need is max(LM, pixel pass)
+// instead of their sum.
+#ifndef EBT_DEDICATED_LEADER
+#define EBT_DEDICATED_LEADER 0
+#endif
+#define PIX_T0 (EBT_DEDICATED_LEADER ? 32 : 0)  // first thread that evaluates pixels in a solve
+#define PIX_NT (NT - PIX_T0)
+#define PIX_NW (PIX_NT / 32)
 #define RMASK (EBT_RING - 1)
 #ifdef EBT_INLINE_ALL
 #define EBT_NOINLINE
@@ -259,17 +270,18 @@ __device__ __forceinline__ void sample_taps(const double2* __restrict__ grid, in
 	}
 }
 
-template <bool JAC>
+// The 625 pixels are strided over STRIDE threads; `tid` is this thread's index among them.
+template <bool JAC, int STRIDE>
 __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, int W, int H,
 											 const double (&x)[5], double vx, double vy,
-											 double tlx, double tly, const double* m,
+											 double tlx, double tly, const double* m, int tid,
 											 double (&acc)[JAC ? 20 : 2])
 {
 	const double cs = x[0], sn = x[1], tx = x[2], ty = x[3];
 #pragma unroll
 	for (int k = 0; k < (JAC ? 20 : 2); ++k) acc[k] = 0.0;
 #pragma unroll kPixUnroll
-	for (int i = threadIdx.x; i < NPIX; i += NT)
+	for (int i = tid; i < NPIX; i += STRIDE)
 	{
 		const int yy = i / SIDE, xx = i - yy * SIDE;
 		const double px = xx + tlx, py = yy + tly;
@@ -434,7 +446,8 @@ __device__ __forceinline__ void post_request(FeatShared& sh, int kind, const dou
 // posted request and leaves its warp totals in sh.red[warp][].
 __device__ __noinline__ void pixel_service(FeatShared& sh)
 {
-	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int tid = (int)threadIdx.x - PIX_T0;
+	const int lane = tid & 31, warp = tid >> 5;
 	double x[5];
 #pragma unroll
 	for (int k = 0; k < 5; ++k) x[k] = sh.req[k];
@@ -443,7 +456,7 @@ __device__ __noinline__ void pixel_service(FeatShared& sh)
 	if (sh.req_kind == 2)
 	{
 		double acc[20];
-		eval_pixels<true>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, acc);
+		eval_pixels<true, PIX_NT>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, tid, acc);
 		Butterfly<20, 16>::run(acc, lane);
 		const int slot = butterfly_slot<20>(lane);
 		if (slot >= 0) sh.red[warp][slot] = acc[0];
@@ -451,7 +464,7 @@ __device__ __noinline__ void pixel_service(FeatShared& sh)
 	else
 	{
 		double acc[2];
-		eval_pixels<false>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, acc);
+		eval_pixels<false, PIX_NT>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, tid, acc);
 		Butterfly<2, 16>::run(acc, lane);
 		const int slot = butterfly_slot<2>(lane);
 		if (slot >= 0) sh.red[warp][slot] = acc[0];
@@ -472,11 +485,12 @@ __device__ void lm_worker(FeatShared& sh)
 // CTA total of reduced value k: pairwise over the per-warp partials
 __device__ __forceinline__ double red_total(const FeatShared& sh, int k)
 {
-	double v[NW];
+	static_assert((PIX_NW & (PIX_NW - 1)) == 0, "pairwise tree over the pixel warps");
+	double v[PIX_NW];
 #pragma unroll
-	for (int w = 0; w < NW; ++w) v[w] = sh.red[w][k];
+	for (int w = 0; w < PIX_NW; ++w) v[w] = sh.red[w][k];
 #pragma unroll
-	for (int n = NW; n > 1; n >>= 1)
+	for (int n = PIX_NW; n > 1; n >>= 1)
 #pragma unroll
 		for (int w = 0; w < n / 2; ++w) v[w] = v[2 * w] + v[2 * w + 1];
 	return v[0];
@@ -499,7 +513,9 @@ __device__ __forceinline__ bool leader_eval(FeatShared& sh, int kind, const doub
 	sincos_fast(x[4], &vy, &vx);
 	post_request(sh, kind, x, vx, vy);
 	PHASE_T(t1);
+#if !EBT_DEDICATED_LEADER
 	pixel_service(sh);
+#endif
 	PHASE_T(t2);
 	partials_wait();
 	PHASE_T(t3);
@@ -1064,7 +1080,7 @@ __device__ __noinline__ void cost_map(FeatShared& sh, double w0, double w1, doub
 		x[2] = (double)ox + w2;
 		x[3] = (double)oy + w3;
 		double acc[2];
-		eval_pixels<false>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, acc);
+		eval_pixels<false, NT>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, (int)threadIdx.x, acc);
 		block_sum<2>(sh, acc);
 		if (threadIdx.x == 0)
 		{
@@ -1528,6 +1544,8 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 	const int f = order[blockIdx.x];
 	DevPatch& gp = patches[f];
 	if (gp.lost) return;  // uniform over the CTA
+	unsigned long long t_enter;
+	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_enter));
 	FeatState st;
 	load_state(st, gp);
 	const int track_id = gp.track_id;
@@ -1699,6 +1717,13 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 	{
 		store_state(st, gp);
 		gp.last_n_opt = n_opt;  // load estimate for the next launch's CTA order
+		unsigned long long t_exit;
+		unsigned sm;
+		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_exit));
+		asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+		gp.last_t0_ns = t_enter;
+		gp.last_t1_ns = t_exit;
+		gp.last_sm = (int)sm;
 	}
 }
 

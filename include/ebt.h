@@ -264,6 +264,13 @@ int ebt_timing_reset(ebt_ctx* ctx);
  * -DEBT_PHASE_CLOCKS (the shipped build is not). */
 int ebt_debug_phase_clocks(ebt_ctx* ctx, uint64_t* out8);
 
+/* Diagnostics (not part of the reference's API): per live patch, what its CTA
+ * did in the previous ebt_push_events: optimisations run, %globaltimer (ns) at
+ * the CTA's entry and exit, SM id.  Used by tools/load_profile.py to show how
+ * the stream kernel's duration follows the heaviest feature's serial chain. */
+int ebt_debug_feature_load(ebt_ctx* ctx, int32_t* track_ids, int32_t* n_opt, uint64_t* t0_ns, uint64_t* t1_ns,
+						   int32_t* sm, int cap, int* n_out);
+
 /* Tuning knob of ebt_push_events (not part of the reference's API).  Before the
  * stream kernel runs, a prefilter marks, per feature, the events whose pixel
  * lies within `pixels` of the feature's patch rect as it stands at the push;
