@@ -11,6 +11,11 @@
 #define EBT_THREADS 128     // threads per feature CTA
 #endif
 // per-feature window ring capacity: a power of two >= 300 + one chunk of EBT_THREADS
+// resident feature CTAs per SM the stream/batched kernels are built for (Makefile MIN_CTAS)
+#ifndef EBT_MIN_CTAS
+#define EBT_MIN_CTAS 3
+#endif
+#define EBT_RESIDENT_CTAS EBT_MIN_CTAS
 #define EBT_RING (EBT_THREADS <= 212 ? 512 : 1024)
 
 // Device mirror of the scalars of tracker::Patch

@@ -43,9 +43,6 @@
 #ifndef EBT_PIX_UNROLL
 #define EBT_PIX_UNROLL 1  // the hot loop must fit the 32 KB L1.5 instruction cache
 #endif
-#ifndef EBT_MIN_CTAS
-#define EBT_MIN_CTAS 4  // resident CTAs per SM the register budget is tuned for
-#endif
 
 // Phase clocks of the leader warp (build with -DEBT_PHASE_CLOCKS; read through
 // ebt_launch_phase_clocks): 0 request+handshake, 1 pixel pass, 2 wait for the
