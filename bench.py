@@ -211,7 +211,7 @@ def main_reference(args):
         "e2e": {"value": value, "unit": "optimisations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 # ---------------------------------------------------------------------------
@@ -414,7 +414,7 @@ def main_ours(args):
                          f"track_batch_kernel of {nS} concurrent streams (kernels overlap: time = the step)",
                          "achieved": achieved,
                          "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
-                         "traffic": traffic, "traffic_unit": "DRAM bytes per launch (ncu --set full, profiles/r1_ncu_metrics.json)",
+                         "traffic": traffic, "traffic_unit": "DRAM bytes per launch (ncu --set full, profiles/r1_track_batch_kernel_ncu_metrics.json)",
                          "launches_per_step": launches_step,
                          "algorithmic_flops_per_launch": flops_step / launches_step if launches_step else None,
                          "kernel_ms_per_launch": kt_s * 1e3 / launches_step if launches_step else None,
@@ -438,14 +438,24 @@ def main_ours(args):
                 "events_per_s": ne / dt,
                 "sample": f"first {cf} frames + event batches of the same stream ({ne} events, {n} optimisations, "
                           f"{dt:.1f} s), single thread as the reference runs it"}
-        print(json.dumps(line))
+        emit(line)
     for L in lanes:
         L.tr.close()
     if world > 1:
         dist.destroy_process_group()
 
 
+def emit(line):
+    """The JSON line is the only thing written to the real stdout."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
 if __name__ == "__main__":
+    # libraries (NCCL's version banner, torchrun notices) must not share stdout with the
+    # one JSON line the contract asks for: everything else goes to stderr
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     a = parse()
     if a.impl == "reference":
         main_reference(a)

@@ -360,6 +360,13 @@ __device__ __forceinline__ void partials_wait()
 	asm volatile("bar.sync 2, %0;" ::"n"(EBT_THREADS) : "memory");
 }
 
+// max / min as one compare + select for the leader's chain (fmax/fmin on doubles
+// expand to ~9 instructions and ~25 cycles of dependent latency on sm_100a,
+// measured with tools/micro/fp64_latency.cu).  `d` is the operand that is
+// never NaN; like fmax/fmin the result is `d` when `v` is NaN.
+__device__ __forceinline__ double sel_max(double d, double v) { return v > d ? v : d; }
+__device__ __forceinline__ double sel_min(double d, double v) { return v < d ? v : d; }
+
 // Branch-free reciprocal / reciprocal square root for the leader's chain:
 // MUFU seed (>= 20 bits) + two Newton steps, ~1 ulp, no slow-path call.  The
 // arguments here are normal, finite and non-zero by construction.
@@ -384,7 +391,7 @@ __device__ __forceinline__ double rsqrt_fast(double x)
 // sqrt for x >= 0 (0 -> 0): x * rsqrt(x) with one Heron correction
 __device__ __forceinline__ double sqrt_fast(double x)
 {
-	const double y = rsqrt_fast(fmax(x, DBL_MIN));
+	const double y = rsqrt_fast(sel_max(DBL_MIN, x));
 	const double s = x * y;
 	return fma(fma(-s, s, x), 0.5 * y, s);
 }
@@ -502,8 +509,16 @@ __device__ __forceinline__ double red_total(const FeatShared& sh, int k)
 // sqrt(rho') (residual_block.cc:134-175, corrector.cc:81-110).
 // Returns false when the evaluation is not finite (ResidualBlock::Evaluate's
 // IsArrayValid check).
+struct NoOverlap
+{
+	__device__ __forceinline__ void operator()() const {}
+};
+// `overlap` is scalar work of the leader that does not depend on this
+// evaluation's result; it runs while the pixel warps are busy.
+template <class Overlap = NoOverlap>
 __device__ __forceinline__ bool leader_eval(FeatShared& sh, int kind, const double (&x)[5],
-											double& cost, double (&Hm)[10], double (&g)[4])
+											double& cost, double (&Hm)[10], double (&g)[4],
+											Overlap overlap = Overlap())
 {
 	PHASE_T(t0);
 	double vy, vx;
@@ -513,6 +528,7 @@ __device__ __forceinline__ bool leader_eval(FeatShared& sh, int kind, const doub
 #if !EBT_DEDICATED_LEADER
 	pixel_service(sh);
 #endif
+	overlap();
 	PHASE_T(t2);
 	partials_wait();
 	PHASE_T(t3);
@@ -547,7 +563,7 @@ __device__ __forceinline__ bool leader_eval(FeatShared& sh, int kind, const doub
 	{
 		const double ir = rsqrt_fast(s);
 		rho0 = 2.0 * a * (s * ir) - b;
-		rho1 = fmax(DBL_MIN, a * ir);
+		rho1 = sel_max(DBL_MIN, a * ir);
 	}
 	cost = 0.5 * rho0;
 	bool ok = isfinite(s);
@@ -565,13 +581,8 @@ __device__ __forceinline__ bool leader_eval(FeatShared& sh, int kind, const doub
 		const double kb = rho1 * isq;
 		const double k2 = rho1 * iN * iN * (2.0 - suu * iN);
 		const double kg = rho1 * iN;
-		double chk = 0.0;
 #pragma unroll
-		for (int q = 0; q < 4; ++q)
-		{
-			g[q] = A[q] * k1 + B[q] * kb;
-			chk += g[q];
-		}
+		for (int q = 0; q < 4; ++q) g[q] = A[q] * k1 + B[q] * kb;
 		int k = 0;
 #pragma unroll
 		for (int q = 0; q < 4; ++q)
@@ -580,9 +591,14 @@ __device__ __forceinline__ bool leader_eval(FeatShared& sh, int kind, const doub
 			{
 				const double G = sh.tot[10 + k];
 				Hm[k] = G * kg - A[q] * A[p] * k2;
-				chk += Hm[k];
 			}
-		ok = ok && isfinite(chk);  // any non-finite term poisons the sum
+		// any non-finite term poisons the sum (summed as a shallow tree: this is on
+		// the leader's dependent chain)
+		const double c0 = (g[0] + g[1]) + (g[2] + g[3]);
+		const double c1 = (Hm[0] + Hm[1]) + (Hm[2] + Hm[3]);
+		const double c2 = (Hm[4] + Hm[5]) + (Hm[6] + Hm[7]);
+		const double c3 = Hm[8] + Hm[9];
+		ok = ok && isfinite((c0 + c1) + (c2 + c3));
 	}
 #ifdef EBT_PHASE_CLOCKS
 	{
@@ -743,7 +759,7 @@ __device__ __forceinline__ void scale_system(const double (&x)[5], bool iter0, c
 	if (iter0)
 	{
 #pragma unroll
-		for (int q = 0; q < 4; ++q) scale[q] = rcp_fast(1.0 + sqrt_fast(fmax(Hm[hidx(q, q)], 0.0)));
+		for (int q = 0; q < 4; ++q) scale[q] = rcp_fast(1.0 + sqrt_fast(sel_max(0.0, Hm[hidx(q, q)])));
 	}
 #pragma unroll
 	for (int q = 0; q < 4; ++q)
@@ -764,7 +780,7 @@ __device__ __forceinline__ void scale_system(const double (&x)[5], bool iter0, c
 	plus5(x, ng, xp);
 	double mx = 0;
 #pragma unroll
-	for (int k = 0; k < 5; ++k) mx = fmax(mx, fabs(x[k] - xp[k]));
+	for (int k = 0; k < 5; ++k) mx = sel_max(mx, fabs(x[k] - xp[k]));
 	grad_max_norm = mx;
 }
 
@@ -828,7 +844,7 @@ __device__ void lm_solve(FeatShared& sh, const DevParams& P, double (&params)[5]
 		}
 		else
 			S.n_unsuccessful++;
-		final_cost = fmin(final_cost, iter_cost);
+		final_cost = sel_min(final_cost, iter_cost);
 		if (iteration >= P.max_iterations) break;
 		if (step_successful && iter_gmn <= P.gradient_tolerance) { S.termination = 1; break; }
 		if (radius <= P.min_radius) { S.termination = 1; break; }
@@ -842,7 +858,7 @@ __device__ void lm_solve(FeatShared& sh, const DevParams& P, double (&params)[5]
 		{
 #pragma unroll
 			for (int q = 0; q < 4; ++q)
-				diag[q] = fmin(fmax(Hs[hidx(q, q)], P.min_lm_diagonal), P.max_lm_diagonal);
+				diag[q] = sel_min(P.max_lm_diagonal, sel_max(P.min_lm_diagonal, Hs[hidx(q, q)]));
 		}
 		double d2[4], step[4], delta[4];
 		{
@@ -898,17 +914,23 @@ __device__ void lm_solve(FeatShared& sh, const DevParams& P, double (&params)[5]
 			S.n_cost++;
 		else
 			S.n_jac++;
-		const bool eval_ok = leader_eval(sh, last ? 1 : 2, cand, cand_cost, Hm, g);
+		// |x - cand| (parameter tolerance) and |cand| (x_norm after acceptance) do not
+		// depend on the evaluation: computed while the pixel warps work
+		double step_norm = 0, cand_norm = 0;
+		const bool eval_ok = leader_eval(sh, last ? 1 : 2, cand, cand_cost, Hm, g, [&]() {
+			double d5[5];
+#pragma unroll
+			for (int k = 0; k < 5; ++k) d5[k] = x[k] - cand[k];
+			step_norm = norm5(d5);
+			cand_norm = norm5(cand);
+		});
 		// ComputeCandidatePointAndEvaluateCost: a failed evaluation is an
 		// infinitely bad candidate (trust_region_minimizer.cc:731-747)
 		const bool cost_ok = isfinite(cand_cost);
 		if (!cost_ok) cand_cost = DBL_MAX;
 		{
 			// ParameterToleranceReached
-			double d5[5];
-#pragma unroll
-			for (int k = 0; k < 5; ++k) d5[k] = x[k] - cand[k];
-			if (norm5(d5) <= P.parameter_tolerance * (x_norm + P.parameter_tolerance))
+			if (step_norm <= P.parameter_tolerance * (x_norm + P.parameter_tolerance))
 			{
 				S.termination = 1;
 				break;
@@ -925,8 +947,8 @@ __device__ void lm_solve(FeatShared& sh, const DevParams& P, double (&params)[5]
 		if (!cost_ok)
 			rho = -DBL_MAX;
 		else
-			rho = fmax((se_cur - cand_cost) * rcp_fast(model_cost_change),
-					   (se_ref - cand_cost) * rcp_fast(se_acc_ref + model_cost_change));
+			rho = sel_max((se_cur - cand_cost) * rcp_fast(model_cost_change),
+						  (se_ref - cand_cost) * rcp_fast(se_acc_ref + model_cost_change));
 		if (!(rho > P.min_relative_decrease))
 		{
 			// HandleUnsuccessfulStep
@@ -938,7 +960,7 @@ __device__ void lm_solve(FeatShared& sh, const DevParams& P, double (&params)[5]
 		// HandleSuccessfulStep
 #pragma unroll
 		for (int k = 0; k < 5; ++k) x[k] = cand[k];
-		x_norm = norm5(x);
+		x_norm = cand_norm;
 		if (!eval_ok)
 		{
 			// cost finite, Jacobian not: "Residual and Jacobian evaluation failed"
@@ -950,7 +972,7 @@ __device__ void lm_solve(FeatShared& sh, const DevParams& P, double (&params)[5]
 		if (!last) scale_system(x, false, Hm, g, scale, Hs, gs, P.gradient_tolerance, grad_max_norm);
 		{
 			const double t = 2.0 * rho - 1.0;
-			radius = fmin(P.max_radius, radius * rcp_fast(fmax(1.0 / 3.0, 1.0 - t * t * t)));
+			radius = sel_min(P.max_radius, radius * rcp_fast(sel_max(1.0 / 3.0, 1.0 - t * t * t)));
 		}
 		decrease_factor = 2.0;
 		reuse_diagonal = false;
