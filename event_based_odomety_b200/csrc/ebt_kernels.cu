@@ -65,10 +65,17 @@ constexpr int kPixUnroll = EBT_PIX_UNROLL;
 // Shared memory of one feature CTA
 // --------------------------------------------------------------------------
 // What one pixel evaluation needs besides the evaluation point
+// Side of the square of template-grid texels staged in shared memory per solve:
+// the warped 25x25 patch (+ 3 texels for the 4x4 taps) with ~3 texels of slack on
+// every side for the motion of the iterates.
+#define TS 36
+
 struct EvalCtx
 {
 	const double2* grid;  // (gx, gy) template grid of the patch's frame
 	int W, H;
+	int r0, c0;           // grid texel of tile[0] (may lie outside the image: the tile is clamp-filled)
+	int staged;           // tile holds grid[clamp(r0 + i)][clamp(c0 + j)]
 	double tlx, tly;      // patch top-left
 	double smm;           // sum m^2
 	double huber_a;
@@ -87,6 +94,7 @@ struct __align__(16) FeatShared
 	int res_i[5];              // n_successful, n_unsuccessful, termination, n_jac, n_cost
 	EvalCtx ctx;               // written by thread 0 before the solve
 	double tot[20];            // CTA totals of one evaluation (leader warp)
+	double2 tile[TS * TS];     // staged template-grid texels of the current solve (stage_tile)
 	long long t_last;          // EBT_PHASE_CLOCKS only
 };
 
@@ -267,12 +275,61 @@ __device__ __forceinline__ void sample_taps(const double2* __restrict__ grid, in
 	}
 }
 
+// The same sums from the staged tile: `base` = texel (row - 1, col - 1) in shared
+// memory, row stride TS.  The tile is filled with clamped indices, so it serves
+// interior and border pixels alike; values and operation order are those of the
+// global-memory form => bit-identical.
+template <bool JAC>
+__device__ __forceinline__ void sample_taps_tile(const double2* base, const double (&wr)[4],
+												 const double (&dr)[4], const double (&wc)[4],
+												 const double (&dc)[4], double& g0, double& g1, double& gr0,
+												 double& gr1, double& gc0, double& gc1)
+{
+	g0 = g1 = gr0 = gr1 = gc0 = gc1 = 0;
+#pragma unroll
+	for (int r = 0; r < 4; ++r)
+	{
+		double f0 = 0, f1 = 0, d0 = 0, d1 = 0;
+#pragma unroll
+		for (int j = 0; j < 4; ++j)
+		{
+			const double2 p = base[r * TS + j];
+			f0 += wc[j] * p.x;
+			f1 += wc[j] * p.y;
+			if (JAC)
+			{
+				d0 += dc[j] * p.x;
+				d1 += dc[j] * p.y;
+			}
+		}
+		g0 += wr[r] * f0;
+		g1 += wr[r] * f1;
+		if (JAC)
+		{
+			gr0 += dr[r] * f0;
+			gr1 += dr[r] * f1;
+			gc0 += wr[r] * d0;
+			gc1 += wr[r] * d1;
+		}
+	}
+	g0 *= 0.25;
+	g1 *= 0.25;
+	if (JAC)
+	{
+		gr0 *= 0.25;
+		gr1 *= 0.25;
+		gc0 *= 0.25;
+		gc1 *= 0.25;
+	}
+}
+
 // The 625 pixels are strided over STRIDE threads; `tid` is this thread's index among them.
 template <bool JAC, int STRIDE>
 __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, int W, int H,
 											 const double (&x)[5], double vx, double vy,
 											 double tlx, double tly, const double* m, int tid,
-											 double (&acc)[JAC ? 20 : 2])
+											 double (&acc)[JAC ? 20 : 2], const double2* tile, int r0, int c0,
+											 bool staged)
 {
 	const double cs = x[0], sn = x[1], tx = x[2], ty = x[3];
 #pragma unroll
@@ -291,7 +348,10 @@ __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, in
 		cr_weights<JAC>(wy - fr, wr, dr);
 		cr_weights<JAC>(wx - fc, wc, dc);
 		double g0, g1, gr0, gr1, gc0, gc1;
-		if (row >= 1 && row + 2 < H && col >= 1 && col + 2 < W)
+		const int tr = row - 1 - r0, tc = col - 1 - c0;
+		if (staged && tr >= 0 && tr + 3 < TS && tc >= 0 && tc + 3 < TS)
+			sample_taps_tile<JAC>(tile + tr * TS + tc, wr, dr, wc, dc, g0, g1, gr0, gr1, gc0, gc1);
+		else if (row >= 1 && row + 2 < H && col >= 1 && col + 2 < W)
 			sample_taps<JAC, true>(grid, W, H, row, col, wr, dr, wc, dc, g0, g1, gr0, gr1, gc0, gc1);
 		else
 			sample_taps<JAC, false>(grid, W, H, row, col, wr, dr, wc, dc, g0, g1, gr0, gr1, gc0, gc1);
@@ -460,7 +520,8 @@ __device__ __noinline__ void pixel_service(FeatShared& sh)
 	if (sh.req_kind == 2)
 	{
 		double acc[20];
-		eval_pixels<true, PIX_NT>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, tid, acc);
+		eval_pixels<true, PIX_NT>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, tid, acc, sh.tile, E.r0, E.c0,
+								  E.staged != 0);
 		Butterfly<20, 16>::run(acc, lane);
 		const int slot = butterfly_slot<20>(lane);
 		if (slot >= 0) sh.red[warp][slot] = acc[0];
@@ -468,7 +529,8 @@ __device__ __noinline__ void pixel_service(FeatShared& sh)
 	else
 	{
 		double acc[2];
-		eval_pixels<false, PIX_NT>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, tid, acc);
+		eval_pixels<false, PIX_NT>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, tid, acc, sh.tile, E.r0, E.c0,
+								   E.staged != 0);
 		Butterfly<2, 16>::run(acc, lane);
 		const int slot = butterfly_slot<2>(lane);
 		if (slot >= 0) sh.red[warp][slot] = acc[0];
@@ -1099,7 +1161,8 @@ __device__ __noinline__ void cost_map(FeatShared& sh, double w0, double w1, doub
 		x[2] = (double)ox + w2;
 		x[3] = (double)oy + w3;
 		double acc[2];
-		eval_pixels<false, NT>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, (int)threadIdx.x, acc);
+		eval_pixels<false, NT>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, sh.m, (int)threadIdx.x, acc, sh.tile, E.r0,
+							   E.c0, E.staged != 0);
 		block_sum<2>(sh, acc);
 		if (threadIdx.x == 0)
 		{
@@ -1138,12 +1201,56 @@ __device__ EBT_NOINLINE void optimize_feature(FeatShared& sh, double* costs, Fea
 	}
 	block_sum<1>(sh, a1);
 
+	// Stage the template-grid texels the solve will sample: the bounding box of the
+	// rect warped by the initial estimate, + the 4x4 tap footprint, centred in a
+	// TS x TS tile.  Pixels whose taps leave the tile later (or a box that does not
+	// fit: large rotation) read global memory as before.
+	int r0 = 0, c0 = 0, staged = 0;
+	{
+		const double c = st.warp[0], s = st.warp[1], tx = st.warp[2], ty = st.warp[3];
+		double lox = DBL_MAX, hix = -DBL_MAX, loy = DBL_MAX, hiy = -DBL_MAX;
+#pragma unroll
+		for (int k = 0; k < 4; ++k)
+		{
+			const double px = st.rx + ((k & 1) ? SIDE - 1 : 0), py = st.ry + ((k & 2) ? SIDE - 1 : 0);
+			const double wx = c * px - s * py + tx, wy = s * px + c * py + ty;
+			lox = wx < lox ? wx : lox;
+			hix = wx > hix ? wx : hix;
+			loy = wy < loy ? wy : loy;
+			hiy = wy > hiy ? wy : hiy;
+		}
+		if (lox > -1e6 && hix < 1e6 && loy > -1e6 && hiy < 1e6)  // also false for NaN
+		{
+			const int cl = (int)floor(lox) - 1, ch = (int)floor(hix) + 2;
+			const int rl = (int)floor(loy) - 1, rh = (int)floor(hiy) + 2;
+			if (ch - cl < TS && rh - rl < TS)
+			{
+				c0 = cl - (TS - (ch - cl + 1)) / 2;
+				r0 = rl - (TS - (rh - rl + 1)) / 2;
+				staged = 1;
+			}
+		}
+	}
+	if (staged)
+	{
+		const double2* grid = ft.grid[st.frame_slot];
+		const int W = P.width, H = P.height;
+		for (int idx = threadIdx.x; idx < TS * TS; idx += NT)
+		{
+			const int i = idx / TS, j = idx - i * TS;
+			const int rr = min(max(r0 + i, 0), H - 1), cc = min(max(c0 + j, 0), W - 1);
+			sh.tile[idx] = __ldg(grid + rr * W + cc);
+		}
+	}
 	if (threadIdx.x == 0)
 	{
 		EvalCtx& E = sh.ctx;
 		E.grid = ft.grid[st.frame_slot];
 		E.W = P.width;
 		E.H = P.height;
+		E.r0 = r0;
+		E.c0 = c0;
+		E.staged = staged;
 		E.tlx = st.rx;
 		E.tly = st.ry;
 		E.smm = a1[0];

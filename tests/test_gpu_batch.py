@@ -94,3 +94,47 @@ def test_batch_border_patches():
     assert dpos[ok].max() <= POS_TOL_PX
     assert _angle_diff_deg(osol["flow_dir"][ok], gsol["flow_dir"][ok]).max() <= ANGLE_TOL_DEG
     assert same_path.mean() >= 0.99
+
+
+@pytest.mark.gpu
+def test_batch_tile_fallbacks():
+    """The solve samples the template grid from a 36x36 shared-memory tile staged around the initial
+    estimate; two families of problems that leave it: (a) rotations of 25-60 degrees (the warped rect's
+    bounding box does not fit: nothing is staged), (b) initial estimates displaced by ~8 px in the template
+    (the iterates walk out of the tile: per-pixel fallback to global memory).  Same gates as everywhere."""
+    w, h = 240, 180
+    ps = synth.make_problems(192, w, h, seed=4711, border=45)
+    pr = ps.problems.copy()
+    rng = np.random.Generator(np.random.PCG64(5))
+    for k in range(len(pr)):
+        c, s, tx, ty = pr["warp"][k]
+        init = np.array([pr["init_x"][k], pr["init_y"][k]])
+        R = np.array([[c, -s], [s, c]])
+        ctr = R.T @ (init - np.array([tx, ty]))  # Patch::updatePatchRect: centre = warp^-1 * initPoint
+        if k % 2 == 0:
+            th = np.arctan2(s, c) + np.deg2rad(rng.uniform(25, 60)) * rng.choice([-1, 1])
+            R2 = np.array([[np.cos(th), -np.sin(th)], [np.sin(th), np.cos(th)]])
+            t2 = init - R2 @ ctr  # same centre, so the window's events stay in the rect
+            pr["warp"][k] = [np.cos(th), np.sin(th), t2[0], t2[1]]
+        else:
+            d = rng.uniform(5, 8, size=2) * rng.choice([-1, 1], size=2)
+            pr["init_x"][k] += d[0]
+            pr["init_y"][k] += d[1]
+            pr["warp"][k] = [c, s, tx + d[0], ty + d[1]]  # same centre, template sampled d away
+    ob = CpuBatch(load_oracle(), w, h)
+    tr = Tracker(w, h)
+    ob.add_frame(ps.frames[0]); tr.add_frame(ps.frames[0])
+    osol, onab, _, _ = ob.optimize(pr, ps.events)
+    gsol, gnab = tr.optimize_batch(pr, ps.events)
+    tr.close()
+    assert np.array_equal(onab.astype(np.int32), gnab)
+    assert np.abs(onab).sum(axis=1).min() > 0  # every window contributes: no trivial FAILURE cases
+    same_path = ((osol["n_successful"] == gsol["n_successful"])
+                 & (osol["n_unsuccessful"] == gsol["n_unsuccessful"])
+                 & (osol["termination"] == gsol["termination"]))
+    dpos = np.hypot(osol["x"] - gsol["x"], osol["y"] - gsol["y"])
+    print(f"\n[tile fallbacks] max dpos {dpos.max():.3e} px, same LM path {same_path.mean():.4f}, "
+          f"rejected steps in {np.count_nonzero(osol['n_unsuccessful'])} solves")
+    assert dpos.max() <= POS_TOL_PX
+    assert _angle_diff_deg(osol["flow_dir"], gsol["flow_dir"]).max() <= ANGLE_TOL_DEG
+    assert same_path.mean() >= 0.99
