@@ -1653,7 +1653,13 @@ __device__ __forceinline__ void window_grow(FeatState& st, int take)
 	st.counter += take;
 }
 
-__global__ void __launch_bounds__(NT, EBT_MIN_CTAS)
+// MINCTAS = resident CTAs per SM the register budget is cut for.  The launcher
+// matches it to the launch: with at most one (two) feature(s) per SM the build
+// with 255 (192) registers runs — every value of the pixel pass and most of the
+// LM state in registers, no spill traffic on the serial chain — and the
+// EBT_MIN_CTAS build (128 registers) when the features outnumber that.
+template <int MINCTAS>
+__global__ void __launch_bounds__(NT, MINCTAS)
 track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __restrict__ order,
 				   ebt_event* __restrict__ rings, int* __restrict__ nablas,
 				   const ebt_event* __restrict__ events, long long n_events,
@@ -1857,7 +1863,8 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 // Batched kernel: F independent feature-patch problems, one CTA each — one
 // Optimizer::optimize (ft/src/optimizer.cpp:62-206) per problem.
 // --------------------------------------------------------------------------
-__global__ void __launch_bounds__(NT, EBT_MIN_CTAS)
+template <int MINCTAS>  // register budget matched to the launch, as for track_batch_kernel
+__global__ void __launch_bounds__(NT, MINCTAS)
 optimize_batch_kernel(const ebt_problem* __restrict__ problems, int n_problems,
 					  const ebt_event* __restrict__ events, FrameTable ft, DevParams P,
 					  ebt_solution* __restrict__ solutions, int* __restrict__ nablas)
@@ -1988,6 +1995,19 @@ __global__ void fma_peak_kernel(T* out, int iters, T a, T b)
 }
 }  // namespace
 
+// multiprocessors of the current device (every device of a box is the same part)
+static int device_sm_count()
+{
+	static int sm_count = 0;
+	if (!sm_count)
+	{
+		int dev = 0;
+		cudaGetDevice(&dev);
+		cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
+	}
+	return sm_count;
+}
+
 cudaError_t ebt_launch_fma_peak(int fp64, void* out, int blocks, int threads, int iters,
 								cudaStream_t stream)
 {
@@ -2014,9 +2034,18 @@ cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, const int* 
 					   (unsigned)((n_patches + PF_FEATS - 1) / PF_FEATS));
 	prefilter_kernel<<<pf_grid, PF_THREADS, 0, stream>>>(patches, n_patches, events, n_events, margin,
 														  mask, words_per_row);
-	track_batch_kernel<<<n_patches, NT, 0, stream>>>(patches, n_patches, order, rings, nablas, events,
-													 n_events, event_base, mask, words_per_row,
-													 margin, ft, P, records, n_records, record_cap);
+	const int sm_count = device_sm_count();
+#define EBT_TRACK_LAUNCH(M)                                                                                 \
+	track_batch_kernel<M><<<n_patches, NT, 0, stream>>>(patches, n_patches, order, rings, nablas, events,  \
+														n_events, event_base, mask, words_per_row, margin, \
+														ft, P, records, n_records, record_cap)
+	if (n_patches <= sm_count)
+		EBT_TRACK_LAUNCH(1);
+	else if (n_patches <= 2 * sm_count && EBT_MIN_CTAS > 2)
+		EBT_TRACK_LAUNCH(2);
+	else
+		EBT_TRACK_LAUNCH(EBT_MIN_CTAS);
+#undef EBT_TRACK_LAUNCH
 	return cudaGetLastError();
 }
 
@@ -2032,8 +2061,14 @@ cudaError_t ebt_launch_optimize_batch(const ebt_problem* problems, int n_problem
 									  cudaStream_t stream)
 {
 	if (n_problems <= 0) return cudaSuccess;
-	optimize_batch_kernel<<<n_problems, NT, 0, stream>>>(problems, n_problems, events, ft, P,
-														 solutions, nablas);
+	const int sm_count = device_sm_count();
+	if (n_problems <= sm_count)
+		optimize_batch_kernel<1><<<n_problems, NT, 0, stream>>>(problems, n_problems, events, ft, P, solutions, nablas);
+	else if (n_problems <= 2 * sm_count && EBT_MIN_CTAS > 2)
+		optimize_batch_kernel<2><<<n_problems, NT, 0, stream>>>(problems, n_problems, events, ft, P, solutions, nablas);
+	else
+		optimize_batch_kernel<EBT_MIN_CTAS><<<n_problems, NT, 0, stream>>>(problems, n_problems, events, ft, P,
+																		solutions, nablas);
 	return cudaGetLastError();
 }
 

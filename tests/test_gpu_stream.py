@@ -99,6 +99,14 @@ def test_stream_c2_shape():
 
 
 @pytest.mark.gpu
+def test_stream_two_features_per_sm_build():
+    """149-296 live patches on a 148-SM device select the 2-CTAs-per-SM build of the stream kernel
+    (<= 148 the 1-CTA build: the c1 tests above; more the 3-CTA build: the c2 / c3 tests)."""
+    S = synth.make_stream(346, 260, 0.10, 2e6, seed=1042, max_corners=240)
+    compare(S, 240)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("margin", [0.0, 0.5, 64.0])
 def test_stream_prefilter_margin(margin):
     """The prefilter is an index, not a filter: results must not depend on how
