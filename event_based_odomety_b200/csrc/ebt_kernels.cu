@@ -15,6 +15,7 @@
 #include <cuda_runtime.h>
 #include <float.h>
 #include <math.h>
+#include <stdlib.h>
 
 #include "ebt_device_types.h"
 #include "ebt_kernels.h"
@@ -83,6 +84,7 @@ struct EvalCtx
 
 struct __align__(16) FeatShared
 {
+	static constexpr int kPixWarps = (EBT_THREADS / 32) - (EBT_DEDICATED_LEADER ? 1 : 0);
 	ebt_event ring[EBT_RING];  // Patch::events_
 	double m[NPIX];            // normalised integrated patch (patch.cpp:156-159)
 	int nabla[NPIX];           // Patch::integratedNabla_, integer valued
@@ -537,6 +539,8 @@ __device__ __noinline__ void pixel_service(FeatShared& sh)
 	}
 }
 
+__device__ __forceinline__ void leader_pixels(FeatShared& sh) { pixel_service(sh); }
+
 __device__ void lm_worker(FeatShared& sh)
 {
 	for (;;)
@@ -549,14 +553,16 @@ __device__ void lm_worker(FeatShared& sh)
 }
 
 // CTA total of reduced value k: pairwise over the per-warp partials
-__device__ __forceinline__ double red_total(const FeatShared& sh, int k)
+template <class SH>
+__device__ __forceinline__ double red_total(const SH& sh, int k)
 {
-	static_assert((PIX_NW & (PIX_NW - 1)) == 0, "pairwise tree over the pixel warps");
-	double v[PIX_NW];
+	constexpr int PW = SH::kPixWarps;
+	static_assert((PW & (PW - 1)) == 0, "pairwise tree over the pixel warps");
+	double v[PW];
 #pragma unroll
-	for (int w = 0; w < PIX_NW; ++w) v[w] = sh.red[w][k];
+	for (int w = 0; w < PW; ++w) v[w] = sh.red[w][k];
 #pragma unroll
-	for (int n = PIX_NW; n > 1; n >>= 1)
+	for (int n = PW; n > 1; n >>= 1)
 #pragma unroll
 		for (int w = 0; w < n / 2; ++w) v[w] = v[2 * w] + v[2 * w + 1];
 	return v[0];
@@ -577,8 +583,9 @@ struct NoOverlap
 };
 // `overlap` is scalar work of the leader that does not depend on this
 // evaluation's result; it runs while the pixel warps are busy.
-template <class Overlap = NoOverlap>
-__device__ __forceinline__ bool leader_eval(FeatShared& sh, int kind, const double (&x)[5],
+__device__ __forceinline__ void wait_partials(FeatShared&) { partials_wait(); }
+template <class SH, class Overlap = NoOverlap>
+__device__ __forceinline__ bool leader_eval(SH& sh, int kind, const double (&x)[5],
 											double& cost, double (&Hm)[10], double (&g)[4],
 											Overlap overlap = Overlap())
 {
@@ -588,11 +595,11 @@ __device__ __forceinline__ bool leader_eval(FeatShared& sh, int kind, const doub
 	post_request(sh, kind, x, vx, vy);
 	PHASE_T(t1);
 #if !EBT_DEDICATED_LEADER
-	pixel_service(sh);
+	leader_pixels(sh);
 #endif
 	overlap();
 	PHASE_T(t2);
-	partials_wait();
+	wait_partials(sh);
 	PHASE_T(t3);
 	PHASE_ADD(0, t0, t1);
 	PHASE_ADD(1, t1, t2);
@@ -858,7 +865,8 @@ __device__ __forceinline__ void scale_system(const double (&x)[5], bool iter0, c
 // iteration limit needs no Jacobian (the limit is tested before the gradient),
 // so it is evaluated cost-only.  params is updated to the lowest-cost accepted
 // iterate, or left alone on FAILURE (solver.cc:428-432).
-__device__ void lm_solve(FeatShared& sh, const DevParams& P, double (&params)[5], LmSummary& S)
+template <class SH>
+__device__ void lm_solve(SH& sh, const DevParams& P, double (&params)[5], LmSummary& S)
 {
 	double x[5], cand[5], best[5];
 	double Hm[10], g[4];
@@ -1863,6 +1871,339 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 // Batched kernel: F independent feature-patch problems, one CTA each — one
 // Optimizer::optimize (ft/src/optimizer.cpp:62-206) per problem.
 // --------------------------------------------------------------------------
+
+// --------------------------------------------------------------------------
+// Batched kernel, shared pixel warps: SB_LEADERS leader warps — one feature-patch
+// problem each at a time — share ONE set of SB_PIXW pixel warps.  While one
+// leader runs its scalar trust-region step, the pixel warps evaluate a sibling's
+// request, so they stay busy (in the one-CTA-per-feature kernels a feature's four
+// pixel warps idle through its scalar half).  ~12 k registers per feature
+// instead of 20 k.  Measured on 65 536 problems (profiles/r1_variants.md): 2 leaders
+// + 4 pixel warps at 170 registers, 2 CTAs per SM (4 problems in flight per SM)
+// is the fastest shape, +18 % over one CTA per problem; 3 or 4 leaders per pixel
+// set fall to 128-144 registers and lose more to spills than they gain.
+// The window, integration, normalisation
+// and post-solve of a problem run on its leader warp alone; the pixel passes and
+// the tile staging are posted as jobs.
+//
+// Hand-off without barriers: a leader writes its request, then bumps
+// slot.req_seq; every pixel warp serves every job (its 32 of the 128 pixel
+// threads' share) in the order it discovers them and bumps slot.done_cnt; the
+// leader spins until done_cnt == SB_PIXW * req_seq.  A leader has at most one job
+// in flight, so the pixel warps need not agree on an order.
+// --------------------------------------------------------------------------
+#ifndef SB_LEADERS
+#define SB_LEADERS 2
+#endif
+#ifndef SB_SLEEP
+#define SB_SLEEP 0  // ns of back-off per poll; plain spinning measured as fast
+#endif
+#define SB_BACKOFF() do { if (SB_SLEEP > 0) __nanosleep(SB_SLEEP); } while (0)
+#ifndef SB_PIXW
+#define SB_PIXW 4
+#endif
+#ifndef SB_CTAS
+#define SB_CTAS 2
+#endif
+#define SB_THREADS ((SB_LEADERS + SB_PIXW) * 32)
+#define SB_RING 304  // >= Patch::maxNumOfEvents_
+#ifndef SB_TILE
+#define SB_TILE 1
+#endif
+
+struct __align__(16) SlotShared
+{
+	static constexpr int kPixWarps = SB_PIXW;
+	ebt_event ring[SB_RING];  // the problem's window, chronological
+#if SB_TILE
+	double2 tile[TS * TS];
+#else
+	double2 tile[1];          // taps through L1
+#endif
+	double m[NPIX];
+	int nabla[NPIX];
+	double red[SB_PIXW][20];
+	double req[8];
+	double tot[20];
+	EvalCtx ctx;
+	int req_kind;             // 1 cost-only pass, 2 cost + Jacobian pass, 3 stage the tile, 4 leader has finished
+	unsigned req_seq;         // jobs posted so far (written by the leader)
+	unsigned done_cnt;        // pixel-warp completions (SB_PIXW per job)
+	unsigned seq_local;       // leader's own copy of req_seq
+	long long t_last;         // EBT_PHASE_CLOCKS only
+};
+
+__device__ __forceinline__ unsigned ld_volatile_u32(const unsigned* p) { return *(const volatile unsigned*)p; }
+
+__device__ __forceinline__ void sb_post(SlotShared& S)
+{
+	__syncwarp();
+	if ((threadIdx.x & 31) == 0)
+	{
+		__threadfence_block();  // request data before the sequence number
+		*(volatile unsigned*)&S.req_seq = ++S.seq_local;
+	}
+	__syncwarp();
+}
+__device__ __forceinline__ void wait_partials(SlotShared& S)
+{
+	const unsigned want = S.seq_local * SB_PIXW;
+	while (ld_volatile_u32(&S.done_cnt) != want) SB_BACKOFF();
+	__threadfence_block();
+	__syncwarp();
+}
+__device__ __forceinline__ void post_request(SlotShared& S, int kind, const double (&x)[5], double vx, double vy)
+{
+	if ((threadIdx.x & 31) == 0)
+	{
+#pragma unroll
+		for (int k = 0; k < 5; ++k) S.req[k] = x[k];
+		S.req[5] = vx;
+		S.req[6] = vy;
+		S.req_kind = kind;
+	}
+	sb_post(S);
+}
+
+// One job of slot S on this pixel warp (ptid = index among the 128 pixel threads).
+__device__ __noinline__ void sb_serve(SlotShared& S, int kind, int ptid)
+{
+	const int lane = ptid & 31, pw = ptid >> 5;
+	const EvalCtx& E = S.ctx;
+	if (kind == 3)
+	{
+		for (int idx = ptid; idx < TS * TS; idx += SB_PIXW * 32)
+		{
+			const int i = idx / TS, j = idx - i * TS;
+			const int rr = min(max(E.r0 + i, 0), E.H - 1), cc = min(max(E.c0 + j, 0), E.W - 1);
+			S.tile[idx] = __ldg(E.grid + rr * E.W + cc);
+		}
+		return;
+	}
+	double x[5];
+#pragma unroll
+	for (int k = 0; k < 5; ++k) x[k] = S.req[k];
+	const double vx = S.req[5], vy = S.req[6];
+	if (kind == 2)
+	{
+		double acc[20];
+		eval_pixels<true, SB_PIXW * 32>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, S.m, ptid, acc, S.tile, E.r0, E.c0,
+										  E.staged != 0);
+		Butterfly<20, 16>::run(acc, lane);
+		const int slot = butterfly_slot<20>(lane);
+		if (slot >= 0) S.red[pw][slot] = acc[0];
+	}
+	else
+	{
+		double acc[2];
+		eval_pixels<false, SB_PIXW * 32>(E.grid, E.W, E.H, x, vx, vy, E.tlx, E.tly, S.m, ptid, acc, S.tile, E.r0, E.c0,
+										   E.staged != 0);
+		Butterfly<2, 16>::run(acc, lane);
+		const int slot = butterfly_slot<2>(lane);
+		if (slot >= 0) S.red[pw][slot] = acc[0];
+	}
+}
+
+// One Optimizer::optimize of problem `pr` on a leader warp (32 lanes), slot S.
+__device__ void sb_optimize(SlotShared& S, const ebt_problem& pr, const ebt_event* __restrict__ events,
+							const FrameTable& ft, const DevParams& P, ebt_solution& out, int* __restrict__ nab_out)
+{
+	const int lane = threadIdx.x & 31;
+	FeatState st;
+	st.ix = pr.init_x;
+	st.iy = pr.init_y;
+#pragma unroll
+	for (int k = 0; k < 4; ++k) st.warp[k] = pr.warp[k];
+	st.flow = pr.flow_dir;
+	st.cur_ts = st.time_last_update = 0;
+	st.time_without_update = 10000000;
+	st.init = 1;
+	st.lost = 0;
+	st.num_of_events = min(max(pr.n_events, P.min_num_events), P.max_num_events);
+	st.size = min(pr.n_events, st.num_of_events);
+	st.counter = pr.n_events;
+	st.tail = 0;
+	st.n_costs = 0;
+	st.n_traj = 0;
+	st.frame_slot = pr.frame_slot;
+	st.rx = st.ry = 0;
+	update_rect(st);
+	// window given newest first; ring is chronological
+	const uint4* ev4 = reinterpret_cast<const uint4*>(events + pr.event_offset);
+	for (int k = lane; k < st.size; k += 32) *reinterpret_cast<uint4*>(&S.ring[k]) = __ldg(ev4 + (st.size - 1 - k));
+	for (int i = lane; i < NPIX; i += 32) S.nabla[i] = 0;
+	__syncwarp();
+	// Patch::integrateEvents (patch.cpp:65-84), as integrate_window
+	for (int k = lane; k < st.size; k += 32)
+	{
+		const ebt_event e = S.ring[k];
+		if (in_rect(st.rx, st.ry, e.x, e.y))
+		{
+			const int px = (int)(e.x - st.rx), py = (int)(e.y - st.ry);
+			atomicAdd(&S.nabla[py * SIDE + px], (int)e.polarity);
+		}
+	}
+	{
+		const long long front = S.ring[st.size - 1].t_us, back = S.ring[0].t_us;
+		st.cur_ts = to_i32((double)(front + back) * 0.5);
+		st.time_last_update = to_i32((double)back);
+	}
+	__syncwarp();
+	// Patch::getNormalizedIntegratedNabla (patch.cpp:156-159)
+	double a = 0;
+	for (int i = lane; i < NPIX; i += 32)
+	{
+		const double v = (double)S.nabla[i];
+		a += v * v;
+	}
+	a = warp_sum(a);
+	const double inv = 1.0 / sqrt(a);
+	double smm = 0;
+	for (int i = lane; i < NPIX; i += 32)
+	{
+		const double v = (double)S.nabla[i] * inv;
+		S.m[i] = v;
+		smm += v * v;
+	}
+	smm = warp_sum(smm);
+	// tile origin: as in optimize_feature
+	int r0 = 0, c0 = 0, staged = 0;
+	{
+		const double c = st.warp[0], s = st.warp[1], tx = st.warp[2], ty = st.warp[3];
+		double lox = DBL_MAX, hix = -DBL_MAX, loy = DBL_MAX, hiy = -DBL_MAX;
+#pragma unroll
+		for (int k = 0; k < 4; ++k)
+		{
+			const double px = st.rx + ((k & 1) ? SIDE - 1 : 0), py = st.ry + ((k & 2) ? SIDE - 1 : 0);
+			const double wx = c * px - s * py + tx, wy = s * px + c * py + ty;
+			lox = wx < lox ? wx : lox;
+			hix = wx > hix ? wx : hix;
+			loy = wy < loy ? wy : loy;
+			hiy = wy > hiy ? wy : hiy;
+		}
+		if (SB_TILE && lox > -1e6 && hix < 1e6 && loy > -1e6 && hiy < 1e6)
+		{
+			const int cl = (int)floor(lox) - 1, ch = (int)floor(hix) + 2;
+			const int rl = (int)floor(loy) - 1, rh = (int)floor(hiy) + 2;
+			if (ch - cl < TS && rh - rl < TS)
+			{
+				c0 = cl - (TS - (ch - cl + 1)) / 2;
+				r0 = rl - (TS - (rh - rl + 1)) / 2;
+				staged = 1;
+			}
+		}
+	}
+	if (lane == 0)
+	{
+		EvalCtx& E = S.ctx;
+		E.grid = ft.grid[st.frame_slot];
+		E.W = P.width;
+		E.H = P.height;
+		E.r0 = r0;
+		E.c0 = c0;
+		E.staged = staged;
+		E.tlx = st.rx;
+		E.tly = st.ry;
+		E.smm = smm;
+		E.huber_a = P.huber_a;
+		S.req_kind = 3;
+	}
+	if (staged)
+	{
+		sb_post(S);
+		wait_partials(S);
+	}
+	double x[5] = {st.warp[0], st.warp[1], st.warp[2], st.warp[3], (double)__double2float_rn(st.flow)};
+	LmSummary L;
+	L.filtered = 0;
+	lm_solve(S, P, x, L);
+	// post-solve (optimizer.cpp:127-189); one final cost => the cost filter cannot fire
+	st.flow = fmod(x[4], 2 * 3.14159265358979323846);
+#pragma unroll
+	for (int k = 0; k < 4; ++k) st.warp[k] = x[k];
+	update_rect(st);
+	if (nab_out)
+		for (int i = lane; i < NPIX; i += 32) nab_out[i] = S.nabla[i];
+	if (lane == 0)
+	{
+		ebt_solution s;
+#pragma unroll
+		for (int k = 0; k < 4; ++k) s.warp[k] = st.warp[k];
+		s.flow_dir = (double)__double2float_rn(st.flow);
+		s.final_cost = L.final_cost;
+		s.x = st.rx + (SIDE - 1) / 2.;
+		s.y = st.ry + (SIDE - 1) / 2.;
+		s.n_successful = L.n_successful;
+		s.n_unsuccessful = L.n_unsuccessful;
+		s.termination = L.termination;
+		s.n_passes = L.n_jac * 100 + L.n_cost;
+		s.ts = st.cur_ts;
+		out = s;
+	}
+	__syncwarp();
+}
+
+#ifdef SB_MAXNREG
+__global__ void __maxnreg__(SB_MAXNREG)
+#else
+__global__ void __launch_bounds__(SB_THREADS, SB_CTAS)
+#endif
+optimize_batch_shared_kernel(const ebt_problem* __restrict__ problems, int n_problems,
+							 const ebt_event* __restrict__ events, FrameTable ft, DevParams P,
+							 ebt_solution* __restrict__ solutions, int* __restrict__ nablas)
+{
+	extern __shared__ __align__(16) unsigned char sb_raw[];
+	SlotShared* slots = reinterpret_cast<SlotShared*>(sb_raw);
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	if (threadIdx.x < SB_LEADERS)
+	{
+		slots[threadIdx.x].req_seq = 0;
+		slots[threadIdx.x].done_cnt = 0;
+		slots[threadIdx.x].seq_local = 0;
+		slots[threadIdx.x].t_last = 0;
+	}
+	__syncthreads();
+	if (warp < SB_LEADERS)
+	{
+		SlotShared& S = slots[warp];
+		for (int b = blockIdx.x * SB_LEADERS + warp; b < n_problems; b += gridDim.x * SB_LEADERS)
+			sb_optimize(S, problems[b], events, ft, P, solutions[b], nablas ? nablas + (size_t)b * NPIX : nullptr);
+		if (lane == 0) S.req_kind = 4;
+		sb_post(S);
+		return;
+	}
+	const int ptid = threadIdx.x - SB_LEADERS * 32;
+	unsigned served[SB_LEADERS];
+#pragma unroll
+	for (int l = 0; l < SB_LEADERS; ++l) served[l] = 0;
+	int exited = 0;
+	while (exited < SB_LEADERS)
+	{
+		bool idle = true;
+#pragma unroll
+		for (int l = 0; l < SB_LEADERS; ++l)
+		{
+			SlotShared& S = slots[l];
+			const unsigned seq = __shfl_sync(0xffffffffu, ld_volatile_u32(&S.req_seq), 0);
+			if (seq == served[l]) continue;
+			served[l] = seq;
+			idle = false;
+			__threadfence_block();  // the request behind the sequence number
+			const int kind = *(const volatile int*)&S.req_kind;
+			if (kind == 4)
+			{
+				++exited;
+				continue;
+			}
+			sb_serve(S, kind, ptid);
+			__threadfence_block();
+			__syncwarp();
+			if (lane == 0) atomicAdd(&S.done_cnt, 1u);
+		}
+		if (idle) SB_BACKOFF();
+	}
+}
+
 template <int MINCTAS>  // register budget matched to the launch, as for track_batch_kernel
 __global__ void __launch_bounds__(NT, MINCTAS)
 optimize_batch_kernel(const ebt_problem* __restrict__ problems, int n_problems,
@@ -2039,9 +2380,11 @@ cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, const int* 
 	track_batch_kernel<M><<<n_patches, NT, 0, stream>>>(patches, n_patches, order, rings, nablas, events,  \
 														n_events, event_base, mask, words_per_row, margin, \
 														ft, P, records, n_records, record_cap)
-	if (n_patches <= sm_count)
+	static const int forced = getenv("EBT_STREAM_BUILD") ? atoi(getenv("EBT_STREAM_BUILD")) : 0;  // tuning only
+	const int build = forced ? forced : (n_patches <= sm_count ? 1 : (n_patches <= 2 * sm_count ? 2 : 3));
+	if (build == 1)
 		EBT_TRACK_LAUNCH(1);
-	else if (n_patches <= 2 * sm_count && EBT_MIN_CTAS > 2)
+	else if (build == 2 && EBT_MIN_CTAS > 2)
 		EBT_TRACK_LAUNCH(2);
 	else
 		EBT_TRACK_LAUNCH(EBT_MIN_CTAS);
@@ -2062,6 +2405,25 @@ cudaError_t ebt_launch_optimize_batch(const ebt_problem* problems, int n_problem
 {
 	if (n_problems <= 0) return cudaSuccess;
 	const int sm_count = device_sm_count();
+	// many problems: the shared-pixel-warp kernel (6 problems in flight per SM); the cost map
+	// needs the whole CTA per problem and stays on the one-CTA-per-problem kernel
+	static const int shared_on = getenv("EBT_BATCH_SHARED") ? atoi(getenv("EBT_BATCH_SHARED")) : 1;
+	if (shared_on && !P.cost_maps && n_problems > 4 * sm_count)
+	{
+		static bool attr_set = false;
+		const size_t smem = SB_LEADERS * sizeof(SlotShared);
+		if (!attr_set)
+		{
+			cudaError_t e = cudaFuncSetAttribute(optimize_batch_shared_kernel,
+												 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+			if (e != cudaSuccess) return e;
+			attr_set = true;
+		}
+		const int ctas = min((n_problems + SB_LEADERS - 1) / SB_LEADERS, SB_CTAS * sm_count);
+		optimize_batch_shared_kernel<<<ctas, SB_THREADS, smem, stream>>>(problems, n_problems, events, ft, P,
+																		 solutions, nablas);
+		return cudaGetLastError();
+	}
 	if (n_problems <= sm_count)
 		optimize_batch_kernel<1><<<n_problems, NT, 0, stream>>>(problems, n_problems, events, ft, P, solutions, nablas);
 	else if (n_problems <= 2 * sm_count && EBT_MIN_CTAS > 2)

@@ -138,3 +138,46 @@ def test_batch_tile_fallbacks():
     assert dpos.max() <= POS_TOL_PX
     assert _angle_diff_deg(osol["flow_dir"], gsol["flow_dir"]).max() <= ANGLE_TOL_DEG
     assert same_path.mean() >= 0.99
+
+
+@pytest.mark.gpu
+def test_batch_shared_pixel_warp_kernel_edges():
+    """More than 4 problems per SM select the shared-pixel-warp kernel (two leader warps share four pixel
+    warps).  Border patches (clamped tile), an empty-in-rect window (NaN patch -> FAILURE) and the rotated /
+    displaced problems that leave the tile, all inside one batch of 1200."""
+    w, h = 240, 180
+    ps = synth.make_problems(1200, w, h, seed=8123, border=2)
+    pr, ev = ps.problems.copy(), ps.events.copy()
+    p0 = pr[7]
+    sl = slice(p0["event_offset"], p0["event_offset"] + p0["n_events"])
+    ev["x"][sl] = 0
+    ev["y"][sl] = 0
+    rng = np.random.Generator(np.random.PCG64(9))
+    for k in range(100, 400):  # rotate about the unchanged centre: nothing staged
+        c, s_, tx, ty = pr["warp"][k]
+        init = np.array([pr["init_x"][k], pr["init_y"][k]])
+        R = np.array([[c, -s_], [s_, c]])
+        ctr = R.T @ (init - np.array([tx, ty]))
+        th = np.arctan2(s_, c) + np.deg2rad(rng.uniform(25, 60)) * rng.choice([-1, 1])
+        R2 = np.array([[np.cos(th), -np.sin(th)], [np.sin(th), np.cos(th)]])
+        t2 = init - R2 @ ctr
+        pr["warp"][k] = [np.cos(th), np.sin(th), t2[0], t2[1]]
+    ob = CpuBatch(load_oracle(), w, h)
+    tr = Tracker(w, h)
+    ob.add_frame(ps.frames[0]); tr.add_frame(ps.frames[0])
+    osol, onab, _, _ = ob.optimize(pr, ev)
+    gsol, gnab = tr.optimize_batch(pr, ev)
+    tr.close()
+    assert np.array_equal(onab.astype(np.int32), gnab)
+    assert osol["termination"][7] == 2 and gsol["termination"][7] == 2 and gsol["final_cost"][7] == -1.0
+    ok = np.isfinite(osol["x"])
+    assert np.array_equal(ok, np.isfinite(gsol["x"]))
+    assert np.array_equal(osol["ts"], gsol["ts"])
+    dpos = np.hypot(osol["x"] - gsol["x"], osol["y"] - gsol["y"])[ok]
+    same_path = ((osol["n_successful"] == gsol["n_successful"])
+                 & (osol["n_unsuccessful"] == gsol["n_unsuccessful"])
+                 & (osol["termination"] == gsol["termination"]))
+    print(f"\n[shared kernel edges] max dpos {dpos.max():.3e} px, same LM path {same_path.mean():.4f}")
+    assert dpos.max() <= POS_TOL_PX
+    assert _angle_diff_deg(osol["flow_dir"][ok], gsol["flow_dir"][ok]).max() <= ANGLE_TOL_DEG
+    assert same_path.mean() >= 0.99
