@@ -57,6 +57,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--duration", type=float, default=0.30, help="stream seconds per step")
+    ap.add_argument("--stream-kernel", type=int, default=0, choices=[0, 1],
+                    help="ebt_set_stream_kernel: 0 one CTA per feature, 1 two features per CTA sharing its pixel warps")
     ap.add_argument("--streams", type=int, default=1,
                     help="independent streams tracked concurrently per GPU (configs[3] throughput mode)")
     ap.add_argument("--cpu-frames", type=int, default=2, help="frames of the stream in the CPU sample")
@@ -221,7 +223,7 @@ class Lane:
     """One event stream of this rank: its tracker context (own CUDA stream), its
     frames and events resident in HBM and in pinned host memory."""
 
-    def __init__(self, torch, Tracker, wl, duration, seed, device):
+    def __init__(self, torch, Tracker, wl, duration, seed, device, stream_kernel=0):
         w, h, feat, rate, _ = wl
         self.S = S = synth.make_stream(w, h, duration, rate, seed, max_corners=feat)
         self.nF = len(S.frames)
@@ -231,6 +233,7 @@ class Lane:
                        for k in range(self.nF)]
         self.n_events = self.bounds[-1][1] - self.bounds[0][0]
         self.tr = Tracker(w, h, feat, device=device, record_capacity=1 << 20)
+        self.tr.set_stream_kernel(stream_kernel)
         self.flows = FlowCache(S)
         ev_bytes = torch.from_numpy(S.events.view(np.uint8).reshape(-1).copy())
         self.d_events = ev_bytes.cuda()
@@ -276,7 +279,7 @@ def main_ours(args):
     # global stream g = rank * streams + lane; stream 0 is the named stream, every
     # further one an independent stream of the same shape (configs[3], seeds 2000 + g)
     nS = max(1, args.streams)
-    lanes = [Lane(torch, Tracker, wl, args.duration, multi.stream_seed(seed, rank * nS + s), local)
+    lanes = [Lane(torch, Tracker, wl, args.duration, multi.stream_seed(seed, rank * nS + s), local, args.stream_kernel)
              for s in range(nS)]
     L0 = lanes[0]
     S, nF, tr = L0.S, L0.nF, L0.tr

@@ -72,6 +72,7 @@ EXPORTS = {
     "ebt_get_patch": (C.c_int, [_vp, C.c_int32, C.c_int, _vp]),
     "ebt_set_products": (C.c_int, [_vp, C.c_int]),
     "ebt_debug_feature_load": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int, _vp]),
+    "ebt_set_stream_kernel": (C.c_int, [_vp, C.c_int]),
     "ebt_set_cost_map": (C.c_int, [_vp, C.c_int]),
     "ebt_get_cost_map": (C.c_int, [_vp, C.c_int32, _vp]),
     "ebt_get_batch_cost_maps": (C.c_int, [_vp, _vp, C.c_int64]),
@@ -338,6 +339,10 @@ class Tracker:
                                                  cap, C.byref(n)))
         k = min(n.value, cap)
         return ids[:k], nopt[:k], t0[:k], t1[:k], sm[:k]
+
+    def set_stream_kernel(self, mode):
+        """0: one CTA per feature; 1: two features per CTA sharing its pixel warps."""
+        self._ck(self.lib.ebt_set_stream_kernel(self.ctx, int(mode)))
 
     def set_cost_map(self, on=True):
         """OptimizerParams::drawCostMap."""

@@ -129,6 +129,8 @@ struct ebt_ctx
 	size_t cap_bcost = 0, n_bcost = 0;
 	ebt_opt_record* d_records = nullptr;
 	unsigned long long* d_nrec = nullptr;
+	int* d_queue = nullptr;  // work-queue cursor of the shared-pixel-warp stream kernel
+	int stream_kernel = 0;   // ebt_set_stream_kernel
 	std::vector<ebt_opt_record> records;
 	size_t records_sorted = 0;  // records[0 .. records_sorted) are in reference order
 	std::vector<size_t> record_batches;  // end offset of every push behind records_sorted
@@ -448,6 +450,7 @@ int ebt_destroy(ebt_ctx* ctx)
 	cudaFree(ctx->d_bcost);
 	cudaFree(ctx->d_records);
 	cudaFree(ctx->d_nrec);
+	cudaFree(ctx->d_queue);
 	cudaFree(ctx->d_events);
 	cudaFree(ctx->d_gray);
 	cudaFree(ctx->d_lut);
@@ -571,6 +574,7 @@ int ebt_create(const ebt_params* params, int device, ebt_ctx** out)
 	CUC(cudaMemset(c->d_nablas, 0, P * EBT_PATCH_PIXELS * sizeof(int)));
 	CUC(cudaMalloc(&c->d_records, static_cast<size_t>(params->record_capacity) * sizeof(ebt_opt_record)));
 	CUC(cudaMalloc(&c->d_nrec, sizeof(unsigned long long)));
+	CUC(cudaMalloc(&c->d_queue, sizeof(int)));
 	CUC(cudaHostAlloc(&c->h_stage, P * sizeof(DevPatch), cudaHostAllocDefault));
 	CUC(cudaMalloc(&c->d_order, P * sizeof(int)));
 	CUC(cudaHostAlloc(&c->h_order, P * sizeof(int), cudaHostAllocDefault));
@@ -749,6 +753,13 @@ int ebt_debug_feature_load(ebt_ctx* ctx, int32_t* track_ids, int32_t* n_opt, uin
 		++n;
 	}
 	*n_out = n;
+	return EBT_OK;
+}
+
+int ebt_set_stream_kernel(ebt_ctx* ctx, int mode)
+{
+	if (!ctx || mode < 0 || mode > 1) return fail(ctx, EBT_E_INVALID, "ebt_set_stream_kernel: mode must be 0 or 1");
+	ctx->stream_kernel = mode;
 	return EBT_OK;
 }
 
@@ -1111,7 +1122,7 @@ static int runStream(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t
 	CU(ebt_launch_track_batch(ctx->d_patches, P, ctx->d_order, ctx->d_rings, ctx->d_nablas, d_events, n,
 							  ctx->event_index, ctx->d_mask, wpr, ctx->prefilter_margin, frameTable(ctx),
 							  ctx->dp, ctx->d_records, ctx->d_nrec,
-							  static_cast<unsigned long long>(ctx->prm.record_capacity), ctx->stream));
+							  static_cast<unsigned long long>(ctx->prm.record_capacity), ctx->stream, ctx->d_queue, ctx->stream_kernel));
 	toc(ctx, K_TRACK);
 	CU(cudaMemcpyAsync(ctx->nrec_stage, ctx->d_nrec, sizeof(unsigned long long), cudaMemcpyDeviceToHost,
 					   ctx->stream));

@@ -1336,6 +1336,24 @@ __device__ EBT_NOINLINE void optimize_feature(FeatShared& sh, double* costs, Fea
 	if (cm_out) cost_map(sh, st.warp[0], st.warp[1], st.warp[2], st.warp[3], st.flow, cm_out);  // optimizer.cpp:191-197
 }
 
+// One pixel of the L1 norm updateNumOfEvents takes: nearest-neighbour sample of the latest
+// grid through OpenCV's fixed-point rule, |gx a + gy b| (0 outside the image).
+__device__ __forceinline__ double num_events_term(const double2* __restrict__ grid, int W, int H, double c, double s,
+												  double tx, double ty, double a, double b, int x0, int y0, int i)
+{
+	const int yy = i / SIDE;
+	const int x = x0 + (i - yy * SIDE), y = y0 + yy;
+	const int X0 = __double2int_rn(c * x * 1024) + __double2int_rn(__dadd_rn(__dmul_rn(-s, y), tx) * 1024) + 512;
+	const int Y0 = __double2int_rn(s * x * 1024) + __double2int_rn(__dadd_rn(__dmul_rn(c, y), ty) * 1024) + 512;
+	const int xi = X0 >> 10, yi = Y0 >> 10;
+	if (xi >= 0 && xi < W && yi >= 0 && yi < H)
+	{
+		const double2 g = __ldg(grid + (size_t)yi * W + xi);
+		return fabs(__dadd_rn(__dmul_rn(g.x, a), __dmul_rn(g.y, b)));
+	}
+	return 0.0;
+}
+
 // Job (2b): FeatureDetector::updateNumOfEvents (ft/src/feature_detector.cpp:
 // 666-712).  cv::warpAffine(flags = WARP_INVERSE_MAP) is nearest-neighbour with
 // 10-bit fixed-point source coordinates; only the cropped rect is sampled, from
@@ -1365,21 +1383,7 @@ __device__ EBT_NOINLINE void update_num_of_events(FeatShared& sh, FeatState& st,
 	const double b = 0.6 * (double)__double2float_rn(sin((double)flow));
 	double acc[1];
 	acc[0] = 0;
-	for (int i = threadIdx.x; i < NPIX; i += NT)
-	{
-		const int yy = i / SIDE;
-		const int x = x0 + (i - yy * SIDE), y = y0 + yy;
-		const int X0 = __double2int_rn(c * x * 1024) +
-					   __double2int_rn(__dadd_rn(__dmul_rn(-s, y), tx) * 1024) + 512;
-		const int Y0 = __double2int_rn(s * x * 1024) +
-					   __double2int_rn(__dadd_rn(__dmul_rn(c, y), ty) * 1024) + 512;
-		const int xi = X0 >> 10, yi = Y0 >> 10;
-		if (xi >= 0 && xi < W && yi >= 0 && yi < H)
-		{
-			const double2 g = __ldg(grid + (size_t)yi * W + xi);
-			acc[0] += fabs(__dadd_rn(__dmul_rn(g.x, a), __dmul_rn(g.y, b)));
-		}
-	}
+	for (int i = threadIdx.x; i < NPIX; i += NT) acc[0] += num_events_term(grid, W, H, c, s, tx, ty, a, b, x0, y0, i);
 	block_sum<1>(sh, acc);
 	// size_t sumPatch = norm; Patch::setNumOfEvents clamps (patch.cpp:208-212)
 	const unsigned long long n = (unsigned long long)acc[0];
@@ -1914,6 +1918,7 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 struct __align__(16) SlotShared
 {
 	static constexpr int kPixWarps = SB_PIXW;
+	static constexpr bool is_slot = true;
 	ebt_event ring[SB_RING];  // the problem's window, chronological
 #if SB_TILE
 	double2 tile[TS * TS];
@@ -1935,7 +1940,8 @@ struct __align__(16) SlotShared
 
 __device__ __forceinline__ unsigned ld_volatile_u32(const unsigned* p) { return *(const volatile unsigned*)p; }
 
-__device__ __forceinline__ void sb_post(SlotShared& S)
+template <class SL>
+__device__ __forceinline__ void sb_post(SL& S)
 {
 	__syncwarp();
 	if ((threadIdx.x & 31) == 0)
@@ -1945,14 +1951,16 @@ __device__ __forceinline__ void sb_post(SlotShared& S)
 	}
 	__syncwarp();
 }
-__device__ __forceinline__ void wait_partials(SlotShared& S)
+template <class SL, class = decltype(SL::is_slot)>
+__device__ __forceinline__ void wait_partials(SL& S)
 {
 	const unsigned want = S.seq_local * SB_PIXW;
 	while (ld_volatile_u32(&S.done_cnt) != want) SB_BACKOFF();
 	__threadfence_block();
 	__syncwarp();
 }
-__device__ __forceinline__ void post_request(SlotShared& S, int kind, const double (&x)[5], double vx, double vy)
+template <class SL, class = decltype(SL::is_slot)>
+__device__ __forceinline__ void post_request(SL& S, int kind, const double (&x)[5], double vx, double vy)
 {
 	if ((threadIdx.x & 31) == 0)
 	{
@@ -1966,7 +1974,8 @@ __device__ __forceinline__ void post_request(SlotShared& S, int kind, const doub
 }
 
 // One job of slot S on this pixel warp (ptid = index among the 128 pixel threads).
-__device__ __noinline__ void sb_serve(SlotShared& S, int kind, int ptid)
+template <class SL>
+__device__ __noinline__ void sb_serve(SL& S, int kind, int ptid)
 {
 	const int lane = ptid & 31, pw = ptid >> 5;
 	const EvalCtx& E = S.ctx;
@@ -2204,6 +2213,416 @@ optimize_batch_shared_kernel(const ebt_problem* __restrict__ problems, int n_pro
 	}
 }
 
+
+// --------------------------------------------------------------------------
+// Stream kernel, shared pixel warps: the per-event loop of track_batch_kernel with
+// two features per CTA, one leader warp each, sharing the CTA's four pixel warps
+// (hand-off as in optimize_batch_shared_kernel).  Everything of a feature except
+// the pixel passes and the tile staging runs on its leader warp: candidate walk
+// (32 mask words = 1024 events per segment, chunks of 32 candidates), window ring,
+// integration, normalisation, window size, record.  Used when the getter-only
+// products and the cost map are off.
+// --------------------------------------------------------------------------
+struct __align__(16) StreamSlot
+{
+	static constexpr int kPixWarps = SB_PIXW;
+	static constexpr bool is_slot = true;
+	ebt_event ring[EBT_RING];
+	double2 tile[TS * TS];
+	double m[NPIX];
+	int nabla[NPIX];
+	double red[SB_PIXW][20];
+	double req[8];
+	double tot[20];
+	double costs[EBT_COST_HISTORY];
+	EvalCtx ctx;
+	unsigned short cand[32 * 32];
+	int req_kind;
+	unsigned req_seq, done_cnt, seq_local;
+	long long t_last;
+};
+
+// FeatureDetector::updateNumOfEvents on one warp (as update_num_of_events)
+__device__ void ss_update_num_of_events(FeatState& st, const FrameTable& ft, const DevParams& P)
+{
+	const int lane = threadIdx.x & 31;
+	const int W = P.width, H = P.height;
+	const double cx = (st.rx + (st.rx + SIDE)) * 0.5, cy = (st.ry + (st.ry + SIDE)) * 0.5;
+	if (cx <= P.border_margin || cy <= P.border_margin || cx >= W - P.border_margin || cy >= H - P.border_margin)
+	{
+		st.lost = 1;
+		return;
+	}
+	if (st.rx < 0 || st.ry < 0 || st.rx + SIDE >= W || st.ry + SIDE >= H)
+	{
+		st.num_of_events = min(max(P.init_num_events, P.min_num_events), P.max_num_events);
+		return;
+	}
+	const double2* grid = ft.grid[ft.latest];
+	const double c = st.warp[0], s = st.warp[1], tx = st.warp[2], ty = st.warp[3];
+	const int x0 = __double2int_rn(st.rx), y0 = __double2int_rn(st.ry);
+	const float flow = __double2float_rn(st.flow);
+	const double a = 0.6 * (double)__double2float_rn(cos((double)flow));
+	const double b = 0.6 * (double)__double2float_rn(sin((double)flow));
+	double acc = 0;
+	for (int i = lane; i < NPIX; i += 32) acc += num_events_term(grid, W, H, c, s, tx, ty, a, b, x0, y0, i);
+	acc = warp_sum(acc);
+	const unsigned long long n = (unsigned long long)acc;
+	st.num_of_events = (int)min(max(n, (unsigned long long)P.min_num_events), (unsigned long long)P.max_num_events);
+}
+
+// One Optimizer::optimize on a leader warp (as optimize_feature, cost map excluded)
+__device__ void ss_optimize(StreamSlot& S, FeatState& st, const FrameTable& ft, const DevParams& P, LmSummary& L)
+{
+	const int lane = threadIdx.x & 31;
+	L.filtered = 0;
+	for (int i = lane; i < NPIX; i += 32) S.nabla[i] = 0;
+	__syncwarp();
+	for (int k = lane; k < st.size; k += 32)
+	{
+		const ebt_event e = S.ring[(st.tail + k) & RMASK];
+		if (in_rect(st.rx, st.ry, e.x, e.y))
+		{
+			const int px = (int)(e.x - st.rx), py = (int)(e.y - st.ry);
+			atomicAdd(&S.nabla[py * SIDE + px], (int)e.polarity);
+		}
+	}
+	{
+		const long long front = S.ring[(st.tail + st.size - 1) & RMASK].t_us;
+		const long long back = S.ring[st.tail & RMASK].t_us;
+		st.cur_ts = to_i32((double)(front + back) * 0.5);
+		st.time_last_update = to_i32((double)back);
+	}
+	__syncwarp();
+	double a = 0;
+	for (int i = lane; i < NPIX; i += 32)
+	{
+		const double v = (double)S.nabla[i];
+		a += v * v;
+	}
+	a = warp_sum(a);
+	const double inv = 1.0 / sqrt(a);
+	double smm = 0;
+	for (int i = lane; i < NPIX; i += 32)
+	{
+		const double v = (double)S.nabla[i] * inv;
+		S.m[i] = v;
+		smm += v * v;
+	}
+	smm = warp_sum(smm);
+	int r0 = 0, c0 = 0, staged = 0;
+	{
+		const double c = st.warp[0], s = st.warp[1], tx = st.warp[2], ty = st.warp[3];
+		double lox = DBL_MAX, hix = -DBL_MAX, loy = DBL_MAX, hiy = -DBL_MAX;
+#pragma unroll
+		for (int k = 0; k < 4; ++k)
+		{
+			const double px = st.rx + ((k & 1) ? SIDE - 1 : 0), py = st.ry + ((k & 2) ? SIDE - 1 : 0);
+			const double wx = c * px - s * py + tx, wy = s * px + c * py + ty;
+			lox = wx < lox ? wx : lox;
+			hix = wx > hix ? wx : hix;
+			loy = wy < loy ? wy : loy;
+			hiy = wy > hiy ? wy : hiy;
+		}
+		if (lox > -1e6 && hix < 1e6 && loy > -1e6 && hiy < 1e6)
+		{
+			const int cl = (int)floor(lox) - 1, ch = (int)floor(hix) + 2;
+			const int rl = (int)floor(loy) - 1, rh = (int)floor(hiy) + 2;
+			if (ch - cl < TS && rh - rl < TS)
+			{
+				c0 = cl - (TS - (ch - cl + 1)) / 2;
+				r0 = rl - (TS - (rh - rl + 1)) / 2;
+				staged = 1;
+			}
+		}
+	}
+	if (lane == 0)
+	{
+		EvalCtx& E = S.ctx;
+		E.grid = ft.grid[st.frame_slot];
+		E.W = P.width;
+		E.H = P.height;
+		E.r0 = r0;
+		E.c0 = c0;
+		E.staged = staged;
+		E.tlx = st.rx;
+		E.tly = st.ry;
+		E.smm = smm;
+		E.huber_a = P.huber_a;
+		S.req_kind = 3;
+	}
+	if (staged)
+	{
+		sb_post(S);
+		wait_partials(S);
+	}
+	else
+		__syncwarp();
+	double x[5] = {st.warp[0], st.warp[1], st.warp[2], st.warp[3], (double)__double2float_rn(st.flow)};
+	lm_solve(S, P, x, L);
+	// addFinalCost + median-of-5 cost filter (optimizer.cpp:127-157)
+	if (lane == 0) S.costs[st.n_costs & (EBT_COST_HISTORY - 1)] = L.final_cost;
+	st.n_costs++;
+	__syncwarp();
+	if (st.n_costs >= 6)
+	{
+		double v[5];
+#pragma unroll
+		for (int i = 0; i < 5; ++i) v[i] = S.costs[(st.n_costs - 6 + i) & (EBT_COST_HISTORY - 1)];
+#pragma unroll
+		for (int i = 1; i < 5; ++i)
+#pragma unroll
+			for (int j = i; j > 0; --j)
+				if (v[j] < v[j - 1])
+				{
+					const double t = v[j];
+					v[j] = v[j - 1];
+					v[j - 1] = t;
+				}
+		if (v[2] > P.optimizer_threshold)
+		{
+			st.lost = 1;
+			L.filtered = 1;
+			return;
+		}
+	}
+	st.flow = fmod(x[4], 2 * 3.14159265358979323846);
+#pragma unroll
+	for (int k = 0; k < 4; ++k) st.warp[k] = x[k];
+	st.init = 1;
+	const double ox = st.rx, oy = st.ry;
+	update_rect(st);
+	const double h = (SIDE - 1) / 2.;
+	const double dx = (st.rx + h) - (ox + h), dy = (st.ry + h) - (oy + h);
+	st.time_without_update = (long long)(1e6 / fmax(1e-1, sqrt(dx * dx + dy * dy)));
+	st.n_traj++;
+	st.counter = 0;
+}
+
+__global__ void __launch_bounds__(SB_THREADS, SB_CTAS)
+track_shared_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __restrict__ order,
+					ebt_event* __restrict__ rings, int* __restrict__ nablas,
+					const ebt_event* __restrict__ events, long long n_events, long long event_base,
+					unsigned* mask, int words_per_row, double margin, FrameTable ft, DevParams P,
+					ebt_opt_record* __restrict__ records, unsigned long long* n_records,
+					unsigned long long record_cap, int* __restrict__ queue)
+{
+	extern __shared__ __align__(16) unsigned char ss_raw[];
+	StreamSlot* slots = reinterpret_cast<StreamSlot*>(ss_raw);
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	if (threadIdx.x < SB_LEADERS)
+	{
+		slots[threadIdx.x].req_seq = 0;
+		slots[threadIdx.x].done_cnt = 0;
+		slots[threadIdx.x].seq_local = 0;
+		slots[threadIdx.x].t_last = 0;
+	}
+	__syncthreads();
+	if (warp >= SB_LEADERS)
+	{
+		const int ptid = threadIdx.x - SB_LEADERS * 32;
+		unsigned served[SB_LEADERS];
+#pragma unroll
+		for (int l = 0; l < SB_LEADERS; ++l) served[l] = 0;
+		int exited = 0;
+		while (exited < SB_LEADERS)
+		{
+			bool idle = true;
+#pragma unroll
+			for (int l = 0; l < SB_LEADERS; ++l)
+			{
+				StreamSlot& S = slots[l];
+				const unsigned seq = __shfl_sync(0xffffffffu, ld_volatile_u32(&S.req_seq), 0);
+				if (seq == served[l]) continue;
+				served[l] = seq;
+				idle = false;
+				__threadfence_block();
+				const int kind = *(const volatile int*)&S.req_kind;
+				if (kind == 4)
+				{
+					++exited;
+					continue;
+				}
+				sb_serve(S, kind, ptid);
+				__threadfence_block();
+				__syncwarp();
+				if (lane == 0) atomicAdd(&S.done_cnt, 1u);
+			}
+			if (idle) SB_BACKOFF();
+		}
+		return;
+	}
+	// ---- leader warp `warp`.  First feature: CTA c pairs the c-th heaviest with the c-th
+	// lightest (order[] is heaviest first), so two long chains do not share pixel warps;
+	// afterwards the leaders pull the features in between from a queue, heaviest first.
+	StreamSlot& S = slots[warp];
+	static_assert(SB_LEADERS == 2, "feature pairing below is written for two leaders per CTA");
+	const int n_ctas = (int)gridDim.x;
+	int oi = warp == 0 ? (int)blockIdx.x : n_patches - 1 - (int)blockIdx.x;
+	if (warp == 1 && oi < n_ctas) oi = n_patches;  // that one belongs to a first leader
+	for (; oi < n_patches;
+		 oi = __shfl_sync(0xffffffffu, lane == 0 ? atomicAdd(queue, 1) : 0, 0), oi = oi < n_patches - n_ctas ? oi : n_patches)
+	{
+		if (patches[order[oi]].lost) continue;
+		const int f = order[oi];
+		DevPatch& gp = patches[f];
+		unsigned long long t_enter;
+		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_enter));
+		FeatState st;
+		load_state(st, gp);
+		const int track_id = gp.track_id;
+		ebt_event* gring = rings + (size_t)gp.store_slot * EBT_RING;
+		int* gnabla = nablas + (size_t)gp.store_slot * NPIX;
+		for (int k = lane; k < st.size; k += 32) S.ring[k] = gring[(st.tail + k) & RMASK];
+		if (lane < EBT_COST_HISTORY) S.costs[lane] = gp.costs[lane];
+		st.tail = 0;
+		__syncwarp();
+		const uint4* ev4 = reinterpret_cast<const uint4*>(events);
+		unsigned* row = mask + (size_t)f * words_per_row;
+		double srx = st.rx, sry = st.ry;
+		long long start = 0;
+		int n_opt = 0;
+		bool pre = st.init && n_events > 0 && window_need(st, P) <= 0;
+		const long long n_words = (n_events + 31) >> 5;
+		long long seg = start >> 5;
+		while (!st.lost && seg < n_words)
+		{
+			const long long wi = seg + lane;
+			unsigned word = wi < n_words ? row[wi] : 0u;
+			{
+				const long long first = wi << 5;
+				if (first < start) word = (start - first >= 32) ? 0u : (word & (0xffffffffu << (int)(start - first)));
+			}
+			const int c = __popc(word);
+			int incl = c;
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1)
+			{
+				const int up = __shfl_up_sync(0xffffffffu, incl, o);
+				if (lane >= o) incl += up;
+			}
+			int off = incl - c;
+			int n_c = __shfl_sync(0xffffffffu, incl, 31);
+			if (pre)
+			{
+				n_c = 1;
+				if (lane == 0) S.cand[0] = 0;
+			}
+			else
+				while (word)
+				{
+					const int bit = __ffs(word) - 1;
+					word &= word - 1;
+					S.cand[off++] = (unsigned short)(lane * 32 + bit);
+				}
+			__syncwarp();
+			bool restart = false;
+			for (int cbase = 0; cbase < n_c && !restart && !st.lost; cbase += 32)
+			{
+				const int chunk_len = min(32, n_c - cbase);
+				uint4 raw = make_uint4(0, 0, 0, 0);
+				if (lane < chunk_len) raw = __ldg(ev4 + ((seg << 5) + S.cand[cbase + lane]));
+				const int ex = (int)(raw.z & 0xffffu), ey = (int)(raw.z >> 16);
+				int resume = 0;
+				while (resume < chunk_len)
+				{
+					const bool live = lane >= resume && lane < chunk_len;
+					const bool inside = live && in_rect(st.rx, st.ry, ex, ey);
+					const unsigned bal = __ballot_sync(0xffffffffu, inside);
+					const int total = __popc(bal);
+					const int rank = __popc(bal & ((1u << lane) - 1u)) + 1;  // if inside
+					const int need = window_need(st, P);
+					int trig = -1, take = total;
+					if (st.init && need <= 0)
+					{
+						trig = resume;
+						take = (int)((bal >> resume) & 1u);
+					}
+					else if (st.init && total >= need)
+					{
+						take = need;
+						trig = (int)__fns(bal, 0, need);
+					}
+					if (inside && rank <= take)
+						*reinterpret_cast<uint4*>(&S.ring[(st.tail + st.size + rank - 1) & RMASK]) = raw;
+					if (take > 0) window_grow(st, take);
+					__syncwarp();
+					if (trig < 0) break;
+					const long long at = (seg << 5) + S.cand[cbase + trig];
+					// ---- one Optimizer::optimize at stream event `at` and the bookkeeping around it
+					LmSummary L;
+					ss_optimize(S, st, ft, P, L);
+					if (!L.filtered && lane == 0)
+					{
+						// Patch::addTrajectoryPosition: the two newest trajectory entries
+						const double lx = st.rx + (SIDE - 1) / 2., ly = st.ry + (SIDE - 1) / 2.;
+						gp.traj_x[0] = gp.traj_x[1]; gp.traj_y[0] = gp.traj_y[1]; gp.traj_ts[0] = gp.traj_ts[1];
+						gp.traj_x[1] = lx; gp.traj_y[1] = ly; gp.traj_ts[1] = st.cur_ts;
+					}
+					ss_update_num_of_events(st, ft, P);
+					if (lane == 0) write_record(records, n_records, record_cap, st, track_id, L, event_base + at);
+					++n_opt;
+					start = at + 1;
+					if (!st.lost && (fabs(st.rx - srx) > margin || fabs(st.ry - sry) > margin))
+					{
+						// rebuild the mask row from `start` on around the rect's current position
+						const int4 bb = candidate_bounds(st.rx, st.ry, margin);
+						const unsigned* ev32 = reinterpret_cast<const unsigned*>(events);
+						for (long long w = (start >> 5); w < n_words; ++w)
+						{
+							const long long e = w * 32 + lane;
+							bool in = false;
+							if (e < n_events)
+							{
+								const unsigned v = __ldg(ev32 + 4 * e + 2);
+								const int x = (int)(v & 0xffffu), y = (int)(v >> 16);
+								in = x >= bb.x && x <= bb.y && y >= bb.z && y <= bb.w;
+							}
+							const unsigned b2 = __ballot_sync(0xffffffffu, in);
+							if (lane == 0) row[w] = b2;
+						}
+						__syncwarp();
+						srx = st.rx;
+						sry = st.ry;
+						restart = true;
+						break;
+					}
+					if (st.lost) break;
+					resume = trig + 1;
+				}
+			}
+			__syncwarp();
+			if (pre)
+			{
+				pre = false;
+				restart = true;
+			}
+			seg = restart ? (start >> 5) : seg + 32;
+		}
+		__syncwarp();
+		for (int k = lane; k < st.size; k += 32) gring[k] = S.ring[(st.tail + k) & RMASK];
+		if (n_opt > 0)
+			for (int i = lane; i < NPIX; i += 32) gnabla[i] = S.nabla[i];
+		if (lane < EBT_COST_HISTORY) gp.costs[lane] = S.costs[lane];
+		st.tail = 0;
+		if (lane == 0)
+		{
+			store_state(st, gp);
+			gp.last_n_opt = n_opt;
+			unsigned long long t_exit;
+			unsigned sm;
+			asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_exit));
+			asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+			gp.last_t0_ns = t_enter;
+			gp.last_t1_ns = t_exit;
+			gp.last_sm = (int)sm;
+		}
+		__syncwarp();
+	}
+	if (lane == 0) S.req_kind = 4;
+	sb_post(S);
+}
+
 template <int MINCTAS>  // register budget matched to the launch, as for track_batch_kernel
 __global__ void __launch_bounds__(NT, MINCTAS)
 optimize_batch_kernel(const ebt_problem* __restrict__ problems, int n_problems,
@@ -2368,7 +2787,7 @@ cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, const int* 
 								   int words_per_row, double margin, const FrameTable& ft,
 								   const DevParams& P, ebt_opt_record* records,
 								   unsigned long long* n_records, unsigned long long record_cap,
-								   cudaStream_t stream)
+								   cudaStream_t stream, int* queue, int shared_pixel_warps)
 {
 	if (n_patches <= 0 || n_events <= 0) return cudaSuccess;
 	const dim3 pf_grid((unsigned)((n_events + PF_TILE - 1) / PF_TILE),
@@ -2380,6 +2799,25 @@ cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, const int* 
 	track_batch_kernel<M><<<n_patches, NT, 0, stream>>>(patches, n_patches, order, rings, nablas, events,  \
 														n_events, event_base, mask, words_per_row, margin, \
 														ft, P, records, n_records, record_cap)
+	if (shared_pixel_warps && queue && !P.products && !P.cost_maps && n_patches > 2 * sm_count)
+	{
+		static bool attr_set = false;
+		const size_t smem = SB_LEADERS * sizeof(StreamSlot);
+		if (!attr_set)
+		{
+			cudaError_t e = cudaFuncSetAttribute(track_shared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+												 (int)smem);
+			if (e != cudaSuccess) return e;
+			attr_set = true;
+		}
+		const int ctas = min((n_patches + 1) / 2, SB_CTAS * sm_count);
+		cudaError_t e = cudaMemcpyAsync(queue, &ctas, sizeof(int), cudaMemcpyHostToDevice, stream);  // pageable: staged by the driver
+		if (e != cudaSuccess) return e;
+		track_shared_kernel<<<ctas, SB_THREADS, smem, stream>>>(
+			patches, n_patches, order, rings, nablas, events, n_events, event_base, mask, words_per_row, margin, ft,
+			P, records, n_records, record_cap, queue);
+		return cudaGetLastError();
+	}
 	static const int forced = getenv("EBT_STREAM_BUILD") ? atoi(getenv("EBT_STREAM_BUILD")) : 0;  // tuning only
 	const int build = forced ? forced : (n_patches <= sm_count ? 1 : (n_patches <= 2 * sm_count ? 2 : 3));
 	if (build == 1)

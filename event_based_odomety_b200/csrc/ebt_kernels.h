@@ -14,7 +14,7 @@ cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, const int* 
 								   int words_per_row, double margin, const FrameTable& ft,
 								   const DevParams& P, ebt_opt_record* records,
 								   unsigned long long* n_records, unsigned long long record_cap,
-								   cudaStream_t stream);
+								   cudaStream_t stream, int* queue = nullptr, int shared_pixel_warps = 0);
 int ebt_mask_words_per_row(long long n_events);
 cudaError_t ebt_launch_optimize_batch(const ebt_problem* problems, int n_problems,
 									  const ebt_event* events, const FrameTable& ft,

@@ -280,6 +280,15 @@ int ebt_debug_feature_load(ebt_ctx* ctx, int32_t* track_ids, int32_t* n_opt, uin
  * Default 8. */
 int ebt_set_prefilter_margin(ebt_ctx* ctx, double pixels);
 
+/* Tuning knob of ebt_push_events (not part of the reference's API): which build of the
+ * stream kernel runs when more than two features per SM are live.
+ *   0 (default)  one CTA per feature (a leader warp + four pixel warps each)
+ *   1            two features per CTA, their leader warps sharing the CTA's four pixel
+ *                warps, features handed out from a queue (same results; measured equal on
+ *                one stream, +7 % with several streams per GPU; needs the patch products
+ *                and the cost map off, else mode 0 runs) */
+int ebt_set_stream_kernel(ebt_ctx* ctx, int mode);
+
 /* ABI self-description for binding generators/tests. */
 size_t ebt_sizeof_event(void);
 size_t ebt_sizeof_track(void);

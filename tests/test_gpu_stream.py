@@ -23,11 +23,12 @@ def _angle_diff_deg(a, b):
     return np.rad2deg(np.minimum(d, 2 * np.pi - d))
 
 
-def compare(stream, max_patches, n_frames=None, split=None, margin=None):
+def compare(stream, max_patches, n_frames=None, split=None, margin=None, stream_kernel=0):
     cpu = CpuTracker(load_oracle(), stream.width, stream.height, max_patches)
     gpu = Tracker(stream.width, stream.height, max_patches)
     if margin is not None:
         gpu.set_prefilter_margin(margin)
+    gpu.set_stream_kernel(stream_kernel)
     n_cpu = synth.run_stream(cpu, stream, n_frames)
     if split:
         # same stream, but every inter-frame batch pushed in `split` pieces:
@@ -92,10 +93,20 @@ def test_stream_split_batches():
 
 
 @pytest.mark.gpu
-def test_stream_c2_shape():
-    """BASELINE.json configs[1] shape: 346x260, 500 features, ~2 Mev/s (short)."""
+@pytest.mark.parametrize("stream_kernel", [0, 1])
+def test_stream_c2_shape(stream_kernel):
+    """BASELINE.json configs[1] shape: 346x260, 500 features, ~2 Mev/s (short); both builds of the
+    stream kernel (one CTA per feature / two features per CTA sharing its pixel warps)."""
     S = synth.make_stream(346, 260, 0.10, 2e6, seed=1002, max_corners=500)
-    compare(S, 500)
+    compare(S, 500, stream_kernel=stream_kernel)
+
+
+@pytest.mark.gpu
+def test_stream_shared_pixel_warps_split_and_margin():
+    """The two-features-per-CTA kernel with every batch pushed in 5 pieces and a 0.5 px prefilter margin
+    (mask rows rebuilt after nearly every optimisation)."""
+    S = synth.make_stream(346, 260, 0.08, 2e6, seed=1052, max_corners=400)
+    compare(S, 400, split=5, margin=0.5, stream_kernel=1)
 
 
 @pytest.mark.gpu
