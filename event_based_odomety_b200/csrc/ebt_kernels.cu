@@ -2568,18 +2568,26 @@ track_shared_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __
 						// rebuild the mask row from `start` on around the rect's current position
 						const int4 bb = candidate_bounds(st.rx, st.ry, margin);
 						const unsigned* ev32 = reinterpret_cast<const unsigned*>(events);
-						for (long long w = (start >> 5); w < n_words; ++w)
+						// eight mask words per trip: eight independent loads in flight per lane
+						for (long long w0 = (start >> 5); w0 < n_words; w0 += 8)
 						{
-							const long long e = w * 32 + lane;
-							bool in = false;
-							if (e < n_events)
+							unsigned v[8];
+#pragma unroll
+							for (int j = 0; j < 8; ++j)
 							{
-								const unsigned v = __ldg(ev32 + 4 * e + 2);
-								const int x = (int)(v & 0xffffu), y = (int)(v >> 16);
-								in = x >= bb.x && x <= bb.y && y >= bb.z && y <= bb.w;
+								const long long e = (w0 + j) * 32 + lane;
+								v[j] = e < n_events ? __ldg(ev32 + 4 * e + 2) : 0xffffffffu;  // no region holds 65535
 							}
-							const unsigned b2 = __ballot_sync(0xffffffffu, in);
-							if (lane == 0) row[w] = b2;
+							unsigned mine = 0;
+#pragma unroll
+							for (int j = 0; j < 8; ++j)
+							{
+								const int x = (int)(v[j] & 0xffffu), y = (int)(v[j] >> 16);
+								const unsigned b2 =
+									__ballot_sync(0xffffffffu, x >= bb.x && x <= bb.y && y >= bb.z && y <= bb.w);
+								if (lane == j) mine = b2;
+							}
+							if (lane < 8 && w0 + lane < n_words) row[w0 + lane] = mine;
 						}
 						__syncwarp();
 						srx = st.rx;
