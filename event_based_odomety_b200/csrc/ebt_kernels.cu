@@ -1615,18 +1615,25 @@ __device__ void rebuild_mask_row(unsigned* __restrict__ row, const ebt_event* __
 	const unsigned* ev32 = reinterpret_cast<const unsigned*>(events);
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const long long n_words = (n_events + 31) >> 5;
-	for (long long w = (from >> 5) + warp; w < n_words; w += NW)
+	// four mask words per warp and trip: four independent loads in flight per lane
+	for (long long w0 = (from >> 5) + 4 * warp; w0 < n_words; w0 += 4 * NW)
 	{
-		const long long e = w * 32 + lane;
-		bool in = false;
-		if (e < n_events)
+		unsigned v[4];
+#pragma unroll
+		for (int j = 0; j < 4; ++j)
 		{
-			const unsigned v = __ldg(ev32 + 4 * e + 2);
-			const int x = (int)(v & 0xffffu), y = (int)(v >> 16);
-			in = x >= b.x && x <= b.y && y >= b.z && y <= b.w;
+			const long long e = (w0 + j) * 32 + lane;
+			v[j] = e < n_events ? __ldg(ev32 + 4 * e + 2) : 0xffffffffu;  // no region holds 65535
 		}
-		const unsigned bal = __ballot_sync(0xffffffffu, in);
-		if (lane == 0) row[w] = bal;
+		unsigned mine = 0;
+#pragma unroll
+		for (int j = 0; j < 4; ++j)
+		{
+			const int x = (int)(v[j] & 0xffffu), y = (int)(v[j] >> 16);
+			const unsigned bal = __ballot_sync(0xffffffffu, x >= b.x && x <= b.y && y >= b.z && y <= b.w);
+			if (lane == j) mine = bal;
+		}
+		if (lane < 4 && w0 + lane < n_words) row[w0 + lane] = mine;
 	}
 	__syncthreads();  // global writes of this CTA are read back by this CTA only
 }
