@@ -67,6 +67,8 @@ EXPORTS = {
     "ebt_push_events_device": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
     "ebt_parse_events_text": (C.c_int, [_vp, C.c_char_p, C.c_size_t, C.c_int, _vp, C.c_int64,
                                         C.POINTER(C.c_int64), C.POINTER(C.c_size_t)]),
+    "ebt_parse_events_text_static": (C.c_int, [C.c_int, _vp, _vp, C.c_size_t, C.c_int, _vp, C.c_int64,
+                                               C.POINTER(C.c_int64), C.POINTER(C.c_size_t), C.c_char_p, C.c_size_t]),
     "ebt_replay": (C.c_int, [_vp, _vp, C.c_int64, _vp, _vp, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "ebt_get_tracks": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "ebt_get_patch": (C.c_int, [_vp, C.c_int32, C.c_int, _vp]),
@@ -132,6 +134,22 @@ def _ptr(a):
 
 
 K_TRACK, K_BATCH, K_GRAD, K_NUMEV, K_CORNERS, K_PYRAMID, K_LK, K_PARSE = range(8)
+
+
+STATIC_PARSE_MAX_BYTES = 64 << 20  # EBT_STATIC_PARSE_MAX_BYTES (include/ebt.h)
+
+
+def parse_events_text_static(device, d_text_ptr, n_bytes, d_out_ptr, cap, final=True, stream=0):
+    """ebt_parse_events_text_static: text and output are device pointers the caller
+    owns; nothing is allocated by the call.  Returns (lines parsed, bytes consumed)."""
+    lib = load()
+    n, used = C.c_int64(), C.c_size_t()
+    msg = C.create_string_buffer(512)
+    rc = lib.ebt_parse_events_text_static(int(device), _vp(stream), _vp(d_text_ptr), n_bytes, int(final),
+                                          _vp(d_out_ptr), cap, C.byref(n), C.byref(used), msg, len(msg))
+    if rc != 0:
+        raise EbtError(f"ebt error {rc}: {msg.value.decode()}")
+    return n.value, used.value
 
 
 class Tracker:

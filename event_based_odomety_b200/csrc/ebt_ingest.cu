@@ -261,3 +261,163 @@ cudaError_t ebt_launch_parse_lines(const char* d_text, size_t len, const int* d_
 													 d_out, d_err);
 	return cudaGetLastError();
 }
+
+// ---------------------------------------------------------------------------
+// ebt_parse_events_text_static — the same parser for callers that must not
+// allocate (CUDA graph capture set-up, tight serving loops, harnesses that forbid
+// cudaMalloc).  No counterpart in the reference.
+// The tile counts, the line total, the error word and the
+// tail description live in a file-scope __device__ array of fixed size, so the
+// call issues kernels, two small memsets and two small D2H copies and nothing
+// else: no cudaMalloc / cudaFree / cudaHostAlloc, no library routine that
+// allocates.  Text and output are device buffers the caller owns.
+//
+// The array is per device (every GPU that loads the library holds its 65 792
+// bytes until exit) and shared by every call: it keeps the previous call's
+// contents, so the words that must start from a known value (error word, tail
+// words) are re-initialised on the stream before use, and the tile counts of
+// this call's tiles are all rewritten by newline_count_kernel.  Calls that
+// overlap on the GPU (two host threads, or two streams) race on it.
+#include <mutex>
+#include <stdio.h>
+
+#include "../../include/ebt.h"
+
+namespace
+{
+constexpr size_t STATIC_MAX_BYTES = EBT_STATIC_PARSE_MAX_BYTES;
+constexpr size_t STATIC_MAX_TILES = STATIC_MAX_BYTES / TILE;
+constexpr size_t STATIC_HEADER_BYTES = 256;  // [0] newline total, [1] error word, [2] end of last newline, [3] last byte
+constexpr int STATIC_MAX_DEVICES = 64;
+
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_HEADER_BYTES + STATIC_MAX_TILES * sizeof(int)];
+
+std::mutex g_static_mu;
+unsigned char* g_static_ptr[STATIC_MAX_DEVICES];  // device address of g_static_scratch, per device
+
+// In host code `g_static_scratch` is only a handle: the device address has to be
+// asked for, once per device, with that device current.
+cudaError_t static_scratch(int device, unsigned char** out)
+{
+	std::lock_guard<std::mutex> lock(g_static_mu);
+	if (!g_static_ptr[device])
+	{
+		void* p = nullptr;
+		const cudaError_t rc = cudaGetSymbolAddress(&p, g_static_scratch);
+		if (rc != cudaSuccess) return rc;
+		g_static_ptr[device] = static_cast<unsigned char*>(p);
+	}
+	*out = g_static_ptr[device];
+	return cudaSuccess;
+}
+
+// info[2] = offset just behind the last '\n' of the buffer (0 if none), info[3] = last byte
+__global__ void tail_info_kernel(const char* __restrict__ text, size_t len, unsigned long long* __restrict__ info)
+{
+	const int lane = threadIdx.x;
+	if (lane == 0) info[3] = (unsigned char)text[len - 1];
+	size_t end = len;
+	while (end > 0)
+	{
+		const bool inside = (size_t)lane < end;  // lane k looks at byte end - 1 - k
+		const bool nl = inside && text[end - 1 - lane] == '\n';
+		const unsigned m = __ballot_sync(0xffffffffu, nl);
+		if (m)
+		{
+			if (lane == 0) info[2] = end - (__ffs(m) - 1);
+			return;
+		}
+		end = end > 32 ? end - 32 : 0;
+	}
+	if (lane == 0) info[2] = 0;
+}
+
+int static_fail(char* errmsg, size_t cap, int code, const char* fmt, long long a = 0, long long b = 0)
+{
+	if (errmsg && cap) snprintf(errmsg, cap, fmt, a, b);
+	return code;
+}
+}  // namespace
+
+extern "C" int ebt_parse_events_text_static(int device, void* cuda_stream, const char* d_text, size_t len,
+											int final_chunk, ebt_event* d_out, int64_t cap, int64_t* n_out,
+											size_t* consumed, char* errmsg, size_t errmsg_cap)
+{
+	if (errmsg && errmsg_cap) errmsg[0] = 0;
+	if (!n_out || cap < 0 || (len > 0 && !d_text) || (cap > 0 && !d_out) || device < 0 || device >= STATIC_MAX_DEVICES)
+		return static_fail(errmsg, errmsg_cap, EBT_E_INVALID, "ebt_parse_events_text_static: bad argument");
+	*n_out = 0;
+	if (consumed) *consumed = 0;
+	if (len == 0) return EBT_OK;
+	if (len > STATIC_MAX_BYTES)
+		return static_fail(errmsg, errmsg_cap, EBT_E_CAPACITY,
+						   "ebt_parse_events_text_static: %lld bytes of text, the static scratch serves at most %lld "
+						   "per call (EBT_STATIC_PARSE_MAX_BYTES); pass the text in smaller chunks",
+						   (long long)len, (long long)STATIC_MAX_BYTES);
+	if (reinterpret_cast<uintptr_t>(d_text) & 15)
+		return static_fail(errmsg, errmsg_cap, EBT_E_INVALID, "ebt_parse_events_text_static: d_text must be 16-byte aligned");
+	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	int prev = -1;
+	cudaError_t rc = cudaGetDevice(&prev);
+	if (rc == cudaSuccess && prev != device) rc = cudaSetDevice(device);
+	unsigned char* scratch = nullptr;
+	if (rc == cudaSuccess) rc = static_scratch(device, &scratch);
+	unsigned long long host[4] = {0, 0, 0, 0};
+	long long n_lines = 0;
+	int status = EBT_OK;
+	if (rc == cudaSuccess)
+	{
+		unsigned long long* info = reinterpret_cast<unsigned long long*>(scratch);
+		int* counts = reinterpret_cast<int*>(scratch + STATIC_HEADER_BYTES);
+		// the array holds the previous call's words: error word to ~0, totals and tail words to 0
+		rc = cudaMemsetAsync(info, 0, STATIC_HEADER_BYTES, stream);
+		if (rc == cudaSuccess) rc = cudaMemsetAsync(info + 1, 0xff, sizeof(unsigned long long), stream);
+		if (rc == cudaSuccess)
+			rc = ebt_launch_count_lines(d_text, len, counts, reinterpret_cast<long long*>(info), stream);
+		if (rc == cudaSuccess)
+		{
+			tail_info_kernel<<<1, 32, 0, stream>>>(d_text, len, info);
+			rc = cudaGetLastError();
+		}
+		if (rc == cudaSuccess) rc = cudaMemcpyAsync(host, info, sizeof host, cudaMemcpyDeviceToHost, stream);
+		if (rc == cudaSuccess) rc = cudaStreamSynchronize(stream);
+		if (rc == cudaSuccess)
+		{
+			const bool tail = final_chunk && host[3] != '\n';
+			n_lines = (long long)host[0] + (tail ? 1 : 0);
+			*n_out = n_lines;
+			if (n_lines > cap)
+				status = static_fail(errmsg, errmsg_cap, EBT_E_CAPACITY,
+									 "ebt_parse_events_text_static: %lld lines, output holds %lld", n_lines, (long long)cap);
+			else if (n_lines > 0)
+			{
+				rc = ebt_launch_parse_lines(d_text, len, counts, n_lines, final_chunk ? 1 : 0, d_out, info + 1, stream);
+				if (rc == cudaSuccess)
+					rc = cudaMemcpyAsync(host + 1, info + 1, sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream);
+				if (rc == cudaSuccess) rc = cudaStreamSynchronize(stream);
+				if (rc == cudaSuccess && host[1] != ~0ull)
+				{
+					const unsigned code = (unsigned)(host[1] & 0xff);
+					*n_out = 0;
+					status = static_fail(errmsg, errmsg_cap, EBT_E_INVALID,
+										 code == 2   ? "ebt_parse_events_text_static: line %lld: timestamp has too many digits "
+													   "for an exact conversion (mantissa >= 2^53)"
+										 : code == 3 ? "ebt_parse_events_text_static: line %lld: line longer than 128 bytes"
+													 : "ebt_parse_events_text_static: line %lld: malformed line (expected "
+													   "\"t_sec x y p\" with p 0 or 1)",
+										 (long long)(host[1] >> 8));
+				}
+			}
+		}
+	}
+	if (rc != cudaSuccess)
+	{
+		if (errmsg && errmsg_cap)
+			snprintf(errmsg, errmsg_cap, "ebt_parse_events_text_static: CUDA error: %s", cudaGetErrorString(rc));
+		status = EBT_E_CUDA;
+	}
+	else if (status == EBT_OK && consumed)
+		*consumed = final_chunk ? len : (size_t)host[2];
+	if (prev >= 0 && prev != device) cudaSetDevice(prev);
+	return status;
+}

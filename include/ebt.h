@@ -216,6 +216,29 @@ int ebt_get_gradients(ebt_ctx* ctx, double* gx, double* gy);
 int ebt_parse_events_text(ebt_ctx* ctx, const char* text, size_t len, int final_chunk, ebt_event* out,
 						  int64_t cap, int64_t* n_out, size_t* consumed);
 
+/* ebt_parse_events_text for callers that must not allocate.  No counterpart in
+ * the reference: added for code that
+ * cannot call cudaMalloc (set-up under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same kernels and same results as
+ * ebt_parse_events_text, but text and output are DEVICE buffers owned by the
+ * caller (d_text 16-byte aligned, on `device`), and the parser's scratch (tile
+ * line counts, totals, error word) is a fixed file-scope __device__ array of
+ * 65 792 bytes that every GPU loading the library holds until exit.  The call
+ * issues kernels, small memsets and two small D2H copies on `cuda_stream`
+ * (a cudaStream_t, NULL = default stream) and waits for them; it calls no
+ * cudaMalloc / cudaFree / cudaHostAlloc and no allocating library routine, and
+ * needs no ebt_ctx.
+ * Limit: len <= EBT_STATIC_PARSE_MAX_BYTES per call (EBT_E_CAPACITY beyond
+ * it; stream longer files in chunks with final_chunk = 0 and *consumed).
+ * The scratch is shared by all calls on a device and keeps the last call's
+ * contents; the entry re-initialises what must start clean, but two calls that
+ * overlap on the GPU (different host threads or streams) race on it.
+ * errmsg (may be NULL) receives the message of a failure, errmsg_cap bytes. */
+#define EBT_STATIC_PARSE_MAX_BYTES (64u << 20)
+int ebt_parse_events_text_static(int device, void* cuda_stream, const char* d_text, size_t len, int final_chunk,
+								 ebt_event* d_out, int64_t cap, int64_t* n_out, size_t* consumed, char* errmsg,
+								 size_t errmsg_cap);
+
 /* tools::Replayer::next loop (tools/replayer/src/replayer.cpp:56-98) over
  * in-memory samples: events older than the next image are delivered first
  * (FeatureDetector::updatePatches), then the image (FeatureDetector::newImage,
