@@ -2,22 +2,30 @@
 """bench.py — feature-patch optimisations/s and events/s of the tracker hot path.
 
 A "step" is one pass of the hot path over one synthetic stream segment: the
-tracker is reset, then every frame (gradient grid, association, window-size
-kernel) and every inter-frame event batch (stream kernel: event scan, window
-integration, LM solves) is processed.  Workload at N=1 is BASELINE.json
-configs[1]: DAVIS346-shaped stream, 346x260, up to 500 features, ~2 Mev/s.
-At N>1 every rank tracks its own independent stream of the same shape
-(configs[3], sharding by stream; no collective on the data path).
+trackers are reset, then every frame (gradient grid, association, window-size
+kernel) and every inter-frame event batch (prefilter + stream kernel: event
+scan, window integration, LM solves) is processed.
+
+Workloads (BASELINE.json configs):
+  c3 (default at --gpus 1)  640x480, <= 2000 features, ~10 Mev/s: the largest
+                            single-GPU configuration, one stream
+  c2 / c1                   346x260 x 500 features / 240x180 x 100 features
+  c4 (default at --gpus N>1) configs[3] as written: 64 independent C2-shaped
+                            streams in total (seeds 2000..2063), stream s on GPU
+                            s mod N, every GPU's streams in ONE launch per
+                            batch (ebt_push_events_multi); "scaling": "strong"
+With c1/c2/c3 at N>1 every rank tracks its own stream(s) of that shape ("weak").
 
   value  : optimisations/s with frames and events already resident in HBM
-           (ebt_new_frame_begin_device / ebt_push_events_device)
   e2e    : same metric through the host-buffer C-ABI calls (pinned host
            events, H2D inside the timed region, records/tracks D2H inside)
+  parity : the GPU step's records against the CPU reference's on the sample the
+           cpu_baseline leg tracks anyway (same stream, same events)
   roofline / cpu_baseline : see DESIGN.md "Measurement"
 
 `--impl reference` times the reference's own CPU code for the same path
 (oracle/_ref/libebt_ref.so: unmodified Patch + Optimizer + Ceres) on the host
-cores, features sharded over threads, on a bounded sample of the same stream.
+cores, one independent stream sample per host thread (the path shards by stream).
 """
 import argparse
 import json
@@ -26,6 +34,7 @@ import subprocess
 import sys
 import threading
 import time
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 
@@ -33,19 +42,25 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 from event_based_odomety_b200 import multi, synth  # noqa: E402
-from event_based_odomety_b200.records import EVENT, OPT_RECORD, TRACK  # noqa: E402
+from event_based_odomety_b200.records import OPT_RECORD  # noqa: E402
 
 WORKLOADS = {
     # name: (width, height, max_features, target rate ev/s, base seed)
     "c1": (240, 180, 100, 0.5e6, 1001),
     "c2": (346, 260, 500, 2.0e6, 1002),
     "c3": (640, 480, 2000, 10.0e6, 1003),
+    "c4": (346, 260, 500, 2.0e6, 2000),  # 64 streams of the c2 shape, seeds 2000 + s
 }
+C4_STREAMS = 64
 METRIC = "feature-patch optimisations/sec"
+POS_TOL_PX, ANGLE_TOL_DEG = 0.05, 0.5  # north_star parity gates
 
 
-def workload_name(key):
+def workload_name(key, total_streams=1):
     w, h, feat, rate, _ = WORKLOADS[key]
+    if key == "c4":
+        return (f"c4: {total_streams} independent {w}x{h} synthetic streams, <= {feat} features each (25x25 patches), "
+                f"~{rate / 1e6:g} Mev/s each, sharded by stream")
     return f"{key}: {w}x{h} synthetic stream, <= {feat} features (25x25 patches), ~{rate / 1e6:g} Mev/s"
 
 
@@ -55,15 +70,19 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS),
+                    help="default: c3 on one GPU, c4 (64 streams over the GPUs) on several")
     ap.add_argument("--duration", type=float, default=0.30, help="stream seconds per step")
-    ap.add_argument("--stream-kernel", type=int, default=0, choices=[0, 1],
-                    help="ebt_set_stream_kernel: 0 one CTA per feature, 1 two features per CTA sharing its pixel warps")
-    ap.add_argument("--streams", type=int, default=1,
-                    help="independent streams tracked concurrently per GPU (configs[3] throughput mode)")
-    ap.add_argument("--cpu-frames", type=int, default=2, help="frames of the stream in the CPU sample")
+    ap.add_argument("--stream-kernel", type=int, default=1, choices=[0, 1, 2],
+                    help="ebt_set_stream_kernel: 0 one CTA per feature, 2 persistent CTAs sharing pixel warps, 1 automatic")
+    ap.add_argument("--streams", type=int, default=None,
+                    help="c4: total number of streams over all GPUs (default 64); c1-c3: streams per GPU (default 1)")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU time budget of the cpu_baseline / parity sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    return ap.parse_args()
+    a = ap.parse_args()
+    if a.workload is None:
+        a.workload = "c3" if a.gpus <= 1 else "c4"
+    return a
 
 
 class FlowCache:
@@ -84,23 +103,18 @@ class FlowCache:
         return self.cache[key]
 
 
-def run_step(tr, S, flows, frame_fn, push_fn, n_frames):
-    """Replayer/Evaluator order (replayer.cpp:56-98): image k, then the events
-    before image k+1."""
-    total = 0
-    for k in range(n_frames):
-        frame_fn(k)
-        ids, xy = tr.get_uninit()
-        if len(ids):
-            found, nxt = flows.get(k, ids, xy)
-            if hasattr(tr, "set_flows"):
-                tr.set_flows(ids, found, nxt)
-            else:
-                for i in range(len(ids)):
-                    tr.set_flow(ids[i], found[i], nxt[i, 0], nxt[i, 1])
-        tr.new_frame_end()
-        total += push_fn(k)
-    return total
+def frame_phase(tr, S, flows, frame_fn, k):
+    """FeatureDetector::newImage for image k (Replayer/Evaluator order, replayer.cpp:56-98)."""
+    frame_fn(k)
+    ids, xy = tr.get_uninit()
+    if len(ids):
+        found, nxt = flows.get(k, ids, xy)
+        if hasattr(tr, "set_flows"):
+            tr.set_flows(ids, found, nxt)
+        else:
+            for i in range(len(ids)):
+                tr.set_flow(ids[i], found[i], nxt[i, 0], nxt[i, 1])
+    tr.new_frame_end()
 
 
 class ClockSampler(threading.Thread):
@@ -152,34 +166,80 @@ def cpu_lib():
     return (ref, "reference") if ref is not None else (load_oracle(), "port")
 
 
-def cpu_run(S, max_feat, n_frames, threads):
-    """Reference CPU tracker on the first n_frames frames (+ their event
-    batches).  threads > 1: the path shards by independent stream,
-    so every host thread tracks its own copy of the stream sample with its own
-    tracker instance (ctypes releases the GIL); units = threads x optimisations."""
+def cpu_sample(S, max_feat, lib, budget_s=None, max_events=None, slice_events=20000):
+    """The reference CPU tracker on the head of stream S: image 0, its event batch
+    (new patches only collect events until the next image gives them a flow), image
+    1, then the events after it in slices until the time budget or max_events is
+    used up (never past the stream).  The clock starts at image 1: the warm-in batch
+    holds no optimisation, and a short sample would otherwise be dominated by it.
+    Returns (optimisations, stream events consumed in all, seconds from image 1 on,
+    records, events consumed from image 1 on)."""
     from tests._oracle import CpuTracker
-    lib, kind = cpu_lib()
+    tr = CpuTracker(lib, S.width, S.height, max_feat)
     flows = FlowCache(S)
-    counts = [0] * threads
-
-    def work(t):
-        tr = CpuTracker(lib, S.width, S.height, max_feat)
-
-        def frame_fn(k):
-            tr.new_frame_begin(S.frames[k], S.frame_ts[k], S.corners[k])
-        counts[t] = run_step(tr, S, flows, frame_fn, lambda k: tr.push_events(S.events_between(k)), n_frames)
-        tr.close()
-
+    nF = len(S.frames)
     t0 = time.perf_counter()
-    if threads == 1:
-        work(0)
-    else:
-        th = [threading.Thread(target=work, args=(t,)) for t in range(threads)]
-        [x.start() for x in th]
-        [x.join() for x in th]
+    n_opt = consumed = first = 0
+    for k in range(nF):
+        if k == 1:
+            t0 = time.perf_counter()
+        frame_phase(tr, S, flows, lambda kk: tr.new_frame_begin(S.frames[kk], S.frame_ts[kk], S.corners[kk]), k)
+        ev = S.events_between(k)
+        if k == 0:
+            n_opt += tr.push_events(ev)
+            consumed += len(ev)
+            first = consumed
+            continue
+        pos = 0
+        stop = False
+        while pos < len(ev):
+            m = min(slice_events, len(ev) - pos)
+            if max_events is not None:
+                m = min(m, max_events - consumed)
+                if m <= 0:
+                    stop = True
+                    break
+            n_opt += tr.push_events(ev[pos:pos + m])
+            pos += m
+            consumed += m
+            if budget_s is not None and time.perf_counter() - t0 > budget_s:
+                stop = True
+                break
+        if stop or pos < len(ev):
+            break
     dt = time.perf_counter() - t0
-    n_ev = sum(len(S.events_between(k)) for k in range(n_frames))
-    return sum(counts), n_ev * threads, dt, kind
+    rec = tr.records().copy()
+    tr.close()
+    return n_opt, consumed, dt, rec, consumed - first
+
+
+def parity_gate(cpu_rec, gpu_rec, consumed):
+    """North-star gates on the sample both sides tracked: the same optimisations at the
+    same stream events for the same tracks, positions within 0.05 px, flow angle within
+    0.5 degrees, same window sizes and lost flags."""
+    g = gpu_rec[gpu_rec["event_index"] < consumed]
+    out = {"checked": int(len(cpu_rec)), "gpu_records_on_sample": int(len(g)), "events": int(consumed)}
+    same = len(g) == len(cpu_rec) and np.array_equal(g["event_index"], cpu_rec["event_index"]) \
+        and np.array_equal(g["track_id"], cpu_rec["track_id"])
+    out["same_optimisations"] = bool(same)
+    if same and len(g):
+        d = np.abs(g["flow_dir"] - cpu_rec["flow_dir"]) % (2 * np.pi)
+        out["max_dpos_px"] = float(np.hypot(g["x"] - cpu_rec["x"], g["y"] - cpu_rec["y"]).max())
+        out["max_dangle_deg"] = float(np.rad2deg(np.minimum(d, 2 * np.pi - d)).max())
+        if (cpu_rec["n_successful"] >= 0).all():  # the reference build reports final costs only (-1 here)
+            out["same_lm_path"] = float(((g["n_successful"] == cpu_rec["n_successful"])
+                                         & (g["n_unsuccessful"] == cpu_rec["n_unsuccessful"])
+                                         & (g["termination"] == cpu_rec["termination"])).mean())
+        out["max_dcost"] = float(np.abs(g["final_cost"] - cpu_rec["final_cost"]).max())
+        out["same_window_sizes"] = bool(np.array_equal(g["num_of_events"], cpu_rec["num_of_events"]))
+        out["same_lost_flags"] = bool(np.array_equal(g["lost"] != 0, cpu_rec["lost"] != 0))
+        out["ok"] = bool(out["max_dpos_px"] <= POS_TOL_PX and out["max_dangle_deg"] <= ANGLE_TOL_DEG
+                         and out["same_window_sizes"] and out["same_lost_flags"])
+    else:
+        out["ok"] = bool(same)
+    out["gates"] = (f"position <= {POS_TOL_PX} px, flow angle <= {ANGLE_TOL_DEG} deg, same events / tracks / "
+                    f"window sizes / lost flags")
+    return out
 
 
 def main_reference(args):
@@ -187,27 +247,56 @@ def main_reference(args):
     if rank != 0:
         return
     w, h, feat, rate, seed = WORKLOADS[args.workload]
-    S = synth.make_stream(w, h, args.duration, rate, seed, max_corners=feat)  # same stream as our arm
-    args.cpu_frames = min(args.cpu_frames, len(S.frames))
     cores = os.cpu_count() or 1
-    for _ in range(args.warmup if args.warmup < 2 else 1):  # CPU needs no clock warm-up; one pass
-        cpu_run(S, feat, min(2, args.cpu_frames), cores)
+    total_streams = args.streams or C4_STREAMS
+    if args.workload == "c4":
+        # one stream of the job per host thread (streams 0 .. cores-1 of the 64)
+        specs = [(w, h, args.duration, rate, seed + s, feat) for s in range(min(cores, total_streams))]
+        streams = synth.make_streams(specs, cores)
+        streams = [streams[t % len(streams)] for t in range(cores)]
+    else:
+        streams = [synth.make_stream(w, h, args.duration, rate, seed, max_corners=feat)] * cores  # our arm's stream
+    lib, kind = cpu_lib()
+    # bounded sample: all steps together get about two minutes of host time
+    budget = max(2.0, min(24.0, 120.0 / max(args.steps, 1)))
+    # events after image 1 one thread gets through in the budget (measured on one thread first)
+    _, _, dt0, _, after0 = cpu_sample(streams[0], feat, lib, budget_s=min(3.0, budget))
+    first = len(streams[0].events_between(0))
+    per_s = max(after0 / max(dt0, 1e-3), 1.0)
+    max_events = first + int(per_s * budget * 0.8)  # all cores busy run slower than one alone
+
+    def one_pass(limit):
+        res = [None] * cores
+
+        def work(t):
+            res[t] = cpu_sample(streams[t], feat, lib, max_events=limit)
+        th = [threading.Thread(target=work, args=(t,)) for t in range(cores)]
+        [x.start() for x in th]
+        [x.join() for x in th]
+        # every thread's clock starts at its image 1; the slowest thread's span is the step
+        return sum(r[0] for r in res), sum(r[4] for r in res), max(r[2] for r in res)
+
+    warm = 1 if args.warmup > 0 else 0  # the CPU needs no clock warm-up: one short pass loads code and data
+    for _ in range(warm):
+        one_pass(first + max(1, (max_events - first) // 8))
     times, opts, nev = [], 0, 0
     for _ in range(args.steps):
-        n, ne, dt, kind = cpu_run(S, feat, args.cpu_frames, cores)
+        n, ne, dt = one_pass(max_events)
         times.append(dt)
         opts, nev = n, ne
     T = float(np.sum(times))
     value = opts * args.steps / T
-    sample = (f"first {args.cpu_frames} frames + event batches of the {args.workload} stream "
-              f"({nev} events, {opts} optimisations per step summed over {cores} host threads, "
-              f"one independent copy of the stream sample per thread)")
+    sample = (f"per host thread: one stream of the workload up to stream event {max_events}, timed from image 1 on "
+              f"(the warm-in batch before it holds no optimisation): {nev} events, {opts} optimisations per step "
+              f"summed over {cores} host threads, step time = the slowest thread; {warm} short warm-up pass run, "
+              f"the CPU needs no clock warm-up")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "optimisations/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": T / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": warm, "warmup_requested": args.warmup,
+        "ms_per_step": T / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "strong" if args.workload == "c4" else "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(args.workload), "sample": sample},
+        "config": {"workload": workload_name(args.workload, total_streams), "sample": sample},
         "events_per_s": nev * args.steps / T,
         "cpu_baseline": {"value": value, "unit": "optimisations/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "optimisations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -220,19 +309,18 @@ def main_reference(args):
 # Our arm
 # ---------------------------------------------------------------------------
 class Lane:
-    """One event stream of this rank: its tracker context (own CUDA stream), its
-    frames and events resident in HBM and in pinned host memory."""
+    """One event stream of this rank: its tracker context, its frames and events
+    resident in HBM and in pinned host memory."""
 
-    def __init__(self, torch, Tracker, wl, duration, seed, device, stream_kernel=0):
-        w, h, feat, rate, _ = wl
-        self.S = S = synth.make_stream(w, h, duration, rate, seed, max_corners=feat)
+    def __init__(self, torch, Tracker, S, feat, device, stream_kernel):
+        self.S = S
         self.nF = len(S.frames)
         t = S.events["t_us"]
         self.bounds = [(int(np.searchsorted(t, S.frame_ts[k], "left")),
                         int(np.searchsorted(t, S.frame_ts[k + 1], "left")) if k + 1 < self.nF else len(S.events))
                        for k in range(self.nF)]
         self.n_events = self.bounds[-1][1] - self.bounds[0][0]
-        self.tr = Tracker(w, h, feat, device=device, record_capacity=1 << 20)
+        self.tr = Tracker(S.width, S.height, feat, device=device, record_capacity=1 << 20)
         self.tr.set_stream_kernel(stream_kernel)
         self.flows = FlowCache(S)
         ev_bytes = torch.from_numpy(S.events.view(np.uint8).reshape(-1).copy())
@@ -246,24 +334,16 @@ class Lane:
     def frame_host(self, k):
         self.tr.new_frame_begin(self.S.frames[k], self.S.frame_ts[k], self.S.corners[k])
 
-    def push_dev(self, k):
+    def batch(self, k, host):
         lo, hi = self.bounds[k]
-        return self.tr.push_events_device(self.d_events.data_ptr() + lo * 16, hi - lo)
-
-    def push_host(self, k):
-        lo, hi = self.bounds[k]
-        return self.tr.push_events_ptr(self.h_events.data_ptr() + lo * 16, hi - lo)
-
-    def step(self, host):
-        self.tr.reset()
-        return run_step(self.tr, self.S, self.flows, self.frame_host if host else self.frame_dev,
-                        self.push_host if host else self.push_dev, self.nF)
+        base = self.h_events.data_ptr() if host else self.d_events.data_ptr()
+        return base + lo * 16, hi - lo
 
 
 def main_ours(args):
     import torch
     import torch.distributed as dist
-    from event_based_odomety_b200.cabi import K_GRAD, K_NUMEV, K_TRACK, Tracker
+    from event_based_odomety_b200.cabi import K_GRAD, K_NUMEV, K_TRACK, Tracker, push_events_multi
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -274,51 +354,75 @@ def main_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    wl = WORKLOADS[args.workload]
-    w, h, feat, rate, seed = wl
-    # global stream g = rank * streams + lane; stream 0 is the named stream, every
-    # further one an independent stream of the same shape (configs[3], seeds 2000 + g)
-    nS = max(1, args.streams)
-    lanes = [Lane(torch, Tracker, wl, args.duration, multi.stream_seed(seed, rank * nS + s), local, args.stream_kernel)
-             for s in range(nS)]
+    w, h, feat, rate, seed = WORKLOADS[args.workload]
+    cores = max(1, (os.cpu_count() or 1) // max(1, min(world, 8)))
+    if args.workload == "c4":
+        total_streams = args.streams or C4_STREAMS
+        mine = multi.streams_of_rank(total_streams, rank, world)  # stream s -> GPU s mod G
+        scaling = "strong"
+        specs = [(w, h, args.duration, rate, seed + s, feat) for s in mine]
+    else:
+        per = max(1, args.streams or 1)
+        total_streams = per * world
+        scaling = "weak"
+        # global stream g = rank * per + lane; stream 0 is the named stream, every further one
+        # an independent stream of the same shape (seeds 2000 + g)
+        specs = [(w, h, args.duration, rate, multi.stream_seed(seed, rank * per + s), feat) for s in range(per)]
+    if not specs:
+        raise SystemExit(f"bench.py: rank {rank} has no stream (fewer streams than GPUs)")
+    streams = synth.make_streams(specs, cores)
+    lanes = [Lane(torch, Tracker, S, feat, local, args.stream_kernel) for S in streams]
+    nS = len(lanes)
+    trackers = [L.tr for L in lanes]
     L0 = lanes[0]
-    S, nF, tr = L0.S, L0.nF, L0.tr
+    nF = max(L.nF for L in lanes)
     n_events = sum(L.n_events for L in lanes)
-    fp64_peak, fp32_peak = tr.measure_fma_peak()
+    fp64_peak, fp32_peak = trackers[0].measure_fma_peak()
     # L2 flush between steps: 256 MB (> the 126 MB L2) rewritten at the start of
     # every step, inside the timed region (~0.05 ms)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     torch.cuda.synchronize()
+    pool = ThreadPoolExecutor(max_workers=min(nS, max(1, min(cores, 8)))) if nS > 1 else None
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def all_lanes(host):
-        """One step of every stream of this rank; streams run concurrently, one
-        host thread and one CUDA stream each (ctypes releases the GIL)."""
-        if nS == 1:
-            return L0.step(host)
-        out = [0] * nS
+    def step(host):
+        """One step of every stream of this rank.  Per image: the frames of all streams
+        (host logic per stream: a few host threads, ctypes releases the GIL), then ONE
+        ebt_push_events_multi for the event batches of all of them."""
+        for L in lanes:
+            L.tr.reset()
+        total = 0
+        for k in range(nF):
+            live = [L for L in lanes if k < L.nF]
 
-        def work(i):
-            out[i] = lanes[i].step(host)
-        th = [threading.Thread(target=work, args=(i,)) for i in range(nS)]
-        [x.start() for x in th]
-        [x.join() for x in th]
-        return sum(out)
+            def frame(L):
+                frame_phase(L.tr, L.S, L.flows, L.frame_host if host else L.frame_dev, k)
+            if pool is not None:
+                list(pool.map(frame, live))
+            else:
+                for L in live:
+                    frame(L)
+            if len(live) == 1:
+                ptr, n = live[0].batch(k, host)
+                total += live[0].tr.push_events_ptr(ptr, n) if host else live[0].tr.push_events_device(ptr, n)
+            else:
+                b = [L.batch(k, host) for L in live]
+                total += sum(push_events_multi([L.tr for L in live], [p for p, _ in b], [n for _, n in b],
+                                               device_resident=not host))
+        return total
 
     def timed(host, steps, with_timing):
         """K steps bracketed by barrier + synchronize; device time by CUDA events
-        (the library syncs its own stream inside every call, so the events on
+        (the library syncs its own streams inside every call, so the events on
         the current stream bracket all of its work)."""
         barrier()
-        if with_timing and nS == 1:
-            # per-kernel CUDA events on the library stream; with several streams per
-            # GPU the kernels overlap and the events would serialise them, so the
-            # launch counts are then taken from one extra untimed step below
-            tr.timing(True)
+        if with_timing:
+            for t in trackers:
+                t.timing(True)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         t0 = time.perf_counter()
@@ -326,7 +430,7 @@ def main_ours(args):
         for _ in range(steps):
             flush.zero_()
             torch.cuda.current_stream().synchronize()
-            opts += all_lanes(host)
+            opts += step(host)
         e1.record()
         barrier()
         wall = time.perf_counter() - t0
@@ -335,28 +439,22 @@ def main_ours(args):
 
     for _ in range(max(args.warmup, 0)):
         flush.zero_()  # also loads torch's fill kernel outside the timed region
-        all_lanes(False)
+        step(False)
     sampler = ClockSampler(local)
     sampler.start()
     opts, secs, wall = timed(False, args.steps, True)
     kt_ms = kt_n = kg_ms = kg_n = kn_ms = kn_n = 0
-    for L in lanes:
-        a, b = L.tr.timing_get(K_TRACK); kt_ms += a; kt_n += b
-        a, b = L.tr.timing_get(K_GRAD); kg_ms += a; kg_n += b
-        a, b = L.tr.timing_get(K_NUMEV); kn_ms += a; kn_n += b
-    flops_step = sum(lm_flops(L.tr.records()) for L in lanes)  # records of the last step
-    if nS > 1:
-        for L in lanes:
-            L.tr.timing(True)
-        all_lanes(False)
-        kt_n, kg_n, kn_n = (args.steps * sum(L.tr.timing_get(k)[1] for L in lanes) for k in (K_TRACK, K_GRAD, K_NUMEV))
-        kg_ms, kn_ms = (args.steps * sum(L.tr.timing_get(k)[0] for L in lanes) for k in (K_GRAD, K_NUMEV))
-    for L in lanes:
-        L.tr.timing(False)
-    all_lanes(True)  # e2e warm-up
+    for t in trackers:
+        a, b = t.timing_get(K_TRACK); kt_ms += a; kt_n += b
+        a, b = t.timing_get(K_GRAD); kg_ms += a; kg_n += b
+        a, b = t.timing_get(K_NUMEV); kn_ms += a; kn_n += b
+        t.timing(False)
+    flops_step = sum(lm_flops(t.records()) for t in trackers)  # records of the last step
+    gpu_rec0 = trackers[0].records().copy()
+    step(True)  # e2e warm-up
     e_opts, e_secs, _ = timed(True, args.steps, False)
     clocks = sampler.result()
-    n_tracks = sum(len(L.tr.tracks()) + len(L.tr.tracks(True)) for L in lanes)
+    n_tracks = sum(len(t.tracks()) + len(t.tracks(True)) for t in trackers)
 
     # whole-job aggregate: sum of units over ranks / max time over ranks
     def agg(units, seconds):
@@ -365,12 +463,14 @@ def main_ours(args):
     g_opts, g_secs = agg(opts, secs)
     g_events, _ = agg(n_events * args.steps, secs)
     ge_opts, ge_secs = agg(e_opts, e_secs)
+    g_flops, _ = agg(flops_step, secs)
+    g_kt, _ = agg(kt_ms, secs)
+    per_rank = multi.gather_rows([rank, nS, opts / args.steps, secs / args.steps * 1e3, e_opts / args.steps,
+                                  e_secs / args.steps * 1e3, kt_ms / args.steps], device="cuda")
 
     if rank == 0:
         opts_step = opts / args.steps
-        # stream-kernel time per step; with several streams per GPU their kernels
-        # overlap, so the kernel's time is the step itself
-        kt_s = kt_ms * 1e-3 / args.steps if nS == 1 else secs / args.steps
+        kt_s = kt_ms * 1e-3 / args.steps  # prefilter + stream kernel of this rank, CUDA events on the library stream
         achieved = flops_step / kt_s / 1e12 if kt_s > 0 else 0.0
         hbm_bytes = 16.0 * n_events + (2500.0 + 128.0) * opts_step
         peaks = {}
@@ -379,28 +479,33 @@ def main_ours(args):
         except Exception:
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-        traffic = None  # DRAM bytes of one stream-kernel launch, from the committed ncu --set full capture
-        try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_kernel_traffic.json")))[
-                "track_batch_kernel"]["dram_bytes_per_launch"]
-        except Exception:
-            pass
+        # DRAM bytes and FP64-pipe utilisation of one stream-kernel launch, from the committed ncu --set full capture
+        ncu = {}
+        for name in ("r2_kernel_traffic.json", "r1_kernel_traffic.json"):
+            try:
+                ncu = json.load(open(os.path.join(ROOT, "profiles", name)))
+                ncu["file"] = "profiles/" + name
+                break
+            except Exception:
+                pass
+        multi_launch = args.stream_kernel != 0 and (nS > 1 or args.stream_kernel == 2 or feat > 2 * 148)
+        kname = "track_multi_kernel" if multi_launch and "track_multi_kernel" in ncu else "track_batch_kernel"
+        ncu_k = ncu.get(kname, {})
         launches_step = kt_n / args.steps
-        if world > 1 or nS > 1:
-            sharding = (f"{nS} independent stream(s) per GPU (one context + CUDA stream + host thread each), "
-                        f"{world} GPU(s), no collective")
-        else:
-            sharding = "single stream"
+        kernel_name = ("track_multi_kernel (persistent CTAs: 2 leader warps + 4 pixel warps)" if multi_launch
+                       else "track_batch_kernel (one CTA per feature)")
         line = {
             "metric": METRIC, "value": g_opts / g_secs, "unit": "optimisations/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": g_secs / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "ms_per_step": g_secs / args.steps * 1e3, "higher_is_better": True, "scaling": scaling,
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {
-                "workload": workload_name(args.workload),
-                "segment": f"{args.duration:g} s = {nF} frames, {n_events} events, {int(opts_step)} optimisations, "
-                           f"{n_tracks} tracks per step" + (f" over {nS} streams" if nS > 1 else ""),
-                "sharding": sharding,
+                "workload": workload_name(args.workload, total_streams),
+                "segment": f"{args.duration:g} s = {nF} frames per stream; rank 0: {n_events} events, {int(opts_step)} "
+                           f"optimisations, {n_tracks} tracks per step over its {nS} stream(s)",
+                "sharding": (f"{total_streams} stream(s) over {world} GPU(s) ({nS} on rank 0: one context each, all of a "
+                             f"GPU's batches in one ebt_push_events_multi launch), no collective on the data path"
+                             if total_streams > 1 else "single stream"),
                 "l2": "flushed: a 256 MB buffer (> 126 MB L2) is rewritten at the start of every step, inside the "
                       "timed region; a step then reads its event stream (%.1f MB) and template grids from HBM once, "
                       "the kernel is FP64-pipe bound (see roofline)" % (n_events * 16 / 1e6),
@@ -410,40 +515,53 @@ def main_ours(args):
                     "h2d_bytes_per_step": int(n_events * 16 + sum(
                         L.nF * w * h + 8 * sum(len(c) * 2 for c in L.S.corners) for L in lanes)),
                     "d2h_bytes_per_step": int(opts_step * OPT_RECORD.itemsize + 2 * nF * feat * 288 * nS)},
-            # every push launches prefilter_kernel + track_batch_kernel
+            # every push launches one prefilter kernel + one stream kernel; every frame of every
+            # stream one gradient and one window-size kernel
             "gpu_launches": int(2 * kt_n + kg_n + kn_n),
-            "roofline": {"bound": "fp64",
-                         "kernel": "track_batch_kernel (timed with its prefilter_kernel, 1.4 % of it)" if nS == 1 else
-                         f"track_batch_kernel of {nS} concurrent streams (kernels overlap: time = the step)",
+            "roofline": {"bound": "fp64", "kernel": kernel_name + ", timed with its prefilter kernel",
                          "achieved": achieved,
                          "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
-                         "traffic": traffic, "traffic_unit": "DRAM bytes per launch (ncu --set full, profiles/r1_track_batch_kernel_ncu_metrics.json)",
+                         "frac_all_ranks": (g_flops / (g_kt * 1e-3 / args.steps / world) / 1e12 / fp64_peak / world
+                                            if g_kt > 0 and fp64_peak else None),
+                         "traffic": ncu_k.get("dram_bytes_per_launch"),
+                         "traffic_unit": "DRAM bytes per launch (ncu --set full, %s)" % ncu.get("file"),
+                         "fp64_pipe_util_ncu": ncu_k.get("fp64_pipe_util"),
+                         "fp64_pipe_util_note": "executed FP64-pipe utilisation of this kernel in the committed ncu "
+                                                "capture (north_star asks for pipe utilisation; frac counts the "
+                                                "reference's algorithmic flops, ~1.5x what the fused pass executes)",
                          "launches_per_step": launches_step,
                          "algorithmic_flops_per_launch": flops_step / launches_step if launches_step else None,
                          "kernel_ms_per_launch": kt_s * 1e3 / launches_step if launches_step else None,
                          "peak_source": "measured in this run: dependent-chain DFMA microbenchmark "
-                         "(ebt_measure_fma_peak); FP32 non-tensor peak measured %.1f TFLOP/s" % fp32_peak,
+                         "(ebt_measure_fma_peak); FP32 non-tensor peak measured %.1f TFLOP/s; theoretical "
+                         "37.2 / 74.5 TFLOP/s at 1965 MHz" % fp32_peak,
                          "algorithmic_flops_per_step": flops_step, "kernel_ms_per_step": kt_s * 1e3,
                          "kernel_share_of_step": kt_s / (secs / args.steps)},
-            "roofline_hbm": {"bound": "hbm", "kernel": "track_batch_kernel (event scan + integration side)",
+            "roofline_hbm": {"bound": "hbm", "kernel": "stream kernel (event scan + integration side)",
                              "achieved": hbm_bytes / kt_s / 1e9 if kt_s > 0 else 0.0, "peak": hbm_peak,
                              "unit": "GB/s", "frac": hbm_bytes / kt_s / 1e9 / hbm_peak if kt_s > 0 else None,
                              "algorithmic_bytes_per_step": hbm_bytes},
             "other_kernels_ms_per_step": {"grad_kernel": kg_ms / args.steps, "num_events_kernel": kn_ms / args.steps},
+            "per_rank": [{"rank": int(r[0]), "streams": int(r[1]), "optimisations_per_step": r[2], "ms_per_step": r[3],
+                          "e2e_optimisations_per_step": r[4], "e2e_ms_per_step": r[5], "stream_kernel_ms_per_step": r[6]}
+                         for r in per_rank],
             "clocks": clocks,
             "wall_s_timed_region": wall,
         }
         if not args.no_cpu_baseline:
-            cf = min(args.cpu_frames, nF)
-            n, ne, dt, kind = cpu_run(S, feat, cf, 1)
-            line["cpu_baseline"] = {
-                "value": n / dt, "unit": "optimisations/s", "cores": 1, "kind": kind,
-                "events_per_s": ne / dt,
-                "sample": f"first {cf} frames + event batches of the same stream ({ne} events, {n} optimisations, "
-                          f"{dt:.1f} s), single thread as the reference runs it"}
+            lib, kind = cpu_lib()
+            n, consumed, dt, cpu_rec, after = cpu_sample(L0.S, feat, lib, budget_s=args.cpu_seconds)
+            sample = (f"rank 0's first stream up to stream event {consumed}, timed from image 1 on (the warm-in batch "
+                      f"before it holds no optimisation): {after} events, {n} optimisations, {dt:.1f} s, single "
+                      f"thread as the reference runs it")
+            line["cpu_baseline"] = {"value": n / dt, "unit": "optimisations/s", "cores": 1, "kind": kind,
+                                    "events_per_s": after / dt, "sample": sample}
+            line["parity"] = parity_gate(cpu_rec, gpu_rec0, consumed)
+            line["parity"]["against"] = ("oracle/_ref (the reference's Patch + Optimizer + Ceres, compiled unmodified)"
+                                         if kind == "reference" else "oracle port")
         emit(line)
-    for L in lanes:
-        L.tr.close()
+    for t in trackers:
+        t.close()
     if world > 1:
         dist.destroy_process_group()
 

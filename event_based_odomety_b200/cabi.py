@@ -65,6 +65,7 @@ EXPORTS = {
     "ebt_get_features": (C.c_int, [_vp, _vp, C.c_int, C.POINTER(C.c_int)]),
     "ebt_push_events": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
     "ebt_push_events_device": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
+    "ebt_push_events_multi": (C.c_int, [_vp, C.c_int, _vp, _vp, C.c_int, _vp]),
     "ebt_parse_events_text": (C.c_int, [_vp, C.c_char_p, C.c_size_t, C.c_int, _vp, C.c_int64,
                                         C.POINTER(C.c_int64), C.POINTER(C.c_size_t)]),
     "ebt_parse_events_text_static": (C.c_int, [C.c_int, _vp, _vp, C.c_size_t, C.c_int, _vp, C.c_int64,
@@ -134,6 +135,32 @@ def _ptr(a):
 
 
 K_TRACK, K_BATCH, K_GRAD, K_NUMEV, K_CORNERS, K_PYRAMID, K_LK, K_PARSE = range(8)
+
+
+def push_events_multi(trackers, events, counts=None, device_resident=False):
+    """ebt_push_events_multi: one batch per tracker in one launch.  events: list of
+    numpy EVENT arrays (host) or of raw pointers with `counts` (host pinned or device).
+    Returns the optimisation count per stream."""
+    lib = load()
+    S = len(trackers)
+    ctxs = (_vp * S)(*[t.ctx for t in trackers])
+    keep = []
+    if counts is None:
+        arrs = [np.ascontiguousarray(e) for e in events]
+        for a in arrs:
+            assert a.dtype == EVENT
+        keep = arrs
+        ptrs = (_vp * S)(*[a.ctypes.data if len(a) else None for a in arrs])
+        counts = [len(a) for a in arrs]
+    else:
+        ptrs = (_vp * S)(*[int(p) if p else None for p in events])
+    n = (C.c_int64 * S)(*[int(c) for c in counts])
+    out = (C.c_int64 * S)()
+    rc = lib.ebt_push_events_multi(ctxs, S, ptrs, n, int(bool(device_resident)), out)
+    del keep
+    if rc != 0:
+        raise EbtError(f"ebt error {rc}: {lib.ebt_last_error(trackers[0].ctx).decode()}")
+    return [int(v) for v in out]
 
 
 STATIC_PARSE_MAX_BYTES = 64 << 20  # EBT_STATIC_PARSE_MAX_BYTES (include/ebt.h)

@@ -9,6 +9,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstddef>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -93,8 +94,12 @@ struct ebt_ctx
 	cudaStream_t stream = nullptr;
 	std::string err;
 
-	Frame frames[EBT_MAX_FRAMES];
+	std::vector<Frame> frames = std::vector<Frame>(EBT_INIT_FRAMES);  // grows on demand (allocFrameSlot)
 	int latest = 0;
+	const double2** d_frame_ptrs = nullptr;  // device copy of frames[i].grid: FrameTable::grid
+	size_t frame_ptrs_cap = 0;
+	bool frame_ptrs_dirty = true;
+	std::vector<const double2*> h_frame_ptrs;
 
 	std::vector<DevPatch> h;        // FeatureDetector::patches_ (list order)
 	std::vector<DevPatch> arch;     // FeatureDetector::archivedPatches_
@@ -130,7 +135,23 @@ struct ebt_ctx
 	ebt_opt_record* d_records = nullptr;
 	unsigned long long* d_nrec = nullptr;
 	int* d_queue = nullptr;  // work-queue cursor of the shared-pixel-warp stream kernel
-	int stream_kernel = 0;   // ebt_set_stream_kernel
+	int stream_kernel = 1;   // ebt_set_stream_kernel
+	int sm_count = 0;
+	// launch scratch of a (multi-stream) push on the shared-pixel-warp kernel, owned by ctxs[0]
+	StreamDesc* d_descs = nullptr;
+	StreamDesc* h_descs = nullptr;  // pinned
+	size_t descs_cap = 0;
+	WorkItem* d_work = nullptr;
+	WorkItem* h_work = nullptr;  // pinned
+	size_t work_cap = 0;
+	std::vector<int> work_load, work_idx;
+	std::vector<WorkItem> work_tmp;
+	cudaEvent_t join_event = nullptr;  // orders this context's own stream before a multi-stream launch
+	double opt_per_event = 0.25;       // optimisations per stream event of the last piece (bounds the next piece)
+	unsigned char* arch_stage = nullptr;  // pinned: products of the patches archived at a frame
+	size_t arch_stage_cap = 0;
+	size_t pending_records = 0;        // records on their way into rec_stage
+	bool pending_overflow = false;
 	std::vector<ebt_opt_record> records;
 	size_t records_sorted = 0;  // records[0 .. records_sorted) are in reference order
 	std::vector<size_t> record_batches;  // end offset of every push behind records_sorted
@@ -159,7 +180,7 @@ struct ebt_ctx
 	ebt_solution* d_solutions = nullptr;
 	int* d_bnabla = nullptr;
 	ebt_event* d_bevents = nullptr;
-	size_t cap_problems = 0, cap_bnabla = 0, cap_bevents = 0;
+	size_t cap_problems = 0, cap_solutions = 0, cap_bnabla = 0, cap_bevents = 0;
 
 	bool timing = false;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -205,13 +226,48 @@ int fail(ebt_ctx* c, int code, const std::string& msg)
 						std::string(#call) + ": " + cudaGetErrorString(e_));             \
 	} while (0)
 
+// The kernels read the grid pointers from a device array; bring it up to date
+// (new grids, a grown table) before a launch that uses it.
+int syncFrameTable(ebt_ctx* ctx)
+{
+	if (!ctx->frame_ptrs_dirty) return EBT_OK;
+	const size_t n = ctx->frames.size();
+	if (n > ctx->frame_ptrs_cap)
+	{
+		CU(cudaStreamSynchronize(ctx->stream));  // kernels in flight read the old table
+		cudaFree(ctx->d_frame_ptrs);
+		ctx->d_frame_ptrs = nullptr;
+		ctx->frame_ptrs_cap = 0;
+		CU(cudaMalloc(&ctx->d_frame_ptrs, n * sizeof(const double2*)));
+		ctx->frame_ptrs_cap = n;
+	}
+	ctx->h_frame_ptrs.resize(n);
+	for (size_t i = 0; i < n; ++i) ctx->h_frame_ptrs[i] = ctx->frames[i].grid;
+	// pageable source: the copy is staged before the call returns
+	CU(cudaMemcpyAsync(ctx->d_frame_ptrs, ctx->h_frame_ptrs.data(), n * sizeof(const double2*), cudaMemcpyHostToDevice,
+					   ctx->stream));
+	ctx->frame_ptrs_dirty = false;
+	return EBT_OK;
+}
+
 FrameTable frameTable(const ebt_ctx* c)
 {
 	FrameTable ft;
-	for (int i = 0; i < EBT_MAX_FRAMES; ++i) ft.grid[i] = c->frames[i].grid;
+	ft.grid = c->d_frame_ptrs;
 	ft.latest = c->latest;
 	ft.pad = 0;
 	return ft;
+}
+
+// A slot for a new template frame: a dead one, or a new one at the end of the
+// table (FeatureDetector::optimizers_ is an unbounded map).
+int allocFrameSlot(ebt_ctx* c)
+{
+	for (size_t i = 0; i < c->frames.size(); ++i)
+		if (!c->frames[i].alive) return static_cast<int>(i);
+	c->frames.resize(c->frames.size() * 2);
+	c->frame_ptrs_dirty = true;
+	return static_cast<int>(c->frames.size() / 2);
 }
 
 cudaEvent_t takeEvent(ebt_ctx* c)
@@ -317,8 +373,8 @@ void materialise(ebt_ctx* c)
 
 int findFrame(const ebt_ctx* c, int64_t ts)
 {
-	for (int i = 0; i < EBT_MAX_FRAMES; ++i)
-		if (c->frames[i].alive && c->frames[i].ts == ts) return i;
+	for (size_t i = 0; i < c->frames.size(); ++i)
+		if (c->frames[i].alive && c->frames[i].ts == ts) return static_cast<int>(i);
 	return -1;
 }
 
@@ -327,7 +383,11 @@ int buildGrid(ebt_ctx* ctx, const uint8_t* gray, int slot, bool on_device = fals
 {
 	const size_t npx = static_cast<size_t>(ctx->prm.width) * ctx->prm.height;
 	Frame& f = ctx->frames[slot];
-	if (!f.grid) CU(cudaMalloc(&f.grid, npx * sizeof(double2)));
+	if (!f.grid)
+	{
+		CU(cudaMalloc(&f.grid, npx * sizeof(double2)));
+		ctx->frame_ptrs_dirty = true;
+	}
 	CU(cudaMemcpyAsync(ctx->d_gray, gray, npx,
 					   on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
 	tic(ctx);
@@ -441,6 +501,7 @@ int ebt_destroy(ebt_ctx* ctx)
 	if (!ctx) return EBT_E_INVALID;
 	cudaSetDevice(ctx->device);
 	for (auto& f : ctx->frames) cudaFree(f.grid);
+	cudaFree(ctx->d_frame_ptrs);
 	cudaFree(ctx->d_patches);
 	cudaFree(ctx->d_rings);
 	cudaFree(ctx->d_nablas);
@@ -451,6 +512,11 @@ int ebt_destroy(ebt_ctx* ctx)
 	cudaFree(ctx->d_records);
 	cudaFree(ctx->d_nrec);
 	cudaFree(ctx->d_queue);
+	cudaFree(ctx->d_descs);
+	cudaFreeHost(ctx->h_descs);
+	cudaFree(ctx->d_work);
+	cudaFreeHost(ctx->h_work);
+	if (ctx->join_event) cudaEventDestroy(ctx->join_event);
 	cudaFree(ctx->d_events);
 	cudaFree(ctx->d_gray);
 	cudaFree(ctx->d_lut);
@@ -462,6 +528,7 @@ int ebt_destroy(ebt_ctx* ctx)
 	cudaFree(ctx->d_order);
 	cudaFreeHost(ctx->h_order);
 	cudaFreeHost(ctx->h_stage);
+	cudaFreeHost(ctx->arch_stage);
 	cudaFreeHost(ctx->rec_stage);
 	cudaFreeHost(ctx->nrec_stage);
 	cudaFree(ctx->d_text);
@@ -565,6 +632,7 @@ int ebt_create(const ebt_params* params, int device, ebt_ctx** out)
 			return EBT_E_CUDA;                                                            \
 		}                                                                                 \
 	} while (0)
+	CUC(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
 	CUC(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
 	CUC(cudaEventCreate(&c->ev0));
 	CUC(cudaEventCreate(&c->ev1));
@@ -758,7 +826,7 @@ int ebt_debug_feature_load(ebt_ctx* ctx, int32_t* track_ids, int32_t* n_opt, uin
 
 int ebt_set_stream_kernel(ebt_ctx* ctx, int mode)
 {
-	if (!ctx || mode < 0 || mode > 1) return fail(ctx, EBT_E_INVALID, "ebt_set_stream_kernel: mode must be 0 or 1");
+	if (!ctx || mode < 0 || mode > 2) return fail(ctx, EBT_E_INVALID, "ebt_set_stream_kernel: mode must be 0, 1 or 2");
 	ctx->stream_kernel = mode;
 	return EBT_OK;
 }
@@ -792,9 +860,7 @@ static int newFrameBegin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us, const
 		return fail(ctx, EBT_E_INVALID, "ebt_new_frame_begin: bad argument");
 	CU(cudaSetDevice(ctx->device));
 	int slot = findFrame(ctx, ts_us);
-	for (int i = 0; i < EBT_MAX_FRAMES && slot < 0; ++i)
-		if (!ctx->frames[i].alive) slot = i;
-	if (slot < 0) return fail(ctx, EBT_E_CAPACITY, "ebt_new_frame_begin: too many live template frames");
+	if (slot < 0) slot = allocFrameSlot(ctx);
 	{
 		const int rc = buildGrid(ctx, gray, slot, on_device);
 		if (rc != EBT_OK) return rc;
@@ -995,6 +1061,8 @@ int ebt_new_frame_end(ebt_ctx* ctx)
 	{
 		const int rc = uploadPatches(ctx);
 		if (rc != EBT_OK) return rc;
+		const int rcf = syncFrameTable(ctx);
+		if (rcf != EBT_OK) return rcf;
 		tic(ctx);
 		CU(ebt_launch_num_events(ctx->d_patches, static_cast<int>(ctx->h.size()), frameTable(ctx),
 								 ctx->dp, ctx->stream));
@@ -1002,83 +1070,111 @@ int ebt_new_frame_end(ebt_ctx* ctx)
 		const int rc2 = downloadPatches(ctx);
 		if (rc2 != EBT_OK) return rc2;
 	}
-	// archive lost patches, keep list order (feature_detector.cpp:512-523)
-	size_t k = 0;
-	bool moved = false;
-	for (size_t i = 0; i < ctx->h.size(); ++i)
+	// archive lost patches, keep list order (feature_detector.cpp:512-523): their
+	// patch products come back through one pinned staging buffer — every copy and
+	// every clearing of a freed slot is queued on the context's stream, one wait
+	size_t n_lost = 0;
+	for (const DevPatch& p : ctx->h) n_lost += p.lost ? 1 : 0;
+	if (n_lost > 0)
 	{
-		if (ctx->h[i].lost)
+		const bool prod = ctx->dp.products != 0, cmap = ctx->dp.cost_maps != nullptr;
+		const size_t per = EBT_PATCH_PIXELS * sizeof(int) +
+						   (prod ? EBT_PATCH_PIXELS * (sizeof(int) + sizeof(double)) : 0) + (cmap ? 121 * sizeof(double) : 0);
+		if (n_lost * per > ctx->arch_stage_cap)
 		{
-			std::vector<int> nab(EBT_PATCH_PIXELS);
-			CU(cudaMemcpy(nab.data(), ctx->d_nablas + static_cast<size_t>(ctx->h[i].store_slot) * EBT_PATCH_PIXELS,
-						  EBT_PATCH_PIXELS * sizeof(int), cudaMemcpyDeviceToHost));
-			CU(cudaMemset(ctx->d_nablas + static_cast<size_t>(ctx->h[i].store_slot) * EBT_PATCH_PIXELS, 0,
-						  EBT_PATCH_PIXELS * sizeof(int)));
-			if (ctx->dp.products)
+			cudaFreeHost(ctx->arch_stage);
+			ctx->arch_stage = nullptr;
+			ctx->arch_stage_cap = 0;
+			const size_t cap = n_lost * per * 2 + 65536;
+			CU(cudaHostAlloc(&ctx->arch_stage, cap, cudaHostAllocDefault));
+			ctx->arch_stage_cap = cap;
+		}
+		unsigned char* dst = ctx->arch_stage;
+		for (const DevPatch& p : ctx->h)
+		{
+			if (!p.lost) continue;
+			const size_t off = static_cast<size_t>(p.store_slot) * EBT_PATCH_PIXELS;
+			CU(cudaMemcpyAsync(dst, ctx->d_nablas + off, EBT_PATCH_PIXELS * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+			CU(cudaMemsetAsync(ctx->d_nablas + off, 0, EBT_PATCH_PIXELS * sizeof(int), ctx->stream));
+			dst += EBT_PATCH_PIXELS * sizeof(int);
+			if (prod)
 			{
-				const size_t off = static_cast<size_t>(ctx->h[i].store_slot) * EBT_PATCH_PIXELS;
-				std::vector<int> mc(EBT_PATCH_PIXELS);
+				CU(cudaMemcpyAsync(dst, ctx->d_mc_nablas + off, EBT_PATCH_PIXELS * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+				CU(cudaMemsetAsync(ctx->d_mc_nablas + off, 0, EBT_PATCH_PIXELS * sizeof(int), ctx->stream));
+				dst += EBT_PATCH_PIXELS * sizeof(int);
+				CU(cudaMemcpyAsync(dst, ctx->d_pred_nablas + off, EBT_PATCH_PIXELS * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+				CU(cudaMemsetAsync(ctx->d_pred_nablas + off, 0, EBT_PATCH_PIXELS * sizeof(double), ctx->stream));
+				dst += EBT_PATCH_PIXELS * sizeof(double);
+			}
+			if (cmap)
+			{
+				const size_t coff = static_cast<size_t>(p.store_slot) * 121;
+				CU(cudaMemcpyAsync(dst, ctx->d_cost_maps + coff, 121 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+				CU(cudaMemsetAsync(ctx->d_cost_maps + coff, 0, 121 * sizeof(double), ctx->stream));
+				dst += 121 * sizeof(double);
+			}
+		}
+		CU(cudaStreamSynchronize(ctx->stream));
+		const unsigned char* src = ctx->arch_stage;
+		size_t k = 0;
+		for (size_t i = 0; i < ctx->h.size(); ++i)
+		{
+			const DevPatch& p = ctx->h[i];
+			if (!p.lost)
+			{
+				if (k != i) ctx->h[k] = ctx->h[i];
+				++k;
+				continue;
+			}
+			const int* nab = reinterpret_cast<const int*>(src);
+			ctx->arch_nabla.emplace_back(nab, nab + EBT_PATCH_PIXELS);
+			src += EBT_PATCH_PIXELS * sizeof(int);
+			if (prod)
+			{
+				const int* mc = reinterpret_cast<const int*>(src);
+				ctx->arch_mc.emplace_back(mc, mc + EBT_PATCH_PIXELS);
+				src += EBT_PATCH_PIXELS * sizeof(int);
 				std::vector<double> pr(EBT_PATCH_PIXELS);
-				CU(cudaMemcpy(mc.data(), ctx->d_mc_nablas + off, EBT_PATCH_PIXELS * sizeof(int), cudaMemcpyDeviceToHost));
-				CU(cudaMemcpy(pr.data(), ctx->d_pred_nablas + off, EBT_PATCH_PIXELS * sizeof(double), cudaMemcpyDeviceToHost));
-				CU(cudaMemset(ctx->d_mc_nablas + off, 0, EBT_PATCH_PIXELS * sizeof(int)));
-				CU(cudaMemset(ctx->d_pred_nablas + off, 0, EBT_PATCH_PIXELS * sizeof(double)));
-				ctx->arch_mc.push_back(std::move(mc));
+				std::memcpy(pr.data(), src, EBT_PATCH_PIXELS * sizeof(double));  // staged behind ints: not 8-byte aligned
 				ctx->arch_pred.push_back(std::move(pr));
+				src += EBT_PATCH_PIXELS * sizeof(double);
 			}
 			else
 			{
 				ctx->arch_mc.emplace_back();
 				ctx->arch_pred.emplace_back();
 			}
-			if (ctx->dp.cost_maps)
+			if (cmap)
 			{
-				const size_t off = static_cast<size_t>(ctx->h[i].store_slot) * 121;
 				std::vector<double> cm(121);
-				CU(cudaMemcpy(cm.data(), ctx->d_cost_maps + off, 121 * sizeof(double), cudaMemcpyDeviceToHost));
-				CU(cudaMemset(ctx->d_cost_maps + off, 0, 121 * sizeof(double)));
+				std::memcpy(cm.data(), src, 121 * sizeof(double));
 				ctx->arch_cost.push_back(std::move(cm));
+				src += 121 * sizeof(double);
 			}
 			else
 				ctx->arch_cost.emplace_back();
-			ctx->arch.push_back(ctx->h[i]);
-			ctx->arch_nabla.push_back(std::move(nab));
-			ctx->free_slots.push_back(ctx->h[i].store_slot);
-			ctx->frames[ctx->h[i].frame_slot].users--;
-			moved = true;
+			ctx->arch.push_back(p);
+			ctx->free_slots.push_back(p.store_slot);
+			ctx->frames[static_cast<size_t>(p.frame_slot)].users--;
 		}
-		else
-		{
-			if (k != i) ctx->h[k] = ctx->h[i];
-			++k;
-		}
+		ctx->h.resize(k);
+		ctx->host_dirty = true;
 	}
-	ctx->h.resize(k);
-	if (moved) ctx->host_dirty = true;
 	// erase unused optimizers (feature_detector.cpp:525-535)
 	for (auto& f : ctx->frames)
 		if (f.alive && f.users == 0) f.alive = false;
 	return EBT_OK;
 }
 
-static int runStream(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t* n_opt)
+// ---- one push = prefilter + stream kernel over one piece of the batch ---------
+// Mask scratch of a context for a piece of n events.
+static int ensureMask(ebt_ctx* ctx, int64_t n, int* wpr_out)
 {
-	if (n_opt) *n_opt = 0;
-	const int P = static_cast<int>(ctx->h.size());
-	if (n <= 0 || P == 0)
-	{
-		ctx->event_index += n > 0 ? n : 0;
-		return EBT_OK;
-	}
-	{
-		const int rc = uploadPatches(ctx);
-		if (rc != EBT_OK) return rc;
-	}
-	// scratch for the prefilter mask
 	const int wpr = ebt_mask_words_per_row(n);
-	const size_t need_words = static_cast<size_t>(P) * static_cast<size_t>(wpr);
+	const size_t need_words = ctx->h.size() * static_cast<size_t>(wpr);
 	if (need_words > ctx->mask_cap_words)
 	{
+		CU(cudaStreamSynchronize(ctx->stream));
 		cudaFree(ctx->d_mask);
 		ctx->d_mask = nullptr;
 		ctx->mask_cap_words = 0;
@@ -1086,53 +1182,52 @@ static int runStream(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t
 		CU(cudaMalloc(&ctx->d_mask, cap * sizeof(unsigned)));
 		ctx->mask_cap_words = cap;
 	}
-	// CTA order: features with the most optimisations in the previous push first
-	// (longest-processing-time-first keeps the kernel's tail short)
-	// Load estimate = optimisations in the previous push; a patch that has its flow
-	// but has never been optimised (it was created at the previous image, so its
-	// previous push only collected events) is expected to carry the mean load —
-	// rating it 0 would start a full-weight CTA in the last wave.
+	*wpr_out = wpr;
+	return EBT_OK;
+}
+
+// Expected optimisations per patch in the next push (work order: longest-
+// processing-time-first keeps the kernel's tail short) = the previous push's
+// count; a patch that has its flow but has never been optimised (created at the
+// previous image, so its previous push only collected events) is expected to
+// carry the mean load — rating it 0 would start a full-weight chain last.
+static void estimateLoad(ebt_ctx* ctx)
+{
+	const int P = static_cast<int>(ctx->h.size());
+	long long sum = 0, cnt = 0;
+	for (int i = 0; i < P; ++i)
 	{
-		long long sum = 0, cnt = 0;
-		for (int i = 0; i < P; ++i)
+		const DevPatch& p = ctx->h[static_cast<size_t>(i)];
+		if (!p.lost && p.init && p.n_costs > 0)
 		{
-			const DevPatch& p = ctx->h[static_cast<size_t>(i)];
-			if (!p.lost && p.init && p.n_costs > 0)
-			{
-				sum += p.last_n_opt;
-				++cnt;
-			}
-		}
-		const int mean = cnt ? static_cast<int>((sum + cnt - 1) / cnt) : 1;
-		ctx->load_est.resize(static_cast<size_t>(P));
-		for (int i = 0; i < P; ++i)
-		{
-			const DevPatch& p = ctx->h[static_cast<size_t>(i)];
-			ctx->load_est[static_cast<size_t>(i)] =
-				p.lost ? -1 : (!p.init ? 0 : (p.n_costs == 0 ? mean : p.last_n_opt));
+			sum += p.last_n_opt;
+			++cnt;
 		}
 	}
-	for (int i = 0; i < P; ++i) ctx->h_order[i] = i;
-	std::stable_sort(ctx->h_order, ctx->h_order + P,
-					 [&](int a, int b) { return ctx->load_est[static_cast<size_t>(a)] > ctx->load_est[static_cast<size_t>(b)]; });
-	CU(cudaMemcpyAsync(ctx->d_order, ctx->h_order, static_cast<size_t>(P) * sizeof(int), cudaMemcpyHostToDevice,
-					   ctx->stream));
-	CU(cudaMemsetAsync(ctx->d_nrec, 0, sizeof(unsigned long long), ctx->stream));
-	tic(ctx);
-	CU(ebt_launch_track_batch(ctx->d_patches, P, ctx->d_order, ctx->d_rings, ctx->d_nablas, d_events, n,
-							  ctx->event_index, ctx->d_mask, wpr, ctx->prefilter_margin, frameTable(ctx),
-							  ctx->dp, ctx->d_records, ctx->d_nrec,
-							  static_cast<unsigned long long>(ctx->prm.record_capacity), ctx->stream, ctx->d_queue, ctx->stream_kernel));
-	toc(ctx, K_TRACK);
-	CU(cudaMemcpyAsync(ctx->nrec_stage, ctx->d_nrec, sizeof(unsigned long long), cudaMemcpyDeviceToHost,
-					   ctx->stream));
-	CU(cudaMemcpyAsync(ctx->h_stage, ctx->d_patches, ctx->h.size() * sizeof(DevPatch),
-					   cudaMemcpyDeviceToHost, ctx->stream));
-	CU(cudaStreamSynchronize(ctx->stream));
+	const int mean = cnt ? static_cast<int>((sum + cnt - 1) / cnt) : 1;
+	ctx->load_est.resize(static_cast<size_t>(P));
+	for (int i = 0; i < P; ++i)
+	{
+		const DevPatch& p = ctx->h[static_cast<size_t>(i)];
+		ctx->load_est[static_cast<size_t>(i)] = p.lost ? -1 : (!p.init ? 0 : (p.n_costs == 0 ? mean : p.last_n_opt));
+	}
+}
+
+// After the kernel: patch state and record count back (one sync), then the
+// records themselves (second sync).  `on` = the stream the kernel ran on.
+static int collectPush(ebt_ctx* ctx, int64_t n, cudaStream_t on, int64_t* n_opt, bool synced_state)
+{
+	if (!synced_state)
+	{
+		CU(cudaMemcpyAsync(ctx->nrec_stage, ctx->d_nrec, sizeof(unsigned long long), cudaMemcpyDeviceToHost, on));
+		CU(cudaMemcpyAsync(ctx->h_stage, ctx->d_patches, ctx->h.size() * sizeof(DevPatch), cudaMemcpyDeviceToHost, on));
+		CU(cudaStreamSynchronize(on));
+	}
 	std::memcpy(ctx->h.data(), ctx->h_stage, ctx->h.size() * sizeof(DevPatch));
 	const unsigned long long nrec = *ctx->nrec_stage;
 	ctx->event_index += n;
-	if (n_opt) *n_opt = static_cast<int64_t>(nrec);
+	if (n_opt) *n_opt += static_cast<int64_t>(nrec);
+	ctx->opt_per_event = std::max(static_cast<double>(nrec) / static_cast<double>(std::max<int64_t>(n, 1)), 1e-3);
 	const unsigned long long got =
 		std::min<unsigned long long>(nrec, static_cast<unsigned long long>(ctx->prm.record_capacity));
 	if (got > 0)
@@ -1146,9 +1241,20 @@ static int runStream(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t
 			CU(cudaHostAlloc(&ctx->rec_stage, cap * sizeof(ebt_opt_record), cudaHostAllocDefault));
 			ctx->rec_stage_cap = cap;
 		}
-		CU(cudaMemcpyAsync(ctx->rec_stage, ctx->d_records, got * sizeof(ebt_opt_record), cudaMemcpyDeviceToHost,
-						   ctx->stream));
-		CU(cudaStreamSynchronize(ctx->stream));
+		CU(cudaMemcpyAsync(ctx->rec_stage, ctx->d_records, got * sizeof(ebt_opt_record), cudaMemcpyDeviceToHost, on));
+	}
+	ctx->pending_records = got;
+	ctx->pending_overflow = nrec > got;
+	return EBT_OK;
+}
+
+// The records of collectPush have arrived (the caller synchronised `on`).
+static int appendRecords(ebt_ctx* ctx)
+{
+	const size_t got = ctx->pending_records;
+	ctx->pending_records = 0;
+	if (got > 0)
+	{
 		// A feature's records sit in the buffer in the order it produced them,
 		// which is all the per-track histories need (built lazily, materialise());
 		// the global reference order is restored lazily too (sortRecords).
@@ -1158,29 +1264,291 @@ static int runStream(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t
 		ctx->record_batches.push_back(ctx->records.size());
 		ctx->journal.push_back({1, first, ctx->records.size()});
 	}
-	if (nrec > got)
+	if (ctx->pending_overflow)
+	{
+		ctx->pending_overflow = false;
 		return fail(ctx, EBT_E_CAPACITY,
-					"ebt_push_events: record_capacity exceeded; tracks are valid, records/trajectories of this push are truncated");
+					"ebt_push_events: record_capacity exceeded; tracks are valid, records/trajectories of this push are "
+					"truncated (raise ebt_params::record_capacity)");
+	}
 	return EBT_OK;
 }
 
-// A push is cut into pieces small enough for the prefilter scratch (256 MiB);
-// the stream kernel is sequential in the events, so the cut changes nothing.
+// One piece on the one-CTA-per-feature kernel (any feature count, products and cost map allowed).
+static int runStream(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t* n_opt)
+{
+	const int P = static_cast<int>(ctx->h.size());
+	{
+		const int rc = uploadPatches(ctx);
+		if (rc != EBT_OK) return rc;
+		const int rcf = syncFrameTable(ctx);
+		if (rcf != EBT_OK) return rcf;
+	}
+	int wpr = 0;
+	{
+		const int rc = ensureMask(ctx, n, &wpr);
+		if (rc != EBT_OK) return rc;
+	}
+	estimateLoad(ctx);
+	for (int i = 0; i < P; ++i) ctx->h_order[i] = i;
+	std::stable_sort(ctx->h_order, ctx->h_order + P,
+					 [&](int a, int b) { return ctx->load_est[static_cast<size_t>(a)] > ctx->load_est[static_cast<size_t>(b)]; });
+	CU(cudaMemcpyAsync(ctx->d_order, ctx->h_order, static_cast<size_t>(P) * sizeof(int), cudaMemcpyHostToDevice,
+					   ctx->stream));
+	CU(cudaMemsetAsync(ctx->d_nrec, 0, sizeof(unsigned long long), ctx->stream));
+	tic(ctx);
+	CU(ebt_launch_track_batch(ctx->d_patches, P, ctx->d_order, ctx->d_rings, ctx->d_nablas, d_events, n,
+							  ctx->event_index, ctx->d_mask, wpr, ctx->prefilter_margin, frameTable(ctx),
+							  ctx->dp, ctx->d_records, ctx->d_nrec,
+							  static_cast<unsigned long long>(ctx->prm.record_capacity), ctx->stream));
+	toc(ctx, K_TRACK);
+	{
+		const int rc = collectPush(ctx, n, ctx->stream, n_opt, false);
+		if (rc != EBT_OK) return rc;
+	}
+	CU(cudaStreamSynchronize(ctx->stream));
+	return appendRecords(ctx);
+}
+
+// One piece of S streams on the shared-pixel-warp kernel: one prefilter launch and
+// one stream-kernel launch for all of them, on ctxs[0]'s CUDA stream.
+static int runMulti(ebt_ctx* const* ctxs, int S, const ebt_event* const* d_events, const int64_t* n, int64_t* n_opt)
+{
+	ebt_ctx* ctx = ctxs[0];  // owner of the launch scratch and the CUDA stream used
+	cudaStream_t on = ctx->stream;
+	size_t n_work = 0;
+	for (int i = 0; i < S; ++i) n_work += ctxs[i]->h.size();
+	if (static_cast<size_t>(S) > ctx->descs_cap)
+	{
+		CU(cudaStreamSynchronize(on));
+		cudaFree(ctx->d_descs);
+		cudaFreeHost(ctx->h_descs);
+		ctx->d_descs = nullptr;
+		ctx->h_descs = nullptr;
+		ctx->descs_cap = 0;
+		const size_t cap = static_cast<size_t>(S) + 8;
+		CU(cudaMalloc(&ctx->d_descs, cap * sizeof(StreamDesc)));
+		CU(cudaHostAlloc(&ctx->h_descs, cap * sizeof(StreamDesc), cudaHostAllocDefault));
+		ctx->descs_cap = cap;
+	}
+	if (n_work > ctx->work_cap)
+	{
+		CU(cudaStreamSynchronize(on));
+		cudaFree(ctx->d_work);
+		cudaFreeHost(ctx->h_work);
+		ctx->d_work = nullptr;
+		ctx->h_work = nullptr;
+		ctx->work_cap = 0;
+		const size_t cap = n_work + n_work / 4 + 64;
+		CU(cudaMalloc(&ctx->d_work, cap * sizeof(WorkItem)));
+		CU(cudaHostAlloc(&ctx->h_work, cap * sizeof(WorkItem), cudaHostAllocDefault));
+		ctx->work_cap = cap;
+	}
+	int64_t max_events = 0;
+	int max_patches = 0;
+	size_t w = 0;
+	ctx->work_load.clear();
+	for (int i = 0; i < S; ++i)
+	{
+		ebt_ctx* c = ctxs[i];
+		// work of this context still in flight on its own CUDA stream comes first
+		if (c != ctx)
+		{
+			if (!c->join_event) CU(cudaEventCreateWithFlags(&c->join_event, cudaEventDisableTiming));
+			CU(cudaEventRecord(c->join_event, c->stream));
+			CU(cudaStreamWaitEvent(on, c->join_event, 0));
+		}
+		cudaStream_t own = c->stream;
+		c->stream = on;
+		int rc = uploadPatches(c);
+		if (rc == EBT_OK) rc = syncFrameTable(c);
+		int wpr = 0;
+		if (rc == EBT_OK) rc = ensureMask(c, n[i], &wpr);
+		c->stream = own;
+		if (rc != EBT_OK)
+		{
+			if (c != ctx) ctx->err = c->err;
+			return rc;
+		}
+		CU(cudaMemsetAsync(c->d_nrec, 0, sizeof(unsigned long long), on));
+		StreamDesc& D = ctx->h_descs[i];
+		D.patches = c->d_patches;
+		D.rings = c->d_rings;
+		D.nablas = c->d_nablas;
+		D.events = d_events[i];
+		D.n_events = n[i];
+		D.event_base = c->event_index;
+		D.mask = c->d_mask;
+		D.grids = c->d_frame_ptrs;
+		D.records = c->d_records;
+		D.n_records = c->d_nrec;
+		D.record_cap = static_cast<unsigned long long>(c->prm.record_capacity);
+		D.margin = c->prefilter_margin;
+		D.n_patches = static_cast<int>(c->h.size());
+		D.words_per_row = wpr;
+		D.latest = c->latest;
+		D.pad_ = 0;
+		max_events = std::max(max_events, n[i]);
+		max_patches = std::max(max_patches, D.n_patches);
+		estimateLoad(c);
+		for (int f = 0; f < D.n_patches; ++f)
+		{
+			ctx->h_work[w++] = WorkItem{i, f};
+			ctx->work_load.push_back(c->load_est[static_cast<size_t>(f)]);
+		}
+	}
+	{
+		// heaviest first over all streams (stable: equal loads keep stream / list order)
+		std::vector<int>& idx = ctx->work_idx;
+		idx.resize(n_work);
+		for (size_t k = 0; k < n_work; ++k) idx[k] = static_cast<int>(k);
+		std::stable_sort(idx.begin(), idx.end(),
+						 [&](int a, int b) { return ctx->work_load[static_cast<size_t>(a)] > ctx->work_load[static_cast<size_t>(b)]; });
+		ctx->work_tmp.assign(ctx->h_work, ctx->h_work + n_work);
+		for (size_t k = 0; k < n_work; ++k) ctx->h_work[k] = ctx->work_tmp[static_cast<size_t>(idx[k])];
+	}
+	CU(cudaMemcpyAsync(ctx->d_descs, ctx->h_descs, static_cast<size_t>(S) * sizeof(StreamDesc), cudaMemcpyHostToDevice, on));
+	CU(cudaMemcpyAsync(ctx->d_work, ctx->h_work, n_work * sizeof(WorkItem), cudaMemcpyHostToDevice, on));
+	tic(ctx);
+	CU(ebt_launch_track_multi(ctx->d_descs, S, ctx->d_work, static_cast<int>(n_work), max_events, max_patches, ctx->dp,
+							  ctx->d_queue, on));
+	toc(ctx, K_TRACK);
+	for (int i = 0; i < S; ++i)
+	{
+		ebt_ctx* c = ctxs[i];
+		CU(cudaMemcpyAsync(c->nrec_stage, c->d_nrec, sizeof(unsigned long long), cudaMemcpyDeviceToHost, on));
+		CU(cudaMemcpyAsync(c->h_stage, c->d_patches, c->h.size() * sizeof(DevPatch), cudaMemcpyDeviceToHost, on));
+	}
+	CU(cudaStreamSynchronize(on));
+	for (int i = 0; i < S; ++i)
+	{
+		const int rc = collectPush(ctxs[i], n[i], on, n_opt ? n_opt + i : nullptr, true);
+		if (rc != EBT_OK)
+		{
+			if (ctxs[i] != ctx) ctx->err = ctxs[i]->err;
+			return rc;
+		}
+	}
+	CU(cudaStreamSynchronize(on));
+	int result = EBT_OK;
+	for (int i = 0; i < S; ++i)
+	{
+		const int rc = appendRecords(ctxs[i]);
+		if (rc != EBT_OK)
+		{
+			if (ctxs[i] != ctx) ctx->err = ctxs[i]->err;
+			result = rc;
+		}
+	}
+	return result;
+}
+
+// Which kernel a push of these contexts takes: the shared-pixel-warp kernel needs the
+// getter-only products and the cost map off and enough features to fill its persistent
+// CTAs (more than two per SM); ebt_set_stream_kernel(ctx, 0) forces one CTA per feature.
+static bool multiEligible(ebt_ctx* const* ctxs, int S)
+{
+	size_t feats = 0;
+	for (int i = 0; i < S; ++i)
+	{
+		const ebt_ctx* c = ctxs[i];
+		if (c->stream_kernel == 0 || c->dp.products || c->dp.cost_maps) return false;
+		feats += c->h.size();
+	}
+	return S > 1 || ctxs[0]->stream_kernel == 2 || feats > 2 * static_cast<size_t>(ctxs[0]->sm_count);
+}
+
+// A push is cut into pieces small enough for the prefilter scratch (256 MiB per
+// context) and for the record buffer (expected optimisations per event of the
+// previous piece, with a factor 4 in hand); the stream kernel is sequential in the
+// events, so the cut changes nothing.
+static int64_t pieceEvents(const ebt_ctx* ctx)
+{
+	const int64_t rows = std::max<int64_t>(1, static_cast<int64_t>(ctx->h.size()));
+	const int64_t by_mask = std::max<int64_t>(1 << 16, ((int64_t(1) << 26) / rows) * 32);
+	const double by_records = static_cast<double>(ctx->prm.record_capacity) / (4.0 * ctx->opt_per_event);
+	return std::max<int64_t>(4096, std::min<int64_t>(by_mask, static_cast<int64_t>(std::min(by_records, 4e18))));
+}
+
+static int runPiecesMulti(ebt_ctx* const* ctxs, int S, const ebt_event* const* d_events, const int64_t* n, int64_t* n_opt)
+{
+	std::vector<int64_t> done(static_cast<size_t>(S), 0), m(static_cast<size_t>(S), 0), k(static_cast<size_t>(S), 0);
+	std::vector<ebt_ctx*> act;
+	std::vector<const ebt_event*> ev;
+	std::vector<int64_t> cnt;
+	std::vector<int> who;
+	if (n_opt)
+		for (int i = 0; i < S; ++i) n_opt[i] = 0;
+	for (;;)
+	{
+		act.clear();
+		ev.clear();
+		cnt.clear();
+		who.clear();
+		for (int i = 0; i < S; ++i)
+		{
+			ebt_ctx* c = ctxs[i];
+			const int64_t left = n[i] - done[static_cast<size_t>(i)];
+			if (left <= 0) continue;
+			if (c->h.empty())
+			{
+				// no patches: the events only advance the stream position
+				c->event_index += left;
+				done[static_cast<size_t>(i)] = n[i];
+				continue;
+			}
+			act.push_back(c);
+			ev.push_back(d_events[i] + done[static_cast<size_t>(i)]);
+			cnt.push_back(std::min(left, pieceEvents(c)));
+			who.push_back(i);
+		}
+		if (act.empty()) return EBT_OK;
+		const int A = static_cast<int>(act.size());
+		std::vector<int64_t> got(static_cast<size_t>(A), 0);
+		int rc;
+		if (multiEligible(act.data(), A))
+			rc = runMulti(act.data(), A, ev.data(), cnt.data(), got.data());
+		else
+		{
+			rc = EBT_OK;
+			for (int a = 0; a < A && rc == EBT_OK; ++a) rc = runStream(act[static_cast<size_t>(a)], ev[static_cast<size_t>(a)], cnt[static_cast<size_t>(a)], &got[static_cast<size_t>(a)]);
+		}
+		for (int a = 0; a < A; ++a)
+		{
+			done[static_cast<size_t>(who[static_cast<size_t>(a)])] += cnt[static_cast<size_t>(a)];
+			if (n_opt) n_opt[who[static_cast<size_t>(a)]] += got[static_cast<size_t>(a)];
+		}
+		if (rc != EBT_OK)
+		{
+			if (act[0] != ctxs[0]) ctxs[0]->err = act[0]->err;
+			return rc;
+		}
+	}
+}
+
 static int runPieces(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t* n_opt)
 {
 	if (n_opt) *n_opt = 0;
-	const int64_t rows = std::max<int64_t>(1, static_cast<int64_t>(ctx->h.size()));
-	const int64_t piece = std::max<int64_t>(1 << 16, ((int64_t(1) << 26) / rows) * 32);
-	int64_t done = 0;
-	do
+	if (n <= 0) return EBT_OK;
+	return runPiecesMulti(&ctx, 1, &d_events, &n, n_opt);
+}
+
+// Host-buffer upload of one context's batch into its own device buffer, on its own CUDA stream.
+static int uploadEvents(ebt_ctx* ctx, const ebt_event* events, int64_t n)
+{
+	if (n <= 0) return EBT_OK;
+	if (static_cast<size_t>(n) > ctx->d_events_cap)
 	{
-		const int64_t m = std::min(piece, n - done);
-		int64_t k = 0;
-		const int rc = runStream(ctx, d_events + done, m, &k);
-		if (n_opt) *n_opt += k;
-		if (rc != EBT_OK) return rc;
-		done += m;
-	} while (done < n);
+		CU(cudaStreamSynchronize(ctx->stream));
+		cudaFree(ctx->d_events);
+		ctx->d_events = nullptr;
+		ctx->d_events_cap = 0;
+		const size_t cap = static_cast<size_t>(n) + static_cast<size_t>(n) / 4 + 1024;
+		CU(cudaMalloc(&ctx->d_events, cap * sizeof(ebt_event)));
+		ctx->d_events_cap = cap;
+	}
+	CU(cudaMemcpyAsync(ctx->d_events, events, static_cast<size_t>(n) * sizeof(ebt_event), cudaMemcpyHostToDevice,
+					   ctx->stream));
 	return EBT_OK;
 }
 
@@ -1189,21 +1557,49 @@ int ebt_push_events(ebt_ctx* ctx, const ebt_event* events, int64_t n, int64_t* n
 {
 	if (!ctx || n < 0 || (n > 0 && !events)) return fail(ctx, EBT_E_INVALID, "ebt_push_events: bad argument");
 	CU(cudaSetDevice(ctx->device));
-	if (n > 0)
 	{
-		if (static_cast<size_t>(n) > ctx->d_events_cap)
-		{
-			cudaFree(ctx->d_events);
-			ctx->d_events = nullptr;
-			ctx->d_events_cap = 0;
-			const size_t cap = static_cast<size_t>(n) + static_cast<size_t>(n) / 4 + 1024;
-			CU(cudaMalloc(&ctx->d_events, cap * sizeof(ebt_event)));
-			ctx->d_events_cap = cap;
-		}
-		CU(cudaMemcpyAsync(ctx->d_events, events, static_cast<size_t>(n) * sizeof(ebt_event),
-						   cudaMemcpyHostToDevice, ctx->stream));
+		const int rc = uploadEvents(ctx, events, n);
+		if (rc != EBT_OK) return rc;
 	}
 	return runPieces(ctx, ctx->d_events, n, n_optimizations);
+}
+
+int ebt_push_events_multi(ebt_ctx* const* ctxs, int n_streams, const ebt_event* const* events, const int64_t* n_events,
+						  int device_resident, int64_t* n_optimizations)
+{
+	ebt_ctx* ctx = (ctxs && n_streams > 0) ? ctxs[0] : nullptr;
+	if (!ctx || !events || !n_events) return fail(ctx, EBT_E_INVALID, "ebt_push_events_multi: bad argument");
+	for (int i = 0; i < n_streams; ++i)
+	{
+		if (!ctxs[i] || n_events[i] < 0 || (n_events[i] > 0 && !events[i]))
+			return fail(ctx, EBT_E_INVALID, "ebt_push_events_multi: bad argument for stream " + std::to_string(i));
+		if (ctxs[i]->device != ctx->device)
+			return fail(ctx, EBT_E_INVALID, "ebt_push_events_multi: all contexts must live on the same device");
+		// the solver constants travel as one kernel parameter for the whole launch
+		if (std::memcmp(&ctxs[i]->dp, &ctx->dp, offsetof(DevParams, products)) != 0)
+			return fail(ctx, EBT_E_INVALID, "ebt_push_events_multi: the contexts' parameters (image size, solver "
+											"constants) must be equal; stream " + std::to_string(i) + " differs");
+		for (int j = 0; j < i; ++j)
+			if (ctxs[j] == ctxs[i]) return fail(ctx, EBT_E_INVALID, "ebt_push_events_multi: a context is listed twice");
+	}
+	CU(cudaSetDevice(ctx->device));
+	std::vector<const ebt_event*> dev(static_cast<size_t>(n_streams));
+	for (int i = 0; i < n_streams; ++i)
+	{
+		if (device_resident)
+			dev[static_cast<size_t>(i)] = events[i];
+		else
+		{
+			const int rc = uploadEvents(ctxs[i], events[i], n_events[i]);
+			if (rc != EBT_OK)
+			{
+				if (ctxs[i] != ctx) ctx->err = ctxs[i]->err;
+				return rc;
+			}
+			dev[static_cast<size_t>(i)] = ctxs[i]->d_events;
+		}
+	}
+	return runPiecesMulti(ctxs, n_streams, dev.data(), n_events, n_optimizations);
 }
 
 int ebt_push_events_device(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t* n_optimizations)
@@ -1433,9 +1829,7 @@ int ebt_frames_add(ebt_ctx* ctx, const uint8_t* gray)
 {
 	if (!ctx || !gray) return fail(ctx, EBT_E_INVALID, "ebt_frames_add: bad argument");
 	CU(cudaSetDevice(ctx->device));
-	int slot = -1;
-	for (int i = 0; i < EBT_MAX_FRAMES && slot < 0; ++i)
-		if (!ctx->frames[i].alive) slot = i;
+	int slot = allocFrameSlot(ctx);
 	if (slot < 0) return fail(ctx, EBT_E_CAPACITY, "ebt_frames_add: no free template frame slot");
 	const int rc = buildGrid(ctx, gray, slot);
 	if (rc != EBT_OK) return rc;
@@ -1447,7 +1841,7 @@ int ebt_frames_add(ebt_ctx* ctx, const uint8_t* gray)
 
 int ebt_frames_get(ebt_ctx* ctx, int slot, double* gx, double* gy)
 {
-	if (!ctx || slot < 0 || slot >= EBT_MAX_FRAMES || !ctx->frames[slot].grid || !gx || !gy)
+	if (!ctx || slot < 0 || slot >= static_cast<int>(ctx->frames.size()) || !ctx->frames[slot].grid || !gx || !gy)
 		return fail(ctx, EBT_E_INVALID, "ebt_frames_get: bad argument");
 	return copyGrid(ctx, slot, gx, gy);
 }
@@ -1476,6 +1870,10 @@ int ebt_optimize_batch_device(ebt_ctx* ctx, const ebt_problem* d_problems, int64
 		CU(cudaMemsetAsync(ctx->d_bcost, 0, need * sizeof(double), ctx->stream));
 		dp.cost_maps = ctx->d_bcost;
 		ctx->n_bcost = static_cast<size_t>(n_problems);
+	}
+	{
+		const int rcf = syncFrameTable(ctx);
+		if (rcf != EBT_OK) return rcf;
 	}
 	tic(ctx);
 	CU(ebt_launch_optimize_batch(d_problems, static_cast<int>(n_problems), d_events, frameTable(ctx),
@@ -1509,15 +1907,14 @@ int ebt_optimize_batch(ebt_ctx* ctx, const ebt_problem* problems, int64_t n_prob
 	{
 		const ebt_problem& p = problems[i];
 		if (p.n_events < 1 || p.event_offset < 0 || static_cast<int64_t>(p.event_offset) + p.n_events > n_events ||
-			p.frame_slot < 0 || p.frame_slot >= EBT_MAX_FRAMES || !ctx->frames[p.frame_slot].grid)
+			p.frame_slot < 0 || p.frame_slot >= static_cast<int>(ctx->frames.size()) || !ctx->frames[p.frame_slot].grid)
 			return fail(ctx, EBT_E_INVALID, "ebt_optimize_batch: problem " + std::to_string(i) + " is malformed");
 	}
 	CU(cudaSetDevice(ctx->device));
 	const size_t np = static_cast<size_t>(n_problems);
 	{
-		size_t capS = ctx->cap_problems;
 		CU(ensure(&ctx->d_problems, &ctx->cap_problems, np));
-		CU(ensure(&ctx->d_solutions, &capS, np));
+		CU(ensure(&ctx->d_solutions, &ctx->cap_solutions, np));
 		CU(ensure(&ctx->d_bevents, &ctx->cap_bevents, static_cast<size_t>(n_events)));
 		if (nabla) CU(ensure(&ctx->d_bnabla, &ctx->cap_bnabla, np * EBT_PATCH_PIXELS));
 	}

@@ -6,7 +6,9 @@
 
 #include "../../include/ebt_types.h"
 
-#define EBT_MAX_FRAMES 64   // live template frames (FeatureDetector::optimizers_)
+// live template frames (FeatureDetector::optimizers_) a context starts with room for; the
+// table grows on demand (the reference's map is unbounded)
+#define EBT_INIT_FRAMES 64
 #ifndef EBT_THREADS
 #define EBT_THREADS 128     // threads per feature CTA
 #endif
@@ -83,10 +85,40 @@ struct DevParams
 };
 
 // Gradient grids of the live template frames: interleaved (gx, gy) doubles,
-// row stride = width (Optimizer::setGrad, optimizer.cpp:15-30).
+// row stride = width (Optimizer::setGrad, optimizer.cpp:15-30).  `grid` is a
+// device array of grid pointers indexed by DevPatch::frame_slot / ebt_problem::
+// frame_slot; the host grows it as frames are added.
 struct FrameTable
 {
-	const double2* grid[EBT_MAX_FRAMES];
+	const double2* const* grid;
 	int latest;  // slot FeatureDetector::gradX_/gradY_ refer to
 	int pad;
+};
+
+// One stream of a multi-stream push (ebt_launch_track_multi): where its features,
+// windows, event batch, prefilter rows, template grids and records live.
+struct StreamDesc
+{
+	DevPatch* patches;
+	ebt_event* rings;
+	int* nablas;
+	const ebt_event* events;   // this push's batch, stream order
+	long long n_events;
+	long long event_base;      // stream index of events[0] (ebt_opt_record::event_index)
+	unsigned* mask;            // n_patches x words_per_row prefilter words
+	const double2* const* grids;  // FrameTable::grid
+	ebt_opt_record* records;
+	unsigned long long* n_records;
+	unsigned long long record_cap;
+	double margin;             // prefilter margin, pixels
+	int n_patches;
+	int words_per_row;
+	int latest;                // FrameTable::latest
+	int pad_;
+};
+
+// One unit of work of the multi-stream kernel: feature `feature` of stream `stream`.
+struct WorkItem
+{
+	int stream, feature;
 };

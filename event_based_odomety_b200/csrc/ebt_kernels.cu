@@ -59,6 +59,19 @@ __device__ unsigned long long g_phase_clocks[8];
 #define PHASE_ADD(k, a, b)
 #endif
 
+// Walk clocks (build with -DEBT_WALK_CLOCKS, diagnostic builds only; they reuse the
+// g_phase_clocks slots): summed over all features by the feature's first lane,
+// 0 cycles entry->exit, 1 inside Optimizer::optimize, 2 inside lm_solve, 3 mask-row
+// rebuilds, 4 rebuild count, 5 optimisations, 6 window-size update, 7 mask segments walked.
+#ifdef EBT_WALK_CLOCKS
+#define WALK_T(v) const long long v = clock64()
+#define WALK_ADD(cond, k, amount) \
+	if (cond) atomicAdd(&g_phase_clocks[k], (unsigned long long)(amount))
+#else
+#define WALK_T(v)
+#define WALK_ADD(cond, k, amount)
+#endif
+
 namespace
 {
 constexpr int kPixUnroll = EBT_PIX_UNROLL;
@@ -1269,7 +1282,10 @@ __device__ EBT_NOINLINE void optimize_feature(FeatShared& sh, double* costs, Fea
 				   (double)__double2float_rn(st.flow)};
 	if (threadIdx.x < 32)
 	{
+		WALK_T(wl0);
 		lm_solve(sh, P, x, S);  // its first post_request publishes sh.ctx
+		WALK_T(wl1);
+		WALK_ADD(threadIdx.x == 0, 2, wl1 - wl0);
 		if (threadIdx.x == 0)
 		{
 #pragma unroll
@@ -1564,15 +1580,12 @@ __device__ __forceinline__ int4 candidate_bounds(double rx, double ry, double ma
 	return b;
 }
 
-__global__ void __launch_bounds__(PF_THREADS)
-prefilter_kernel(const DevPatch* __restrict__ patches, int n_patches,
-				 const ebt_event* __restrict__ events, long long n_events, double margin,
-				 unsigned* __restrict__ mask, int words_per_row)
+__device__ __forceinline__ void prefilter_tile(const DevPatch* __restrict__ patches, int n_patches,
+											   const ebt_event* __restrict__ events, long long n_events, double margin,
+											   unsigned* __restrict__ mask, int words_per_row, unsigned tile, int f0,
+											   unsigned* xy, int4* bounds)
 {
-	__shared__ unsigned xy[PF_TILE];
-	__shared__ int4 bounds[PF_FEATS];
-	const long long tile0 = (long long)blockIdx.x * PF_TILE;
-	const int f0 = blockIdx.y * PF_FEATS;
+	const long long tile0 = (long long)tile * PF_TILE;
 	const unsigned* ev32 = reinterpret_cast<const unsigned*>(events);
 	for (int k = threadIdx.x; k < PF_TILE; k += PF_THREADS)
 	{
@@ -1602,8 +1615,32 @@ prefilter_kernel(const DevPatch* __restrict__ patches, int n_patches,
 			const unsigned bal = __ballot_sync(0xffffffffu, x >= b.x && x <= b.y && y >= b.z && y <= b.w);
 			if (lane == j) mine = bal;
 		}
-		mask[(size_t)(f0 + k) * words_per_row + (size_t)blockIdx.x * 32 + lane] = mine;
+		mask[(size_t)(f0 + k) * words_per_row + (size_t)tile * 32 + lane] = mine;
 	}
+}
+
+__global__ void __launch_bounds__(PF_THREADS)
+prefilter_kernel(const DevPatch* __restrict__ patches, int n_patches,
+				 const ebt_event* __restrict__ events, long long n_events, double margin,
+				 unsigned* __restrict__ mask, int words_per_row)
+{
+	__shared__ unsigned xy[PF_TILE];
+	__shared__ int4 bounds[PF_FEATS];
+	prefilter_tile(patches, n_patches, events, n_events, margin, mask, words_per_row, blockIdx.x,
+				   (int)blockIdx.y * PF_FEATS, xy, bounds);
+}
+
+// The same for the streams of one multi-stream push: grid z = stream, x and y sized
+// for the largest stream; CTAs beyond a stream's own extent leave at once.
+__global__ void __launch_bounds__(PF_THREADS)
+prefilter_multi_kernel(const StreamDesc* __restrict__ descs)
+{
+	__shared__ unsigned xy[PF_TILE];
+	__shared__ int4 bounds[PF_FEATS];
+	const StreamDesc& D = descs[blockIdx.z];
+	if ((long long)blockIdx.x * PF_TILE >= D.n_events || (int)blockIdx.y * PF_FEATS >= D.n_patches) return;
+	prefilter_tile(D.patches, D.n_patches, D.events, D.n_events, D.margin, D.mask, D.words_per_row, blockIdx.x,
+				   (int)blockIdx.y * PF_FEATS, xy, bounds);
 }
 
 // Rebuild one feature's mask row from event `from` on, for a candidate region
@@ -1697,6 +1734,7 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 	if (gp.lost) return;  // uniform over the CTA
 	unsigned long long t_enter;
 	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_enter));
+	WALK_T(wk_enter);
 	FeatState st;
 	load_state(st, gp);
 	const int track_id = gp.track_id;
@@ -1719,12 +1757,19 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 	// Returns true when the mask row was rebuilt (the caller re-expands).
 	auto optimise_at = [&](long long at) -> bool {
 		LmSummary S;
+		WALK_T(w0);
 		optimize_feature(sh, costs, st, ft, P, S,
 						 P.cost_maps ? P.cost_maps + (size_t)gp.store_slot * 121 : nullptr);
+		WALK_T(w1);
+		WALK_ADD(threadIdx.x == 0, 1, w1 - w0);
+		WALK_ADD(threadIdx.x == 0, 5, 1);
 		if (!S.filtered)
 			motion_compensated(sh, McArgs{st.rx, st.ry, st.cur_ts, st.n_traj, st.size, st.tail}, gp, P.products,
 							   P.mc_nablas);
+		WALK_T(w2);
 		update_num_of_events(sh, st, ft, P);
+		WALK_T(w3);
+		WALK_ADD(threadIdx.x == 0, 6, w3 - w2);
 		if (P.products)  // feature_detector.cpp:615
 			predicted_nabla(PredArgs{st.rx, st.ry, st.warp[0], st.warp[1], st.warp[2], st.warp[3], st.flow},
 							ft.grid[st.frame_slot], P.width, P.height,
@@ -1734,7 +1779,11 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 		start = at + 1;
 		if (!st.lost && (fabs(st.rx - srx) > margin || fabs(st.ry - sry) > margin))
 		{
+			WALK_T(w4);
 			rebuild_mask_row(row, events, n_events, start, st.rx, st.ry, margin);
+			WALK_T(w5);
+			WALK_ADD(threadIdx.x == 0, 3, w5 - w4);
+			WALK_ADD(threadIdx.x == 0, 4, 1);
 			srx = st.rx;
 			sry = st.ry;
 			return true;
@@ -1752,6 +1801,7 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 	while (!st.lost && seg < n_words)
 	{
 		// expand the segment's set bits into cand[], in stream order
+		WALK_ADD(threadIdx.x == 0, 7, 1);
 		const long long wi = seg + threadIdx.x;
 		unsigned word = wi < n_words ? row[wi] : 0u;
 		{
@@ -1868,6 +1918,8 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 	{
 		store_state(st, gp);
 		gp.last_n_opt = n_opt;  // load estimate for the next launch's CTA order
+		WALK_T(wk_exit);
+		WALK_ADD(true, 0, wk_exit - wk_enter);
 		unsigned long long t_exit;
 		unsigned sm;
 		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_exit));
@@ -2222,14 +2274,27 @@ optimize_batch_shared_kernel(const ebt_problem* __restrict__ problems, int n_pro
 
 
 // --------------------------------------------------------------------------
-// Stream kernel, shared pixel warps: the per-event loop of track_batch_kernel with
-// two features per CTA, one leader warp each, sharing the CTA's four pixel warps
-// (hand-off as in optimize_batch_shared_kernel).  Everything of a feature except
-// the pixel passes and the tile staging runs on its leader warp: candidate walk
-// (32 mask words = 1024 events per segment, chunks of 32 candidates), window ring,
-// integration, normalisation, window size, record.  Used when the getter-only
-// products and the cost map are off.
+// Stream kernel, shared pixel warps, many streams: FeatureDetector::updatePatches
+// (ft/src/feature_detector.cpp:585-619) for the event batches of S independent
+// streams in ONE launch.  A work item is one feature of one stream; persistent
+// CTAs of two leader warps + four pixel warps pull work items, heaviest first,
+// from a queue.  A leader warp owns one feature at a time and keeps only what is
+// serial on itself: the candidate walk over the feature's prefilter row and the
+// scalar trust-region chain.  Everything that is parallel over pixels or window
+// events is posted to the CTA's pixel warps as a job (hand-off by sequence
+// numbers, as in optimize_batch_shared_kernel):
+//   5  Patch::integrateEvents: the 625 pixels are dealt out to the pixel warps
+//      (pixel i belongs to warp i mod 4), every warp scans the whole window and
+//      accumulates the events that fall on its own pixels, then sums their squares
+//      — no ordering between the pixel warps is needed
+//   3  normalised patch m = nabla * inv + its squared sum, and the staged tile
+//   1/2 cost / cost + Jacobian pixel pass of the LM solve
+//   6  the 625 nearest-neighbour samples of FeatureDetector::updateNumOfEvents
+// While one leader walks, or runs its scalar step, the pixel warps serve the other.
+// Candidate walk: 128 mask words (4096 stream events) per segment, one 16-byte
+// load per lane, the next segment's words already in flight.
 // --------------------------------------------------------------------------
+#define MQ_SEG_WORDS 128
 struct __align__(16) StreamSlot
 {
 	static constexpr int kPixWarps = SB_PIXW;
@@ -2243,14 +2308,82 @@ struct __align__(16) StreamSlot
 	double tot[20];
 	double costs[EBT_COST_HISTORY];
 	EvalCtx ctx;
-	unsigned short cand[32 * 32];
+	unsigned short cand[MQ_SEG_WORDS * 32];
+	const double2* job_grid;  // job 6: the latest frame's grid
+	int job_i[4];             // integer job arguments (5: window tail, size; 6: x0, y0)
+	int redi[SB_PIXW];        // job 5: per-warp sum of squares of the integer patch
 	int req_kind;
 	unsigned req_seq, done_cnt, seq_local;
 	long long t_last;
 };
 
-// FeatureDetector::updateNumOfEvents on one warp (as update_num_of_events)
-__device__ void ss_update_num_of_events(FeatState& st, const FrameTable& ft, const DevParams& P)
+// Jobs 3, 5 and 6 of slot S on this pixel warp (ptid = index among the 128 pixel threads).
+__device__ __noinline__ void mq_serve(StreamSlot& S, int kind, int ptid)
+{
+	const int lane = ptid & 31, pw = ptid >> 5;
+	const EvalCtx& E = S.ctx;
+	if (kind == 5)
+	{
+		// Patch::integrateEvents (patch.cpp:65-84) on this warp's pixels
+		const double rx = S.req[0], ry = S.req[1];
+		const int tail = S.job_i[0], size = S.job_i[1];
+		for (int i = pw + SB_PIXW * lane; i < NPIX; i += SB_PIXW * 32) S.nabla[i] = 0;
+		__syncwarp();
+		for (int k = lane; k < size; k += 32)
+		{
+			const ebt_event e = S.ring[(tail + k) & RMASK];
+			if (in_rect(rx, ry, e.x, e.y))
+			{
+				const int idx = (int)(e.y - ry) * SIDE + (int)(e.x - rx);
+				if ((idx & (SB_PIXW - 1)) == pw) atomicAdd(&S.nabla[idx], (int)e.polarity);
+			}
+		}
+		__syncwarp();
+		int ss = 0;
+		for (int i = pw + SB_PIXW * lane; i < NPIX; i += SB_PIXW * 32)
+		{
+			const int v = S.nabla[i];
+			ss += v * v;
+		}
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+		if (lane == 0) S.redi[pw] = ss;
+		return;
+	}
+	if (kind == 3)
+	{
+		// Patch::getNormalizedIntegratedNabla (patch.cpp:156-159): Mat * (1/s)
+		const double inv = S.req[0];
+		double a = 0;
+		for (int i = ptid; i < NPIX; i += SB_PIXW * 32)
+		{
+			const double v = (double)S.nabla[i] * inv;
+			S.m[i] = v;
+			a += v * v;
+		}
+		a = warp_sum(a);
+		if (lane == 0) S.red[pw][0] = a;
+		if (E.staged)
+			for (int idx = ptid; idx < TS * TS; idx += SB_PIXW * 32)
+			{
+				const int i = idx / TS, j = idx - i * TS;
+				const int rr = min(max(E.r0 + i, 0), E.H - 1), cc = min(max(E.c0 + j, 0), E.W - 1);
+				S.tile[idx] = __ldg(E.grid + rr * E.W + cc);
+			}
+		return;
+	}
+	// kind 6: the L1 norm FeatureDetector::updateNumOfEvents takes (feature_detector.cpp:695-705)
+	const double c = S.req[0], s = S.req[1], tx = S.req[2], ty = S.req[3], a = S.req[4], b = S.req[5];
+	const int x0 = S.job_i[0], y0 = S.job_i[1];
+	const double2* grid = S.job_grid;
+	double acc = 0;
+	for (int i = ptid; i < NPIX; i += SB_PIXW * 32) acc += num_events_term(grid, E.W, E.H, c, s, tx, ty, a, b, x0, y0, i);
+	acc = warp_sum(acc);
+	if (lane == 0) S.red[pw][0] = acc;
+}
+
+// FeatureDetector::updateNumOfEvents on a leader warp, the pixel sum as job 6
+__device__ void mq_update_num_of_events(StreamSlot& S, FeatState& st, const double2* grid_latest, const DevParams& P)
 {
 	const int lane = threadIdx.x & 31;
 	const int W = P.width, H = P.height;
@@ -2265,58 +2398,51 @@ __device__ void ss_update_num_of_events(FeatState& st, const FrameTable& ft, con
 		st.num_of_events = min(max(P.init_num_events, P.min_num_events), P.max_num_events);
 		return;
 	}
-	const double2* grid = ft.grid[ft.latest];
-	const double c = st.warp[0], s = st.warp[1], tx = st.warp[2], ty = st.warp[3];
-	const int x0 = __double2int_rn(st.rx), y0 = __double2int_rn(st.ry);
 	const float flow = __double2float_rn(st.flow);
-	const double a = 0.6 * (double)__double2float_rn(cos((double)flow));
-	const double b = 0.6 * (double)__double2float_rn(sin((double)flow));
-	double acc = 0;
-	for (int i = lane; i < NPIX; i += 32) acc += num_events_term(grid, W, H, c, s, tx, ty, a, b, x0, y0, i);
-	acc = warp_sum(acc);
+	if (lane == 0)
+	{
+		S.req[0] = st.warp[0];
+		S.req[1] = st.warp[1];
+		S.req[2] = st.warp[2];
+		S.req[3] = st.warp[3];
+		// std::cos(float) rounds to float (feature_detector.cpp:702-704)
+		S.req[4] = 0.6 * (double)__double2float_rn(cos((double)flow));
+		S.req[5] = 0.6 * (double)__double2float_rn(sin((double)flow));
+		S.job_i[0] = __double2int_rn(st.rx);
+		S.job_i[1] = __double2int_rn(st.ry);
+		S.job_grid = grid_latest;
+		S.ctx.W = W;
+		S.ctx.H = H;
+		S.req_kind = 6;
+	}
+	sb_post(S);
+	wait_partials(S);
+	const double acc = red_total(S, 0);
 	const unsigned long long n = (unsigned long long)acc;
 	st.num_of_events = (int)min(max(n, (unsigned long long)P.min_num_events), (unsigned long long)P.max_num_events);
 }
 
 // One Optimizer::optimize on a leader warp (as optimize_feature, cost map excluded)
-__device__ void ss_optimize(StreamSlot& S, FeatState& st, const FrameTable& ft, const DevParams& P, LmSummary& L)
+__device__ void mq_optimize(StreamSlot& S, FeatState& st, const double2* grid, const DevParams& P, LmSummary& L)
 {
 	const int lane = threadIdx.x & 31;
 	L.filtered = 0;
-	for (int i = lane; i < NPIX; i += 32) S.nabla[i] = 0;
-	__syncwarp();
-	for (int k = lane; k < st.size; k += 32)
+	if (lane == 0)
 	{
-		const ebt_event e = S.ring[(st.tail + k) & RMASK];
-		if (in_rect(st.rx, st.ry, e.x, e.y))
-		{
-			const int px = (int)(e.x - st.rx), py = (int)(e.y - st.ry);
-			atomicAdd(&S.nabla[py * SIDE + px], (int)e.polarity);
-		}
+		S.req[0] = st.rx;
+		S.req[1] = st.ry;
+		S.job_i[0] = st.tail;
+		S.job_i[1] = st.size;
+		S.req_kind = 5;
 	}
+	sb_post(S);
+	// while the pixel warps integrate: timestamps and the tile origin
 	{
 		const long long front = S.ring[(st.tail + st.size - 1) & RMASK].t_us;
 		const long long back = S.ring[st.tail & RMASK].t_us;
 		st.cur_ts = to_i32((double)(front + back) * 0.5);
 		st.time_last_update = to_i32((double)back);
 	}
-	__syncwarp();
-	double a = 0;
-	for (int i = lane; i < NPIX; i += 32)
-	{
-		const double v = (double)S.nabla[i];
-		a += v * v;
-	}
-	a = warp_sum(a);
-	const double inv = 1.0 / sqrt(a);
-	double smm = 0;
-	for (int i = lane; i < NPIX; i += 32)
-	{
-		const double v = (double)S.nabla[i] * inv;
-		S.m[i] = v;
-		smm += v * v;
-	}
-	smm = warp_sum(smm);
 	int r0 = 0, c0 = 0, staged = 0;
 	{
 		const double c = st.warp[0], s = st.warp[1], tx = st.warp[2], ty = st.warp[3];
@@ -2343,10 +2469,15 @@ __device__ void ss_optimize(StreamSlot& S, FeatState& st, const FrameTable& ft, 
 			}
 		}
 	}
+	wait_partials(S);
+	// the sum of squares of an integer patch is an exact integer in any order
+	const long long ssq = ((long long)S.redi[0] + S.redi[1]) + ((long long)S.redi[2] + S.redi[3]);
+	static_assert(SB_PIXW == 4, "job 5 deals the pixels out to four warps");
+	const double inv = 1.0 / sqrt((double)ssq);
 	if (lane == 0)
 	{
 		EvalCtx& E = S.ctx;
-		E.grid = ft.grid[st.frame_slot];
+		E.grid = grid;
 		E.W = P.width;
 		E.H = P.height;
 		E.r0 = r0;
@@ -2354,19 +2485,22 @@ __device__ void ss_optimize(StreamSlot& S, FeatState& st, const FrameTable& ft, 
 		E.staged = staged;
 		E.tlx = st.rx;
 		E.tly = st.ry;
-		E.smm = smm;
 		E.huber_a = P.huber_a;
+		S.req[0] = inv;
 		S.req_kind = 3;
 	}
-	if (staged)
+	sb_post(S);
+	wait_partials(S);
 	{
-		sb_post(S);
-		wait_partials(S);
-	}
-	else
+		const double smm = red_total(S, 0);
+		if (lane == 0) S.ctx.smm = smm;
 		__syncwarp();
+	}
 	double x[5] = {st.warp[0], st.warp[1], st.warp[2], st.warp[3], (double)__double2float_rn(st.flow)};
+	WALK_T(wl0);
 	lm_solve(S, P, x, L);
+	WALK_T(wl1);
+	WALK_ADD(lane == 0, 2, wl1 - wl0);
 	// addFinalCost + median-of-5 cost filter (optimizer.cpp:127-157)
 	if (lane == 0) S.costs[st.n_costs & (EBT_COST_HISTORY - 1)] = L.final_cost;
 	st.n_costs++;
@@ -2406,13 +2540,17 @@ __device__ void ss_optimize(StreamSlot& S, FeatState& st, const FrameTable& ft, 
 	st.counter = 0;
 }
 
+// this lane's four words of the 128-word mask segment that starts at word `seg` (a multiple of 4)
+__device__ __forceinline__ uint4 mq_load_segment(const unsigned* row, long long seg, int words_per_row, int lane)
+{
+	const long long w = seg + 4 * lane;
+	if (w < words_per_row) return __ldcg(reinterpret_cast<const uint4*>(row + w));  // rows are whole 128-byte tiles
+	return make_uint4(0, 0, 0, 0);
+}
+
 __global__ void __launch_bounds__(SB_THREADS, SB_CTAS)
-track_shared_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __restrict__ order,
-					ebt_event* __restrict__ rings, int* __restrict__ nablas,
-					const ebt_event* __restrict__ events, long long n_events, long long event_base,
-					unsigned* mask, int words_per_row, double margin, FrameTable ft, DevParams P,
-					ebt_opt_record* __restrict__ records, unsigned long long* n_records,
-					unsigned long long record_cap, int* __restrict__ queue)
+track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restrict__ work, int n_work, DevParams P,
+				   int* __restrict__ queue)
 {
 	extern __shared__ __align__(16) unsigned char ss_raw[];
 	StreamSlot* slots = reinterpret_cast<StreamSlot*>(ss_raw);
@@ -2450,7 +2588,10 @@ track_shared_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __
 					++exited;
 					continue;
 				}
-				sb_serve(S, kind, ptid);
+				if (kind <= 2)
+					sb_serve(S, kind, ptid);
+				else
+					mq_serve(S, kind, ptid);
 				__threadfence_block();
 				__syncwarp();
 				if (lane == 0) atomicAdd(&S.done_cnt, 1u);
@@ -2459,48 +2600,60 @@ track_shared_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __
 		}
 		return;
 	}
-	// ---- leader warp `warp`.  First feature: CTA c pairs the c-th heaviest with the c-th
-	// lightest (order[] is heaviest first), so two long chains do not share pixel warps;
-	// afterwards the leaders pull the features in between from a queue, heaviest first.
+	// ---- leader warp `warp`.  First work item: CTA c pairs the c-th heaviest with the c-th
+	// lightest (work[] is heaviest first), so two long chains do not share pixel warps;
+	// afterwards the leaders pull the items in between from the queue, heaviest first.
 	StreamSlot& S = slots[warp];
-	static_assert(SB_LEADERS == 2, "feature pairing below is written for two leaders per CTA");
+	static_assert(SB_LEADERS == 2, "work pairing below is written for two leaders per CTA");
 	const int n_ctas = (int)gridDim.x;
-	int oi = warp == 0 ? (int)blockIdx.x : n_patches - 1 - (int)blockIdx.x;
-	if (warp == 1 && oi < n_ctas) oi = n_patches;  // that one belongs to a first leader
-	for (; oi < n_patches;
-		 oi = __shfl_sync(0xffffffffu, lane == 0 ? atomicAdd(queue, 1) : 0, 0), oi = oi < n_patches - n_ctas ? oi : n_patches)
+	int oi = warp == 0 ? (int)blockIdx.x : n_work - 1 - (int)blockIdx.x;
+	if (warp == 1 && oi < n_ctas) oi = n_work;  // that one belongs to a first leader
+	for (; oi < n_work;
+		 oi = __shfl_sync(0xffffffffu, lane == 0 ? atomicAdd(queue, 1) : 0, 0), oi = oi < n_work - n_ctas ? oi : n_work)
 	{
-		if (patches[order[oi]].lost) continue;
-		const int f = order[oi];
-		DevPatch& gp = patches[f];
+		const WorkItem item = work[oi];
+		const StreamDesc& D = descs[item.stream];
+		DevPatch& gp = D.patches[item.feature];
+		if (gp.lost) continue;
 		unsigned long long t_enter;
 		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_enter));
+		WALK_T(wk_enter);
 		FeatState st;
 		load_state(st, gp);
 		const int track_id = gp.track_id;
-		ebt_event* gring = rings + (size_t)gp.store_slot * EBT_RING;
-		int* gnabla = nablas + (size_t)gp.store_slot * NPIX;
+		ebt_event* gring = D.rings + (size_t)gp.store_slot * EBT_RING;
+		int* gnabla = D.nablas + (size_t)gp.store_slot * NPIX;
 		for (int k = lane; k < st.size; k += 32) S.ring[k] = gring[(st.tail + k) & RMASK];
 		if (lane < EBT_COST_HISTORY) S.costs[lane] = gp.costs[lane];
 		st.tail = 0;
 		__syncwarp();
+		const ebt_event* events = D.events;
+		const long long n_events = D.n_events;
+		const int wpr = D.words_per_row;
+		const double margin = D.margin;
 		const uint4* ev4 = reinterpret_cast<const uint4*>(events);
-		unsigned* row = mask + (size_t)f * words_per_row;
+		unsigned* row = D.mask + (size_t)item.feature * wpr;
 		double srx = st.rx, sry = st.ry;
 		long long start = 0;
 		int n_opt = 0;
 		bool pre = st.init && n_events > 0 && window_need(st, P) <= 0;
 		const long long n_words = (n_events + 31) >> 5;
-		long long seg = start >> 5;
+		long long seg = 0;
+		uint4 cur = mq_load_segment(row, seg, wpr, lane);
 		while (!st.lost && seg < n_words)
 		{
-			const long long wi = seg + lane;
-			unsigned word = wi < n_words ? row[wi] : 0u;
+			WALK_ADD(lane == 0, 7, 1);
+			// the next segment's words travel while this one is walked
+			const uint4 nxt = mq_load_segment(row, seg + MQ_SEG_WORDS, wpr, lane);
+			unsigned w4[4] = {cur.x, cur.y, cur.z, cur.w};
+			int c = 0;
+#pragma unroll
+			for (int j = 0; j < 4; ++j)
 			{
-				const long long first = wi << 5;
-				if (first < start) word = (start - first >= 32) ? 0u : (word & (0xffffffffu << (int)(start - first)));
+				const long long first = (seg + 4 * lane + j) << 5;
+				if (first < start) w4[j] = (start - first >= 32) ? 0u : (w4[j] & (0xffffffffu << (int)(start - first)));
+				c += __popc(w4[j]);
 			}
-			const int c = __popc(word);
 			int incl = c;
 #pragma unroll
 			for (int o = 1; o < 32; o <<= 1)
@@ -2516,19 +2669,29 @@ track_shared_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __
 				if (lane == 0) S.cand[0] = 0;
 			}
 			else
-				while (word)
+			{
+#pragma unroll
+				for (int j = 0; j < 4; ++j)
 				{
-					const int bit = __ffs(word) - 1;
-					word &= word - 1;
-					S.cand[off++] = (unsigned short)(lane * 32 + bit);
+					unsigned word = w4[j];
+					while (word)
+					{
+						const int bit = __ffs(word) - 1;
+						word &= word - 1;
+						S.cand[off++] = (unsigned short)((4 * lane + j) * 32 + bit);
+					}
 				}
+			}
 			__syncwarp();
 			bool restart = false;
+			// candidate records: chunk c + 1 is loaded before chunk c is walked
+			uint4 raw_next = make_uint4(0, 0, 0, 0);
+			if (lane < n_c) raw_next = __ldg(ev4 + ((seg << 5) + S.cand[lane]));
 			for (int cbase = 0; cbase < n_c && !restart && !st.lost; cbase += 32)
 			{
 				const int chunk_len = min(32, n_c - cbase);
-				uint4 raw = make_uint4(0, 0, 0, 0);
-				if (lane < chunk_len) raw = __ldg(ev4 + ((seg << 5) + S.cand[cbase + lane]));
+				const uint4 raw = raw_next;
+				if (cbase + 32 + lane < n_c) raw_next = __ldg(ev4 + ((seg << 5) + S.cand[cbase + 32 + lane]));
 				const int ex = (int)(raw.z & 0xffffu), ey = (int)(raw.z >> 16);
 				int resume = 0;
 				while (resume < chunk_len)
@@ -2558,7 +2721,11 @@ track_shared_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __
 					const long long at = (seg << 5) + S.cand[cbase + trig];
 					// ---- one Optimizer::optimize at stream event `at` and the bookkeeping around it
 					LmSummary L;
-					ss_optimize(S, st, ft, P, L);
+					WALK_T(w0);
+					mq_optimize(S, st, D.grids[st.frame_slot], P, L);
+					WALK_T(w1);
+					WALK_ADD(lane == 0, 1, w1 - w0);
+					WALK_ADD(lane == 0, 5, 1);
 					if (!L.filtered && lane == 0)
 					{
 						// Patch::addTrajectoryPosition: the two newest trajectory entries
@@ -2566,13 +2733,18 @@ track_shared_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __
 						gp.traj_x[0] = gp.traj_x[1]; gp.traj_y[0] = gp.traj_y[1]; gp.traj_ts[0] = gp.traj_ts[1];
 						gp.traj_x[1] = lx; gp.traj_y[1] = ly; gp.traj_ts[1] = st.cur_ts;
 					}
-					ss_update_num_of_events(st, ft, P);
-					if (lane == 0) write_record(records, n_records, record_cap, st, track_id, L, event_base + at);
+					WALK_T(w2);
+					mq_update_num_of_events(S, st, D.grids[D.latest], P);
+					WALK_T(w3);
+					WALK_ADD(lane == 0, 6, w3 - w2);
+					if (lane == 0) write_record(D.records, D.n_records, D.record_cap, st, track_id, L, D.event_base + at);
 					++n_opt;
 					start = at + 1;
 					if (!st.lost && (fabs(st.rx - srx) > margin || fabs(st.ry - sry) > margin))
 					{
 						// rebuild the mask row from `start` on around the rect's current position
+						WALK_T(w4);
+						WALK_ADD(lane == 0, 4, 1);
 						const int4 bb = candidate_bounds(st.rx, st.ry, margin);
 						const unsigned* ev32 = reinterpret_cast<const unsigned*>(events);
 						// eight mask words per trip: eight independent loads in flight per lane
@@ -2594,9 +2766,11 @@ track_shared_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __
 									__ballot_sync(0xffffffffu, x >= bb.x && x <= bb.y && y >= bb.z && y <= bb.w);
 								if (lane == j) mine = b2;
 							}
-							if (lane < 8 && w0 + lane < n_words) row[w0 + lane] = mine;
+							if (lane < 8 && w0 + lane < n_words) __stcg(row + w0 + lane, mine);
 						}
 						__syncwarp();
+						WALK_T(w5);
+						WALK_ADD(lane == 0, 3, w5 - w4);
 						srx = st.rx;
 						sry = st.ry;
 						restart = true;
@@ -2612,7 +2786,16 @@ track_shared_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __
 				pre = false;
 				restart = true;
 			}
-			seg = restart ? (start >> 5) : seg + 32;
+			if (restart)
+			{
+				seg = (start >> 5) & ~3LL;
+				cur = mq_load_segment(row, seg, wpr, lane);
+			}
+			else
+			{
+				seg += MQ_SEG_WORDS;
+				cur = nxt;
+			}
 		}
 		__syncwarp();
 		for (int k = lane; k < st.size; k += 32) gring[k] = S.ring[(st.tail + k) & RMASK];
@@ -2624,6 +2807,8 @@ track_shared_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __
 		{
 			store_state(st, gp);
 			gp.last_n_opt = n_opt;
+			WALK_T(wk_exit);
+			WALK_ADD(true, 0, wk_exit - wk_enter);
 			unsigned long long t_exit;
 			unsigned sm;
 			asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_exit));
@@ -2637,6 +2822,7 @@ track_shared_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __
 	if (lane == 0) S.req_kind = 4;
 	sb_post(S);
 }
+
 
 template <int MINCTAS>  // register budget matched to the launch, as for track_batch_kernel
 __global__ void __launch_bounds__(NT, MINCTAS)
@@ -2802,7 +2988,7 @@ cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, const int* 
 								   int words_per_row, double margin, const FrameTable& ft,
 								   const DevParams& P, ebt_opt_record* records,
 								   unsigned long long* n_records, unsigned long long record_cap,
-								   cudaStream_t stream, int* queue, int shared_pixel_warps)
+								   cudaStream_t stream)
 {
 	if (n_patches <= 0 || n_events <= 0) return cudaSuccess;
 	const dim3 pf_grid((unsigned)((n_events + PF_TILE - 1) / PF_TILE),
@@ -2814,25 +3000,6 @@ cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, const int* 
 	track_batch_kernel<M><<<n_patches, NT, 0, stream>>>(patches, n_patches, order, rings, nablas, events,  \
 														n_events, event_base, mask, words_per_row, margin, \
 														ft, P, records, n_records, record_cap)
-	if (shared_pixel_warps && queue && !P.products && !P.cost_maps && n_patches > 2 * sm_count)
-	{
-		static bool attr_set = false;
-		const size_t smem = SB_LEADERS * sizeof(StreamSlot);
-		if (!attr_set)
-		{
-			cudaError_t e = cudaFuncSetAttribute(track_shared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-												 (int)smem);
-			if (e != cudaSuccess) return e;
-			attr_set = true;
-		}
-		const int ctas = min((n_patches + 1) / 2, SB_CTAS * sm_count);
-		cudaError_t e = cudaMemcpyAsync(queue, &ctas, sizeof(int), cudaMemcpyHostToDevice, stream);  // pageable: staged by the driver
-		if (e != cudaSuccess) return e;
-		track_shared_kernel<<<ctas, SB_THREADS, smem, stream>>>(
-			patches, n_patches, order, rings, nablas, events, n_events, event_base, mask, words_per_row, margin, ft,
-			P, records, n_records, record_cap, queue);
-		return cudaGetLastError();
-	}
 	static const int forced = getenv("EBT_STREAM_BUILD") ? atoi(getenv("EBT_STREAM_BUILD")) : 0;  // tuning only
 	const int build = forced ? forced : (n_patches <= sm_count ? 1 : (n_patches <= 2 * sm_count ? 2 : 3));
 	if (build == 1)
@@ -2842,6 +3009,34 @@ cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, const int* 
 	else
 		EBT_TRACK_LAUNCH(EBT_MIN_CTAS);
 #undef EBT_TRACK_LAUNCH
+	return cudaGetLastError();
+}
+
+// Prefilter + stream kernel for the event batches of n_streams streams in one launch each.
+// descs: device array of n_streams descriptors; work: device array of n_work (stream, feature)
+// items, heaviest first; max_events / max_patches: the largest stream's (prefilter grid).
+cudaError_t ebt_launch_track_multi(const StreamDesc* descs, int n_streams, const WorkItem* work, int n_work,
+								   long long max_events, int max_patches, const DevParams& P, int* queue,
+								   cudaStream_t stream)
+{
+	if (n_streams <= 0 || n_work <= 0 || max_events <= 0) return cudaSuccess;
+	const dim3 pf_grid((unsigned)((max_events + PF_TILE - 1) / PF_TILE), (unsigned)((max_patches + PF_FEATS - 1) / PF_FEATS),
+					   (unsigned)n_streams);
+	prefilter_multi_kernel<<<pf_grid, PF_THREADS, 0, stream>>>(descs);
+	const size_t smem = SB_LEADERS * sizeof(StreamSlot);
+	int dev = 0;
+	cudaGetDevice(&dev);
+	static unsigned long long attr_devices = 0;
+	if (!(attr_devices >> dev & 1ull))
+	{
+		cudaError_t e = cudaFuncSetAttribute(track_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		if (e != cudaSuccess) return e;
+		attr_devices |= 1ull << dev;
+	}
+	const int ctas = min((n_work + 1) / 2, SB_CTAS * device_sm_count());
+	cudaError_t e = cudaMemcpyAsync(queue, &ctas, sizeof(int), cudaMemcpyHostToDevice, stream);  // pageable: staged by the driver
+	if (e != cudaSuccess) return e;
+	track_multi_kernel<<<ctas, SB_THREADS, smem, stream>>>(descs, work, n_work, P, queue);
 	return cudaGetLastError();
 }
 

@@ -14,7 +14,12 @@ cudaError_t ebt_launch_track_batch(DevPatch* patches, int n_patches, const int* 
 								   int words_per_row, double margin, const FrameTable& ft,
 								   const DevParams& P, ebt_opt_record* records,
 								   unsigned long long* n_records, unsigned long long record_cap,
-								   cudaStream_t stream, int* queue = nullptr, int shared_pixel_warps = 0);
+								   cudaStream_t stream);
+// The same for the event batches of n_streams streams in one launch (shared-pixel-warp
+// kernel, persistent CTAs pulling (stream, feature) work items from `queue`).
+cudaError_t ebt_launch_track_multi(const StreamDesc* descs, int n_streams, const WorkItem* work, int n_work,
+								   long long max_events, int max_patches, const DevParams& P, int* queue,
+								   cudaStream_t stream);
 int ebt_mask_words_per_row(long long n_events);
 cudaError_t ebt_launch_optimize_batch(const ebt_problem* problems, int n_problems,
 									  const ebt_event* events, const FrameTable& ft,

@@ -35,3 +35,17 @@ def aggregate(units: float, seconds: float, device=None):
     dist.all_reduce(u, op=dist.ReduceOp.SUM)
     dist.all_reduce(s, op=dist.ReduceOp.MAX)
     return u.item(), s.item()
+
+
+def gather_rows(row, device=None):
+    """Every rank's row of floats, in rank order (a list of lists); [row] when not
+    distributed.  Only used for the report: per-rank times and counts."""
+    import torch
+    import torch.distributed as dist
+    row = [float(v) for v in row]
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return [row]
+    mine = torch.tensor(row, dtype=torch.float64, device=device)
+    out = [torch.empty_like(mine) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, mine)
+    return [t.tolist() for t in out]

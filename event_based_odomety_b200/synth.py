@@ -16,6 +16,7 @@ Two generators, both host-side numpy, both deterministic for a given seed:
 from __future__ import annotations
 
 import dataclasses
+import os
 
 import numpy as np
 
@@ -201,6 +202,63 @@ def harris_corners(gray: np.ndarray, max_corners: int, quality: float = 0.01,
 
 
 @dataclasses.dataclass
+class Pose:
+    """Camera-plane motion of the generator: t_s -> (theta, offx, offy).  A class, not
+    a closure, so that a Stream can be pickled (streams generated by a process pool)."""
+    amplitude: float
+    theta_max: float
+
+    def __call__(self, t):
+        f1, f2, f3 = 0.5, 0.35, 0.25
+        return (self.theta_max * np.sin(2 * np.pi * f3 * t), self.amplitude * np.sin(2 * np.pi * f1 * t),
+                self.amplitude * (1 - np.cos(2 * np.pi * f2 * t)))
+
+
+def make_streams(specs, processes=None):
+    """make_stream(*spec) for every spec = (width, height, duration_s, rate, seed, max_corners),
+    generated by worker processes (`python -m event_based_odomety_b200.synth`, no CUDA in them)."""
+    import subprocess
+    import sys
+    import tempfile
+    specs = [tuple(sp) for sp in specs]
+    processes = max(1, min(processes or (os.cpu_count() or 1), len(specs)))
+    if processes == 1 or len(specs) == 1:
+        return [make_stream(*sp) for sp in specs]
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = [None] * len(specs)
+    with tempfile.TemporaryDirectory(prefix="ebt_streams_") as tmp:
+        pending = list(enumerate(specs))
+        running = []
+        while pending or running:
+            while pending and len(running) < processes:
+                i, sp = pending.pop(0)
+                path = os.path.join(tmp, f"s{i}.npz")
+                cmd = [sys.executable, "-m", "event_based_odomety_b200.synth", path] + [repr(v) for v in sp]
+                running.append((i, path, subprocess.Popen(cmd, cwd=root, stdout=subprocess.DEVNULL)))
+            i, path, proc = running.pop(0)
+            if proc.wait() != 0:
+                raise RuntimeError(f"stream generator failed for spec {specs[i]}")
+            out[i] = load_stream(path)
+    return out
+
+
+def save_stream(S, path):
+    np.savez(path, width=S.width, height=S.height, frames=np.stack(S.frames), frame_ts=np.array(S.frame_ts, np.int64),
+             events=S.events, corners=np.concatenate(S.corners) if S.corners else np.zeros((0, 2)),
+             corner_counts=np.array([len(c) for c in S.corners], np.int64),
+             pose=np.array([S.pose.amplitude, S.pose.theta_max]), margin=S.margin)
+
+
+def load_stream(path):
+    z = np.load(path)
+    cuts = np.cumsum(z["corner_counts"])[:-1]
+    return Stream(int(z["width"]), int(z["height"]), list(z["frames"]), [int(t) for t in z["frame_ts"]],
+                  z["events"].view(EVENT) if z["events"].dtype != EVENT else z["events"],
+                  [np.ascontiguousarray(c) for c in np.split(z["corners"], cuts)],
+                  Pose(float(z["pose"][0]), float(z["pose"][1])), int(z["margin"]))
+
+
+@dataclasses.dataclass
 class Stream:
     width: int
     height: int
@@ -248,12 +306,7 @@ def make_stream(width: int, height: int, duration_s: float, rate_ev_s: float, se
     rng = np.random.Generator(np.random.PCG64(seed))
     margin = int(amplitude * 2 + 0.2 * max(width, height) + 8)
     tex = make_texture(width + 2 * margin, height + 2 * margin, seed * 31 + 7, sigma=2.5).astype(np.float64)
-    f1, f2, f3 = 0.5, 0.35, 0.25
-    thm = np.deg2rad(theta_max_deg)
-
-    def pose(t):
-        return (thm * np.sin(2 * np.pi * f3 * t), amplitude * np.sin(2 * np.pi * f1 * t),
-                amplitude * (1 - np.cos(2 * np.pi * f2 * t)))
+    pose = Pose(amplitude, np.deg2rad(theta_max_deg))
 
     S = Stream(width, height, [], [], np.zeros(0, EVENT), [], pose, margin)
     yy, xx = np.mgrid[0:height, 0:width]
@@ -341,3 +394,10 @@ def run_stream(tracker, stream: Stream, n_frames: int | None = None, on_batch=No
         if on_batch:
             on_batch(k, ev, n)
     return total
+
+
+if __name__ == "__main__":
+    # worker of make_streams: argv = out.npz width height duration_s rate seed max_corners
+    import sys
+    _a = sys.argv[2:]
+    save_stream(make_stream(int(_a[0]), int(_a[1]), float(_a[2]), float(_a[3]), int(_a[4]), int(_a[5])), sys.argv[1])

@@ -140,6 +140,19 @@ int ebt_push_events(ebt_ctx* ctx, const ebt_event* events, int64_t n, int64_t* n
 int ebt_push_events_device(ebt_ctx* ctx, const ebt_event* d_events, int64_t n,
 						   int64_t* n_optimizations);
 
+/* configs[3] (64 independent streams): the reference runs one FeatureDetector per
+ * stream; this is FeatureDetector::updatePatches (feature_detector.cpp:585-619)
+ * for every event of n_streams detectors' batches in ONE prefilter launch and
+ * ONE stream-kernel launch, driven by one host thread with one wait for all of
+ * them.  events[i] / n_events[i] is stream i's batch for ctxs[i] (host buffers,
+ * or buffers on the contexts' device when device_resident != 0); results per
+ * stream are exactly those of ebt_push_events on that context alone.  All
+ * contexts must live on the same device and have equal image size and solver
+ * parameters; errors are reported on ctxs[0].  n_optimizations (may be NULL)
+ * receives n_streams counts. */
+int ebt_push_events_multi(ebt_ctx* const* ctxs, int n_streams, const ebt_event* const* events,
+						  const int64_t* n_events, int device_resident, int64_t* n_optimizations);
+
 /* FeatureDetector::getPatches / getArchivedPatches (feature_detector.h:71-76):
  * snapshots in list order.  *n_out = number available (may exceed cap). */
 int ebt_get_tracks(ebt_ctx* ctx, ebt_track* out, int cap, int archived, int* n_out);
@@ -303,13 +316,14 @@ int ebt_debug_feature_load(ebt_ctx* ctx, int32_t* track_ids, int32_t* n_opt, uin
  * Default 8. */
 int ebt_set_prefilter_margin(ebt_ctx* ctx, double pixels);
 
-/* Tuning knob of ebt_push_events (not part of the reference's API): which build of the
- * stream kernel runs when more than two features per SM are live.
- *   0 (default)  one CTA per feature (a leader warp + four pixel warps each)
- *   1            two features per CTA, their leader warps sharing the CTA's four pixel
- *                warps, features handed out from a queue (same results; measured equal on
- *                one stream, +7 % with several streams per GPU; needs the patch products
- *                and the cost map off, else mode 0 runs) */
+/* Tuning knob of ebt_push_events (not part of the reference's API): which stream kernel runs.
+ *   0            one CTA per feature (a leader warp + four pixel warps each)
+ *   1 (default)  automatic: persistent CTAs of two leader warps sharing four pixel warps,
+ *                features pulled from a queue, when more than two features per SM are live
+ *                (or several streams are pushed at once) and the patch products and the cost
+ *                map are off; one CTA per feature otherwise
+ *   2            the persistent-CTA kernel whenever products and cost map are off
+ * Same results either way (tests/test_gpu_stream.py runs both). */
 int ebt_set_stream_kernel(ebt_ctx* ctx, int mode);
 
 /* ABI self-description for binding generators/tests. */

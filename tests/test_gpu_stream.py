@@ -46,6 +46,12 @@ def compare(stream, max_patches, n_frames=None, split=None, margin=None, stream_
     else:
         n_gpu = synth.run_stream(gpu, stream, n_frames)
     assert n_cpu == n_gpu and n_cpu > 0
+    check_equal(cpu, gpu, n_cpu)
+    cpu.close()
+    gpu.close()
+
+
+def check_equal(cpu, gpu, n_cpu):
     rc, rg = cpu.records(), gpu.records()
     assert len(rc) == len(rg) == n_cpu
     assert np.array_equal(rc["track_id"], rg["track_id"])
@@ -75,8 +81,6 @@ def compare(stream, max_patches, n_frames=None, split=None, margin=None, stream_
             a, b = cpu.trajectory(tid), gpu.trajectory(tid)
             assert a.shape == b.shape and np.array_equal(a[:, 2], b[:, 2])
             assert np.abs(a[:, :2] - b[:, :2]).max() <= POS_TOL_PX
-    cpu.close()
-    gpu.close()
 
 
 @pytest.mark.gpu
@@ -93,20 +97,84 @@ def test_stream_split_batches():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("stream_kernel", [0, 1])
+@pytest.mark.parametrize("stream_kernel", [0, 1, 2])
 def test_stream_c2_shape(stream_kernel):
-    """BASELINE.json configs[1] shape: 346x260, 500 features, ~2 Mev/s (short); both builds of the
-    stream kernel (one CTA per feature / two features per CTA sharing its pixel warps)."""
+    """BASELINE.json configs[1] shape: 346x260, 500 features, ~2 Mev/s (short); both stream kernels
+    (0 one CTA per feature, 2 persistent CTAs of two leader warps sharing four pixel warps, 1 the
+    automatic choice between them)."""
     S = synth.make_stream(346, 260, 0.10, 2e6, seed=1002, max_corners=500)
     compare(S, 500, stream_kernel=stream_kernel)
 
 
 @pytest.mark.gpu
 def test_stream_shared_pixel_warps_split_and_margin():
-    """The two-features-per-CTA kernel with every batch pushed in 5 pieces and a 0.5 px prefilter margin
+    """The persistent-CTA kernel with every batch pushed in 5 pieces and a 0.5 px prefilter margin
     (mask rows rebuilt after nearly every optimisation)."""
     S = synth.make_stream(346, 260, 0.08, 2e6, seed=1052, max_corners=400)
-    compare(S, 400, split=5, margin=0.5, stream_kernel=1)
+    compare(S, 400, split=5, margin=0.5, stream_kernel=2)
+
+
+@pytest.mark.gpu
+def test_stream_shared_pixel_warps_few_features():
+    """The persistent-CTA kernel forced onto a c1-sized stream: fewer work items than CTAs could hold,
+    second leaders without a first feature, an empty queue."""
+    S = synth.make_stream(240, 180, 0.15, 500e3, seed=1012, max_corners=30)
+    compare(S, 100, stream_kernel=2)
+    S = synth.make_stream(240, 180, 0.10, 300e3, seed=1013, max_corners=1)
+    compare(S, 100, stream_kernel=2)
+
+
+@pytest.mark.gpu
+def test_multi_stream_push_equals_the_streams_alone():
+    """ebt_push_events_multi (configs[3]: independent streams in one launch): three streams of different
+    seeds, feature counts and batch sizes — one of them runs out of events early — each equal to the
+    CPU oracle's per-event loop on that stream alone."""
+    from event_based_odomety_b200.cabi import push_events_multi
+    streams = [synth.make_stream(240, 180, 0.15, 500e3, seed=2000, max_corners=69),
+               synth.make_stream(240, 180, 0.15, 300e3, seed=2001, max_corners=40),
+               synth.make_stream(240, 180, 0.10, 600e3, seed=2002, max_corners=60)]
+    caps = [100, 100, 60]
+    cpus = [CpuTracker(load_oracle(), S.width, S.height, c) for S, c in zip(streams, caps)]
+    gpus = [Tracker(S.width, S.height, c) for S, c in zip(streams, caps)]
+    n_cpu = [synth.run_stream(c, S) for c, S in zip(cpus, streams)]
+    n_gpu = [0, 0, 0]
+    n_frames = max(len(S.frames) for S in streams)
+    for k in range(n_frames):
+        batches = []
+        for i, (g, S) in enumerate(zip(gpus, streams)):
+            if k >= len(S.frames):
+                batches.append(S.events[:0])  # this stream has ended: an empty batch in the same call
+                continue
+            g.new_frame_begin(S.frames[k], S.frame_ts[k], S.corners[k])
+            ids, xy = g.get_uninit()
+            if len(ids):
+                nxt = S.lk_next(k, xy)
+                for j, tid in enumerate(ids):
+                    inside = (0 <= nxt[j, 0] < S.width) and (0 <= nxt[j, 1] < S.height)
+                    g.set_flow(tid, int(inside), nxt[j, 0], nxt[j, 1])
+            g.new_frame_end()
+            batches.append(S.events_between(k))
+        got = push_events_multi(gpus, batches)
+        n_gpu = [a + b for a, b in zip(n_gpu, got)]
+    assert n_gpu == n_cpu and min(n_cpu) > 0
+    for c, g, n in zip(cpus, gpus, n_cpu):
+        check_equal(c, g, n)
+        c.close()
+        g.close()
+
+
+@pytest.mark.gpu
+def test_multi_stream_push_rejects_mismatched_contexts():
+    from event_based_odomety_b200.cabi import EbtError, push_events_multi
+    a, b = Tracker(240, 180, 10), Tracker(346, 260, 10)
+    ev = np.zeros(4, synth.EVENT)
+    with pytest.raises(EbtError, match="must be equal"):
+        push_events_multi([a, b], [ev, ev])
+    with pytest.raises(EbtError, match="listed twice"):
+        push_events_multi([a, a], [ev, ev])
+    assert push_events_multi([a], [ev]) == [0]  # no patches yet: events consumed, nothing happens
+    a.close()
+    b.close()
 
 
 @pytest.mark.gpu

@@ -32,6 +32,9 @@ def _worker(rank, world, port, out):
     t = CpuTracker(load_oracle(), 120, 90, 20)
     n = synth.run_stream(t, S)
     units, secs = multi.aggregate(n, 1.0 + rank)
+    rows = multi.gather_rows([rank, n, 1.0 + rank])  # bench.py's per-rank report
+    assert [r[0] for r in rows] == list(range(world)) and rows[rank][1] == n
+    assert sum(r[1] for r in rows) == units and max(r[2] for r in rows) == secs
     out.put((rank, n, units, secs, len(S.events)))
     dist.barrier()
     dist.destroy_process_group()
@@ -59,3 +62,4 @@ def test_stream_placement():
         assert max(len(multi.streams_of_rank(64, r, world)) for r in range(world)) == 64 // world
     assert multi.stream_seed(1002, 0) == 1002 and multi.stream_seed(1002, 3) == 2003
     assert multi.aggregate(5, 2.0) == (5.0, 2.0)
+    assert multi.gather_rows([1, 2.5]) == [[1.0, 2.5]]
