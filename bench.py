@@ -77,6 +77,9 @@ def parse():
                     help="ebt_set_stream_kernel: 0 one CTA per feature, 2 persistent CTAs sharing pixel warps, 1 automatic")
     ap.add_argument("--streams", type=int, default=None,
                     help="c4: total number of streams over all GPUs (default 64); c1-c3: streams per GPU (default 1)")
+    ap.add_argument("--shard", default="streams", choices=["streams", "features"],
+                    help="multi-GPU partition: independent streams per GPU (default), or ONE stream's features over "
+                         "the GPUs (feature f -> GPU f mod N, host-side gather of patch state after every batch)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU time budget of the cpu_baseline / parity sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     a = ap.parse_args()
@@ -356,7 +359,14 @@ def main_ours(args):
 
     w, h, feat, rate, seed = WORKLOADS[args.workload]
     cores = max(1, (os.cpu_count() or 1) // max(1, min(world, 8)))
-    if args.workload == "c4":
+    by_features = args.shard == "features" and world > 1
+    if by_features:
+        if args.workload == "c4":
+            raise SystemExit("bench.py: --shard features splits ONE stream (c1/c2/c3), not the 64 of c4")
+        total_streams = 1
+        scaling = "strong"
+        specs = [(w, h, args.duration, rate, seed, feat)]  # the same stream on every rank
+    elif args.workload == "c4":
         total_streams = args.streams or C4_STREAMS
         mine = multi.streams_of_rank(total_streams, rank, world)  # stream s -> GPU s mod G
         scaling = "strong"
@@ -375,6 +385,9 @@ def main_ours(args):
     nS = len(lanes)
     trackers = [L.tr for L in lanes]
     L0 = lanes[0]
+    # one stream's features over the ranks: rank r tracks track ids = r (mod world); patch state is gathered on
+    # the host (gloo) after every batch
+    shard = multi.FeatureShard(L0.tr, rank, world, multi.host_group()) if by_features else None
     nF = max(L.nF for L in lanes)
     n_events = sum(L.n_events for L in lanes)
     fp64_peak, fp32_peak = trackers[0].measure_fma_peak()
@@ -408,7 +421,8 @@ def main_ours(args):
                     frame(L)
             if len(live) == 1:
                 ptr, n = live[0].batch(k, host)
-                total += live[0].tr.push_events_ptr(ptr, n) if host else live[0].tr.push_events_device(ptr, n)
+                pusher = shard if shard is not None else live[0].tr
+                total += pusher.push_events_ptr(ptr, n) if host else pusher.push_events_device(ptr, n)
             else:
                 b = [L.batch(k, host) for L in live]
                 total += sum(push_events_multi([L.tr for L in live], [p for p, _ in b], [n for _, n in b],
@@ -461,7 +475,8 @@ def main_ours(args):
         return multi.aggregate(units, seconds, device="cuda")
 
     g_opts, g_secs = agg(opts, secs)
-    g_events, _ = agg(n_events * args.steps, secs)
+    # sharded by features every rank reads the whole stream: its events count once
+    g_events, _ = agg(n_events * args.steps if (not by_features or rank == 0) else 0, secs)
     ge_opts, ge_secs = agg(e_opts, e_secs)
     g_flops, _ = agg(flops_step, secs)
     g_kt, _ = agg(kt_ms, secs)
@@ -503,7 +518,10 @@ def main_ours(args):
                 "workload": workload_name(args.workload, total_streams),
                 "segment": f"{args.duration:g} s = {nF} frames per stream; rank 0: {n_events} events, {int(opts_step)} "
                            f"optimisations, {n_tracks} tracks per step over its {nS} stream(s)",
-                "sharding": (f"{total_streams} stream(s) over {world} GPU(s) ({nS} on rank 0: one context each, all of a "
+                "sharding": (f"ONE stream's features over {world} GPUs (track id mod {world}); every GPU gets every "
+                             f"image and event batch; patch state gathered on the host (gloo) after every batch; no "
+                             f"NCCL collective, no GPU-to-GPU traffic" if by_features else
+                             f"{total_streams} stream(s) over {world} GPU(s) ({nS} on rank 0: one context each, all of a "
                              f"GPU's batches in one ebt_push_events_multi launch), no collective on the data path"
                              if total_streams > 1 else "single stream"),
                 "l2": "flushed: a 256 MB buffer (> 126 MB L2) is rewritten at the start of every step, inside the "
@@ -556,6 +574,8 @@ def main_ours(args):
                       f"thread as the reference runs it")
             line["cpu_baseline"] = {"value": n / dt, "unit": "optimisations/s", "cores": 1, "kind": kind,
                                     "events_per_s": after / dt, "sample": sample}
+            if by_features:  # rank 0 holds the records of its own tracks
+                cpu_rec = cpu_rec[cpu_rec["track_id"] % world == 0]
             line["parity"] = parity_gate(cpu_rec, gpu_rec0, consumed)
             line["parity"]["against"] = ("oracle/_ref (the reference's Patch + Optimizer + Ceres, compiled unmodified)"
                                          if kind == "reference" else "oracle port")

@@ -66,6 +66,10 @@ EXPORTS = {
     "ebt_push_events": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
     "ebt_push_events_device": (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]),
     "ebt_push_events_multi": (C.c_int, [_vp, C.c_int, _vp, _vp, C.c_int, _vp]),
+    "ebt_set_shard": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "ebt_sizeof_patch_state": (C.c_size_t, []),
+    "ebt_get_patch_state": (C.c_int, [_vp, _vp, C.c_int, C.POINTER(C.c_int)]),
+    "ebt_merge_patch_state": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
     "ebt_parse_events_text": (C.c_int, [_vp, C.c_char_p, C.c_size_t, C.c_int, _vp, C.c_int64,
                                         C.POINTER(C.c_int64), C.POINTER(C.c_size_t)]),
     "ebt_parse_events_text_static": (C.c_int, [C.c_int, _vp, _vp, C.c_size_t, C.c_int, _vp, C.c_int64,
@@ -308,6 +312,25 @@ class Tracker:
         return n.value
 
     # ---- ingestion ------------------------------------------------------
+    # ---- feature-batch sharding ------------------------------------------
+    def set_shard(self, index, count):
+        self._ck(self.lib.ebt_set_shard(self.ctx, int(index), int(count)))
+
+    def patch_state(self):
+        """Opaque per-patch state of this shard's list, (n, ebt_sizeof_patch_state()) bytes."""
+        sz = self.lib.ebt_sizeof_patch_state()
+        n = C.c_int()
+        self._ck(self.lib.ebt_get_patch_state(self.ctx, None, 0, C.byref(n)))
+        out = np.zeros((max(n.value, 1), sz), np.uint8)
+        self._ck(self.lib.ebt_get_patch_state(self.ctx, _ptr(out), n.value, C.byref(n)))
+        return out[:n.value]
+
+    def merge_patch_state(self, states):
+        """states: one patch_state() array per shard, in shard order."""
+        states = [np.ascontiguousarray(s, np.uint8) for s in states]
+        ptrs = (_vp * len(states))(*[s.ctypes.data if len(s) else None for s in states])
+        self._ck(self.lib.ebt_merge_patch_state(self.ctx, ptrs, len(states), len(states[0])))
+
     def parse_events_text(self, text: bytes, final=True, cap=None):
         """(events, bytes consumed) of a buffer of "t_sec x y p" lines."""
         if cap is None:

@@ -147,6 +147,7 @@ struct ebt_ctx
 	std::vector<int> work_load, work_idx;
 	std::vector<WorkItem> work_tmp;
 	cudaEvent_t join_event = nullptr;  // orders this context's own stream before a multi-stream launch
+	int shard_index = 0, shard_count = 1;  // ebt_set_shard: this context tracks track ids = index (mod count)
 	double opt_per_event = 0.25;       // optimisations per stream event of the last piece (bounds the next piece)
 	unsigned char* arch_stage = nullptr;  // pinned: products of the patches archived at a frame
 	size_t arch_stage_cap = 0;
@@ -965,6 +966,7 @@ static int newFrameBegin(ebt_ctx* ctx, const uint8_t* gray, int64_t ts_us, const
 		p.track_id = ctx->next_track_id++;
 		p.num_of_events = 75;  // patch.cpp:22
 		p.frame_slot = slot;
+		p.foreign = (p.track_id % ctx->shard_count) != ctx->shard_index;
 		p.store_slot = ctx->free_slots.back();
 		ctx->free_slots.pop_back();
 		addTraj(ctx, p);
@@ -1198,7 +1200,7 @@ static void estimateLoad(ebt_ctx* ctx)
 	for (int i = 0; i < P; ++i)
 	{
 		const DevPatch& p = ctx->h[static_cast<size_t>(i)];
-		if (!p.lost && p.init && p.n_costs > 0)
+		if (!p.lost && !p.foreign && p.init && p.n_costs > 0)
 		{
 			sum += p.last_n_opt;
 			++cnt;
@@ -1209,7 +1211,8 @@ static void estimateLoad(ebt_ctx* ctx)
 	for (int i = 0; i < P; ++i)
 	{
 		const DevPatch& p = ctx->h[static_cast<size_t>(i)];
-		ctx->load_est[static_cast<size_t>(i)] = p.lost ? -1 : (!p.init ? 0 : (p.n_costs == 0 ? mean : p.last_n_opt));
+		ctx->load_est[static_cast<size_t>(i)] =
+			(p.lost || p.foreign) ? -1 : (!p.init ? 0 : (p.n_costs == 0 ? mean : p.last_n_opt));
 	}
 }
 
@@ -1608,6 +1611,57 @@ int ebt_push_events_device(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, i
 		return fail(ctx, EBT_E_INVALID, "ebt_push_events_device: bad argument");
 	CU(cudaSetDevice(ctx->device));
 	return runPieces(ctx, d_events, n, n_optimizations);
+}
+
+// ---- feature-batch sharding of one stream over several contexts (GPUs) ----------
+int ebt_set_shard(ebt_ctx* ctx, int index, int count)
+{
+	if (!ctx || count < 1 || index < 0 || index >= count)
+		return fail(ctx, EBT_E_INVALID, "ebt_set_shard: need 0 <= index < count");
+	if (!ctx->h.empty() || !ctx->arch.empty())
+		return fail(ctx, EBT_E_INVALID, "ebt_set_shard: set the shard before the first image (or after ebt_reset)");
+	ctx->shard_index = index;
+	ctx->shard_count = count;
+	return EBT_OK;
+}
+
+size_t ebt_sizeof_patch_state(void) { return sizeof(DevPatch); }
+
+int ebt_get_patch_state(ebt_ctx* ctx, void* out, int cap, int* n_out)
+{
+	if (!ctx || !n_out || cap < 0 || (cap > 0 && !out)) return fail(ctx, EBT_E_INVALID, "ebt_get_patch_state: bad argument");
+	*n_out = static_cast<int>(ctx->h.size());
+	const size_t n = std::min(ctx->h.size(), static_cast<size_t>(cap));
+	if (n) std::memcpy(out, ctx->h.data(), n * sizeof(DevPatch));
+	return EBT_OK;
+}
+
+int ebt_merge_patch_state(ebt_ctx* ctx, const void* const* states, int n_shards, int n_patches)
+{
+	if (!ctx || !states || n_shards != ctx->shard_count)
+		return fail(ctx, EBT_E_INVALID, "ebt_merge_patch_state: one state per shard is needed");
+	if (n_patches != static_cast<int>(ctx->h.size()))
+		return fail(ctx, EBT_E_INVALID, "ebt_merge_patch_state: the shards' patch lists differ in length");
+	for (int s = 0; s < n_shards; ++s)
+		if (!states[s] && n_patches > 0) return fail(ctx, EBT_E_INVALID, "ebt_merge_patch_state: null state");
+	for (size_t i = 0; i < ctx->h.size(); ++i)
+	{
+		DevPatch& mine = ctx->h[i];
+		const int owner = mine.track_id % ctx->shard_count;
+		if (owner == ctx->shard_index) continue;
+		DevPatch theirs;
+		std::memcpy(&theirs, static_cast<const unsigned char*>(states[owner]) + i * sizeof(DevPatch), sizeof(DevPatch));
+		if (theirs.track_id != mine.track_id)
+			return fail(ctx, EBT_E_INVALID, "ebt_merge_patch_state: the shards' patch lists are out of step at entry " +
+											std::to_string(i));
+		// the owner's tracking state; where the patch's data lives on THIS device stays ours
+		theirs.store_slot = mine.store_slot;
+		theirs.frame_slot = mine.frame_slot;
+		theirs.foreign = 1;
+		mine = theirs;
+	}
+	ctx->host_dirty = true;
+	return EBT_OK;
 }
 
 int ebt_get_tracks(ebt_ctx* ctx, ebt_track* out, int cap, int archived, int* n_out)

@@ -45,7 +45,11 @@ struct DevPatch
 	// load diagnostics of the previous push (ebt_debug_feature_load): %globaltimer at the
 	// CTA's entry and exit, and the SM it ran on
 	unsigned long long last_t0_ns, last_t1_ns;
-	int last_sm, pad_;
+	int last_sm;
+	// feature-batch sharding of one stream over several GPUs (ebt_set_shard): this patch is
+	// tracked by another shard; it stays in the list (association and list order are global)
+	// but no kernel of this context touches it
+	int foreign;
 };
 
 // Solver constants: the reference's OptimizerParams

@@ -1598,7 +1598,7 @@ __device__ __forceinline__ void prefilter_tile(const DevPatch* __restrict__ patc
 	{
 		const int f = f0 + k;
 		int4 b = make_int4(1, 0, 1, 0);  // empty
-		if (f < n_patches && !patches[f].lost) b = candidate_bounds(patches[f].rx, patches[f].ry, margin);
+		if (f < n_patches && !patches[f].lost && !patches[f].foreign) b = candidate_bounds(patches[f].rx, patches[f].ry, margin);
 		bounds[k] = b;
 	}
 	__syncthreads();
@@ -1731,7 +1731,7 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 	if ((int)blockIdx.x >= n_patches) return;
 	const int f = order[blockIdx.x];
 	DevPatch& gp = patches[f];
-	if (gp.lost) return;  // uniform over the CTA
+	if (gp.lost || gp.foreign) return;  // uniform over the CTA
 	unsigned long long t_enter;
 	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_enter));
 	WALK_T(wk_enter);
@@ -2614,7 +2614,7 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 		const WorkItem item = work[oi];
 		const StreamDesc& D = descs[item.stream];
 		DevPatch& gp = D.patches[item.feature];
-		if (gp.lost) continue;
+		if (gp.lost || gp.foreign) continue;
 		unsigned long long t_enter;
 		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_enter));
 		WALK_T(wk_enter);

@@ -49,3 +49,57 @@ def gather_rows(row, device=None):
     out = [torch.empty_like(mine) for _ in range(dist.get_world_size())]
     dist.all_gather(out, mine)
     return [t.tolist() for t in out]
+
+
+class FeatureShard:
+    """One stream's features over the ranks of a job (north_star "partitioned by feature batch"):
+    every rank feeds its own tracker context the SAME images and event batches; rank r tracks the patches
+    whose track id = r (mod world) (ebt_set_shard) and, after every push, the ranks gather their patch
+    states on the HOST (a gloo group: no NCCL collective, no GPU-to-GPU traffic) and merge them
+    (ebt_merge_patch_state), so that the next image's association, window sizes and archive decisions are
+    the same on every rank and the same as on one GPU.  Wraps a cabi.Tracker; everything else passes through."""
+
+    def __init__(self, tracker, rank, world, group=None):
+        self.tr, self.rank, self.world, self.group = tracker, rank, world, group
+        tracker.set_shard(rank, world)
+
+    def __getattr__(self, k):
+        return getattr(self.tr, k)
+
+    def exchange(self):
+        import numpy as np
+        import torch
+        import torch.distributed as dist
+        mine = self.tr.patch_state()
+        if self.world == 1 or len(mine) == 0:
+            return
+        t = torch.from_numpy(np.ascontiguousarray(mine).reshape(-1))
+        out = [torch.empty_like(t) for _ in range(self.world)]
+        dist.all_gather(out, t, group=self.group)  # CPU tensors on a gloo group: a host-side gather
+        self.tr.merge_patch_state([o.numpy().reshape(mine.shape) for o in out])
+
+    def push_events(self, events):
+        n = self.tr.push_events(events)
+        self.exchange()
+        return n
+
+    def push_events_ptr(self, ptr, n_events):
+        n = self.tr.push_events_ptr(ptr, n_events)
+        self.exchange()
+        return n
+
+    def push_events_device(self, ptr, n_events):
+        n = self.tr.push_events_device(ptr, n_events)
+        self.exchange()
+        return n
+
+
+def host_group():
+    """A gloo process group next to the default one (NCCL on the GPU box) for host-side gathers; the default
+    group itself when that already is gloo; None when not distributed."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return None
+    if dist.get_backend() == "gloo":
+        return dist.group.WORLD
+    return dist.new_group(backend="gloo")

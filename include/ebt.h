@@ -153,6 +153,26 @@ int ebt_push_events_device(ebt_ctx* ctx, const ebt_event* d_events, int64_t n,
 int ebt_push_events_multi(ebt_ctx* const* ctxs, int n_streams, const ebt_event* const* events,
 						  const int64_t* n_events, int device_resident, int64_t* n_optimizations);
 
+/* ---- one stream's features over several GPUs (north_star: "partitioned ... by
+ * feature batch or stream with only a host-side gather of tracks") ------------
+ * The reference has one FeatureDetector per stream on one core; there is no
+ * counterpart.  Between two images a patch's evolution depends only on its own
+ * state and the ordered event stream (feature_detector.cpp:587-617); the only
+ * cross-feature steps are associatePatches and the archive at image time
+ * (:512-535, 630-664).  So G contexts (one per GPU) are fed the SAME images and
+ * the SAME event batches; context `index` of `count` tracks the patches whose
+ * track id = index (mod count) and carries the others along as list entries only.
+ * After every ebt_push_events the caller gathers the shards' patch states on the
+ * host (ebt_get_patch_state: n x ebt_sizeof_patch_state() opaque bytes, list order)
+ * and hands all of them to every shard (ebt_merge_patch_state), so that the next
+ * image's association, window sizes and archive decisions are the same everywhere
+ * — and the same as on one GPU.  Optimisation records, trajectories and patch
+ * products of a track live on its owner shard.  No GPU-to-GPU traffic, no collective. */
+int ebt_set_shard(ebt_ctx* ctx, int index, int count);
+size_t ebt_sizeof_patch_state(void);
+int ebt_get_patch_state(ebt_ctx* ctx, void* out, int cap, int* n_out);
+int ebt_merge_patch_state(ebt_ctx* ctx, const void* const* states, int n_shards, int n_patches);
+
 /* FeatureDetector::getPatches / getArchivedPatches (feature_detector.h:71-76):
  * snapshots in list order.  *n_out = number available (may exceed cap). */
 int ebt_get_tracks(ebt_ctx* ctx, ebt_track* out, int cap, int archived, int* n_out);

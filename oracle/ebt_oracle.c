@@ -930,7 +930,7 @@ static void optimize_patch(opatch* p, const oframe* frame, double huber_a,
 /* ------------------------------------------------------------------------ */
 /* tracker::FeatureDetector — tracking part (ft/src/feature_detector.cpp)    */
 /* ------------------------------------------------------------------------ */
-#define MAX_FRAMES 64
+#define MAX_FRAMES 4096 /* optimizers_ is an unbounded map in the reference */
 typedef struct
 {
 	int w, h, max_patches;

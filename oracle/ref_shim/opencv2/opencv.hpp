@@ -148,6 +148,9 @@ class Mat
 
 	Mat() {}
 	Mat(int r, int c, int /*type*/) { create(r, c); }
+	// header over caller-owned pixels, cv::Mat(rows, cols, type, data): no copy, as in
+	// OpenCV (how a CV_8U frame reaches FeatureDetector::newImage in the drop-in tests)
+	Mat(int r, int c, int type, void* ext) : rows(r), cols(c), data(static_cast<unsigned char*>(ext)), type_(type), step_(c) {}
 
 	static Mat zeros(int r, int c, int type)
 	{
@@ -166,7 +169,9 @@ class Mat
 		base_ = buf_->data();
 		data = reinterpret_cast<unsigned char*>(base_);
 	}
-	int type() const { return CV_64F; }
+	int type() const { return type_; }
+	int channels() const { return 1; }
+	bool isContinuous() const { return step_ == cols; }
 	bool empty() const { return rows == 0 || cols == 0; }
 
 	template <typename T>
@@ -202,6 +207,7 @@ class Mat
 	}
 
    private:
+	int type_ = CV_64F;
 	int step_ = 0;
 	std::shared_ptr<std::vector<double>> buf_;
 	double* base_ = nullptr;

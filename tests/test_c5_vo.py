@@ -1,0 +1,118 @@
+"""BASELINE.json configs[4] (C5): the full VO pipeline — GPU tracker + the reference's UNCHANGED CPU
+Ceres/OpenGV back end — on a synthetic stream, trajectory ATE matched to the CPU tracker's.
+
+oracle/_ref/vo_driver is the reference's implementation/visual_odometry/src/*.cpp + vendored OpenGV + Ceres
+compiled unmodified against the DROP-IN headers include/ebt_dropin/feature_tracker/*.h (which replace the
+reference's feature_tracker/include on the include path) and driven exactly as tools::Evaluator drives
+tracker and VO (evaluator.cpp:32-104).  That it builds at all is the proof that the reference's callers
+compile against the drop-in boundary; it is built in the authoring container (`make -C oracle vo`, needs
+/root/reference) and travels to the GPU box prebuilt.
+
+* CPU test: the back end behind the drop-in tracker::Patch on ideal tracks (no GPU involved).
+* GPU test: mode "gpu" = tracker::FeatureDetector (drop-in, CUDA library) fed event by event and image by
+  image, Keyframe(getPatches()) -> VisualOdometryFrontEnd::newKeyframeCandidate, against the golden result of
+  the same back end fed with the CPU oracle's tracks (tests/golden/c5_vo_oracle.json,
+  tests/golden/make_c5_golden.py) and, tighter, against the same back end fed with the CPU oracle's tracks
+  computed on the spot from the same corners and LK flows: equal keyframes, ATE
+  (visual_odometry::align_cameras_sim3, vo/src/aligner.cpp:95-114) and camera centres equal to 1e-3 relative."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from tools import c5_case
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+needs_driver = pytest.mark.skipif(not os.path.exists(c5_case.VO_DRIVER),
+                                  reason="oracle/_ref/vo_driver is built in the authoring container only")
+
+
+@needs_driver
+def test_unmodified_vo_back_end_behind_the_dropin_patch(tmp_path):
+    S = c5_case.make_stream(1.5)
+    rng = np.random.Generator(np.random.PCG64(3))
+    pts0 = np.stack([rng.uniform(15, c5_case.W - 15, 120), rng.uniform(15, c5_case.H - 15, 120)], axis=1)
+    q = S.to_texture(0.0, pts0)
+    per = []
+    for k in range(len(S.frames)):
+        p = S.from_texture(S.frame_ts[k] * 1e-6, q)
+        ok = (p[:, 0] > 8) & (p[:, 0] < c5_case.W - 8) & (p[:, 1] > 8) & (p[:, 1] < c5_case.H - 8)
+        per.append((np.nonzero(ok)[0].astype(np.int32), p[ok]))
+    inp, out = str(tmp_path / "ideal.bin"), str(tmp_path / "ideal.txt")
+    c5_case.write_tracks_input(inp, S, per)
+    r = c5_case.run_vo("tracks", inp, out)
+    # every image from the third on becomes a keyframe on ideal tracks; the plane-parallel trajectory is
+    # recovered to a few millimetres over ~0.2 m
+    assert r["keyframes"] == len(S.frames) - 2
+    assert r["ate_count"] == r["keyframes"] and r["ate_rmse"] < 0.01
+
+
+class CpuTrackerBehindTheGpuFrontEnd:
+    """The CPU oracle tracker with FeatureDetector::newImage's OpenCV calls (goodFeaturesToTrack,
+    calcOpticalFlowPyrLK) answered by the CUDA front-end kernels — the same corners and flows the drop-in
+    detector uses inside ebt_new_image — so that the two arms differ in the hot path only."""
+
+    def __init__(self, cpu, fe):
+        self.cpu, self.fe, self.prev = cpu, fe, None
+
+    def __getattr__(self, k):
+        return getattr(self.cpu, k)
+
+    def new_image(self, gray, ts):
+        self.cpu.new_frame_begin(gray, ts, self.fe.detect_features(gray))
+        ids, xy = self.cpu.get_uninit()
+        if len(ids):
+            nxt, st = self.fe.lk_flow(self.prev, gray, xy.astype(np.float32))
+            for i, tid in enumerate(ids):
+                self.cpu.set_flow(tid, int(st[i]), nxt[i, 0], nxt[i, 1])
+        self.cpu.new_frame_end()
+        self.prev = gray
+
+
+@needs_driver
+@pytest.mark.gpu
+def test_c5_gpu_tracker_with_unchanged_cpu_back_end(tmp_path):
+    from event_based_odomety_b200.cabi import Tracker
+    from tests._oracle import CpuTracker, load_oracle
+    gold = json.load(open(os.path.join(HERE, "golden", "c5_vo_oracle.json")))
+    S = c5_case.make_stream(gold["duration_s"])
+    assert len(S.frames) == gold["frames"] and len(S.events) == gold["events"]
+    # arm 1: drop-in tracker::FeatureDetector (CUDA) + the unchanged back end, driven like tools::Evaluator
+    inp, out = str(tmp_path / "gpu.bin"), str(tmp_path / "gpu.txt")
+    c5_case.write_gpu_input(inp, S)
+    dump = str(tmp_path / "gpu_tracks.txt")
+    g = c5_case.run_vo("gpu", inp, out, dump)
+    # arm 2: the CPU oracle's tracks (same corners and LK flows) + the same back end
+    fe = Tracker(c5_case.W, c5_case.H, c5_case.MAX_PATCHES)
+    cpu = CpuTrackerBehindTheGpuFrontEnd(CpuTracker(load_oracle(), c5_case.W, c5_case.H, c5_case.MAX_PATCHES), fe)
+    per = c5_case.tracks_of(cpu, S)
+    n_cpu = len(cpu.records())
+    fe.close()
+    inp2, out2 = str(tmp_path / "cpu.bin"), str(tmp_path / "cpu.txt")
+    c5_case.write_tracks_input(inp2, S, per)
+    c = c5_case.run_vo("tracks", inp2, out2)
+    print("gpu   ", {k: v for k, v in g.items() if k != "pose"})
+    print("oracle", {k: v for k, v in c.items() if k != "pose"}, "optimisations", n_cpu)
+    print("golden (numpy front end) keyframes", gold["keyframes"], "ate_rmse", gold["ate_rmse"])
+    assert g["optimisations"] == n_cpu > 10000
+    # the live patches after every image: same tracks, corners equal far below the 0.05 px gate
+    rows = np.loadtxt(dump).reshape(-1, 4)
+    worst = 0.0
+    for k, (ids, xy) in enumerate(per):
+        r = rows[rows[:, 0] == k]
+        assert np.array_equal(r[:, 1].astype(np.int32), ids), f"track lists differ after image {k}"
+        worst = max(worst, np.abs(r[:, 2:] - xy).max(initial=0))
+    print(f"max corner difference between the two arms over all images: {worst:.3e} px")
+    assert worst <= 1e-6
+    assert g["keyframes"] == c["keyframes"] > 50 and g["landmarks"] == c["landmarks"]
+    assert np.array_equal(g["pose"][:, 0], c["pose"][:, 0])       # the same images became keyframes
+    # tracks agree to ~1e-11 px, so RANSAC and the bundle adjustment take the same path: the ATE of
+    # visual_odometry::align_cameras_sim3 and the camera centres must match far below their own size
+    assert abs(g["ate_rmse"] - c["ate_rmse"]) <= 1e-3 * c["ate_rmse"]
+    assert np.abs(g["pose"][:, 1:] - c["pose"][:, 1:]).max() <= 1e-3 * np.abs(c["pose"][:, 1:]).max()
+    # against the all-CPU golden (numpy Harris/LK restatement, LK differs by ~1e-4 px so RANSAC may draw
+    # differently): same number of keyframes, ATE of the same order (trajectory extent ~0.3 m)
+    assert g["keyframes"] == gold["keyframes"]
+    assert g["ate_rmse"] < 0.05 and gold["ate_rmse"] < 0.05

@@ -9,7 +9,7 @@ import pytest
 
 from event_based_odomety_b200 import synth
 from event_based_odomety_b200.cabi import Tracker
-from tests._oracle import CpuBatch, load_oracle
+from tests._oracle import CpuBatch, load_oracle, load_ref
 
 POS_TOL_PX = 0.05
 ANGLE_TOL_DEG = 0.5
@@ -181,3 +181,43 @@ def test_batch_shared_pixel_warp_kernel_edges():
     assert dpos.max() <= POS_TOL_PX
     assert _angle_diff_deg(osol["flow_dir"][ok], gsol["flow_dir"][ok]).max() <= ANGLE_TOL_DEG
     assert same_path.mean() >= 0.99
+
+
+@pytest.mark.gpu
+def test_batch_parity_against_the_reference_build():
+    """500 problems against oracle/_ref (the reference's Patch + Optimizer + Ceres compiled unmodified),
+    not its port: integer patches bit-exact, positions / angle within the north-star gates, costs 1e-6."""
+    ref = load_ref()
+    if ref is None:
+        pytest.skip("oracle/_ref/libebt_ref.so is not built here")
+    ps = synth.make_problems(500, 346, 260, seed=3500, n_frames=2)
+    ob = CpuBatch(ref, 346, 260)
+    tr = Tracker(346, 260)
+    for f in ps.frames:
+        assert ob.add_frame(f) == tr.add_frame(f)
+    osol, onab, _, _ = ob.optimize(ps.problems, ps.events)
+    gsol, gnab = tr.optimize_batch(ps.problems, ps.events)
+    tr.close()
+    assert np.array_equal(onab.astype(np.int32), gnab), "integer event patches differ"
+    dpos = np.hypot(osol["x"] - gsol["x"], osol["y"] - gsol["y"])
+    dang = _angle_diff_deg(osol["flow_dir"], gsol["flow_dir"])
+    print(f"\nvs reference build: max dpos {dpos.max():.3e} px, max dangle {dang.max():.3e} deg, "
+          f"max dcost {np.abs(osol['final_cost'] - gsol['final_cost']).max():.3e}")
+    assert dpos.max() <= POS_TOL_PX and dang.max() <= ANGLE_TOL_DEG
+    assert np.abs(osol["final_cost"] - gsol["final_cost"]).max() < 1e-6
+
+
+@pytest.mark.gpu
+def test_batch_kernels_are_deterministic():
+    """Stand-in for racecheck (closed on this pool): optimize_batch_shared_kernel hands jobs over through
+    sequence numbers in shared memory.  2000 problems (shared-pixel-warp kernel) and 100 problems (one CTA
+    per problem), 50 launches each: bit-identical solutions and integer patches."""
+    for n in (2000, 100):
+        ps = synth.make_problems(n, 346, 260, seed=4100 + n)
+        tr = Tracker(346, 260)
+        tr.add_frame(ps.frames[0])
+        sol0, nab0 = tr.optimize_batch(ps.problems, ps.events)
+        for _ in range(49):
+            sol, nab = tr.optimize_batch(ps.problems, ps.events)
+            assert sol.tobytes() == sol0.tobytes() and np.array_equal(nab, nab0)
+        tr.close()

@@ -12,7 +12,7 @@ import pytest
 
 from event_based_odomety_b200 import synth
 from event_based_odomety_b200.cabi import Tracker
-from tests._oracle import CpuTracker, load_oracle
+from tests._oracle import CpuTracker, load_oracle, load_ref
 
 POS_TOL_PX = 0.05
 ANGLE_TOL_DEG = 0.5
@@ -23,8 +23,19 @@ def _angle_diff_deg(a, b):
     return np.rad2deg(np.minimum(d, 2 * np.pi - d))
 
 
-def compare(stream, max_patches, n_frames=None, split=None, margin=None, stream_kernel=0):
-    cpu = CpuTracker(load_oracle(), stream.width, stream.height, max_patches)
+def checker(kind):
+    """'oracle' = the plain-C restatement; 'ref' = oracle/_ref/libebt_ref.so, the reference's own
+    Patch + Optimizer + vendored Ceres compiled unmodified (travels to the GPU box prebuilt)."""
+    if kind == "ref":
+        lib = load_ref()
+        if lib is None:
+            pytest.skip("oracle/_ref/libebt_ref.so is not built here")
+        return lib
+    return load_oracle()
+
+
+def compare(stream, max_patches, n_frames=None, split=None, margin=None, stream_kernel=0, against="oracle"):
+    cpu = CpuTracker(checker(against), stream.width, stream.height, max_patches)
     gpu = Tracker(stream.width, stream.height, max_patches)
     if margin is not None:
         gpu.set_prefilter_margin(margin)
@@ -61,8 +72,12 @@ def check_equal(cpu, gpu, n_cpu):
     assert np.array_equal(rc["lost"] != 0, rg["lost"] != 0)
     dpos = np.hypot(rc["x"] - rg["x"], rc["y"] - rg["y"])
     dang = _angle_diff_deg(rc["flow_dir"], rg["flow_dir"])
-    same = ((rc["n_successful"] == rg["n_successful"]) & (rc["n_unsuccessful"] == rg["n_unsuccessful"])
-            & (rc["termination"] == rg["termination"]))
+    if (rc["n_successful"] >= 0).all():
+        same = ((rc["n_successful"] == rg["n_successful"]) & (rc["n_unsuccessful"] == rg["n_unsuccessful"])
+                & (rc["termination"] == rg["termination"]))
+    else:
+        same = np.ones(len(rc), bool)  # the reference build reports final costs only, not Ceres' iteration counts
+    assert np.abs(rc["final_cost"] - rg["final_cost"]).max() < 1e-6
     print(f"\n{n_cpu} optimisations: max dpos {dpos.max():.3e} px, max dangle {dang.max():.3e} deg, "
           f"same LM path {same.mean():.5f}, rejected steps seen {int(rc['n_unsuccessful'].sum())}")
     assert dpos.max() <= POS_TOL_PX and dang.max() <= ANGLE_TOL_DEG
@@ -73,7 +88,8 @@ def check_equal(cpu, gpu, n_cpu):
         for k in ("lost", "init", "num_of_events", "window_size", "n_optimizations", "n_trajectory",
                   "current_ts", "time_last_update", "init_time"):
             assert np.array_equal(tc[k], tg[k]), k
-        assert np.array_equal(tc["counter"], tg["counter"])
+        if (tc["counter"] >= 0).all():  # Patch::counter_ has no getter in the reference build
+            assert np.array_equal(tc["counter"], tg["counter"])
         if len(tc):
             assert np.abs(tc["rect_x"] - tg["rect_x"]).max() <= POS_TOL_PX
         for tid in tc["track_id"]:
@@ -88,6 +104,40 @@ def test_stream_c1_shape():
     """BASELINE.json configs[0]: DAVIS 240x180, <= 100 patches."""
     S = synth.make_stream(240, 180, 0.30, 500e3, seed=1001, max_corners=69)
     compare(S, 100)
+
+
+@pytest.mark.gpu
+def test_stream_c1_shape_against_the_reference_build():
+    """The same stream against oracle/_ref: the CUDA path meets the reference's own code, not only its port."""
+    S = synth.make_stream(240, 180, 0.30, 500e3, seed=1001, max_corners=69)
+    compare(S, 100, against="ref")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("stream_kernel", [0, 2])
+def test_stream_c2_shape_against_the_reference_build(stream_kernel):
+    S = synth.make_stream(346, 260, 0.10, 2e6, seed=1002, max_corners=500)
+    compare(S, 500, stream_kernel=stream_kernel, against="ref")
+
+
+@pytest.mark.gpu
+def test_stream_kernels_are_deterministic():
+    """Stand-in for racecheck (compute-sanitizer is closed on this pool): the hand-offs of the persistent-CTA
+    kernel are sequence numbers in shared memory, no barriers — a race would show up as run-to-run
+    differences.  The same c2 stream 12 times: bit-identical records every time."""
+    S = synth.make_stream(346, 260, 0.10, 2e6, seed=1002, max_corners=500)
+    first = None
+    for _ in range(12):
+        g = Tracker(S.width, S.height, 500)
+        g.set_stream_kernel(2)
+        synth.run_stream(g, S)
+        r = g.records().copy()
+        g.close()
+        if first is None:
+            first = r
+            assert len(first) > 1000
+        else:
+            assert first.tobytes() == r.tobytes()
 
 
 @pytest.mark.gpu
@@ -229,5 +279,53 @@ def test_stream_empty_and_tiny_pushes():
     rc, rg = cpu.records(), gpu.records()
     assert np.array_equal(rc["track_id"], rg["track_id"]) and np.array_equal(rc["event_index"], rg["event_index"])
     assert np.hypot(rc["x"] - rg["x"], rc["y"] - rg["y"]).max() <= POS_TOL_PX
+    cpu.close()
+    gpu.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("against", ["oracle", "ref"])
+def test_stream_more_than_64_live_template_frames(against):
+    """FeatureDetector::optimizers_ is an unbounded map (one gradient grid per frame that still has a
+    patch created at it).  150 frames, each creating one more long-lived patch, keep 150 template
+    grids alive at once (the first build capped them at 64); then events make the oldest, a middle
+    and the newest patches optimise against their own template frames."""
+    W, H, N = 240, 180, 150
+    rng = np.random.Generator(np.random.PCG64(404))
+    base = synth.make_stream(W, H, 0.05, 100e3, seed=1404, max_corners=4).frames[0]
+    spots = [(20.0 + 14 * (i % 15), 20.0 + 14 * (i // 15)) for i in range(N)]
+    cpu = CpuTracker(checker(against), W, H, 200)
+    gpu = Tracker(W, H, 200)
+    gpu.set_stream_kernel(2)
+    ts = 0
+    for k in range(N):
+        frame = np.roll(base, k, axis=1).copy()
+        corners = np.array(spots[:k + 1], np.float64)
+        for t in (cpu, gpu):
+            t.new_frame_begin(frame, ts, corners)
+            ids, xy = t.get_uninit()
+            for tid, (x, y) in zip(ids, xy):
+                t.set_flow(tid, 1, x + 0.75, y - 0.5)
+            t.new_frame_end()
+        ts += 44065
+    tc, tg = cpu.tracks(), gpu.tracks()
+    assert len(tc) == len(tg) == N and np.array_equal(tc["track_id"], tg["track_id"])
+    assert not tc["lost"].any()
+    # events on the oldest, a middle and the newest initialised patches
+    ev = []
+    for j in (0, 70, N - 2):
+        cx, cy = spots[j]
+        n = 400
+        e = np.zeros(n, synth.EVENT)
+        e["x"] = np.clip(np.rint(cx + rng.uniform(-12, 12, n)), 0, W - 1)
+        e["y"] = np.clip(np.rint(cy + rng.uniform(-12, 12, n)), 0, H - 1)
+        e["polarity"] = rng.choice(np.array([-1, 1], np.int8), n)
+        ev.append(e)
+    ev = np.concatenate(ev)
+    ev = ev[rng.permutation(len(ev))]
+    ev["t_us"] = ts + np.arange(len(ev))
+    n_cpu, n_gpu = cpu.push_events(ev), gpu.push_events(ev)
+    assert n_cpu == n_gpu and n_cpu >= 9
+    check_equal(cpu, gpu, n_cpu)
     cpu.close()
     gpu.close()

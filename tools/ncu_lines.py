@@ -23,9 +23,13 @@ LIB = os.path.join(ROOT, "event_based_odomety_b200", "libebt_cuda.so")
 
 # section name -> functions whose bodies belong to it
 SECTIONS = collections.OrderedDict([
-    ("pixel pass (eval_pixels, bicubic taps, Jacobian sums)", ["cr_weights", "sample_taps", "eval_pixels", "pixel_service"]),
+    ("pixel pass (eval_pixels, bicubic taps, Jacobian sums)", ["cr_weights", "sample_taps", "sample_taps_tile", "eval_pixels", "pixel_service", "sb_serve"]),
     ("warp butterfly + block reductions", ["butterfly_slot", "Butterfly", "block_sum", "warp_sum", "red_total"]),
     ("pixel warps waiting for the next request (lm_worker, barriers)", ["lm_worker", "handshake", "partials_arrive", "partials_wait"]),
+    ("hand-off by sequence numbers: leaders posting / polling for completion (sb_post, wait_partials)", ["sb_post", "wait_partials", "ld_volatile_u32"]),
+    ("pixel-warp jobs of the multi-stream kernel: integration, normalisation + tile staging, window-size sum (mq_serve)", ["mq_serve", "num_events_term"]),
+    ("leader: per-optimisation scalar work of the multi-stream kernel (mq_optimize, mq_update_num_of_events)", ["mq_optimize", "mq_update_num_of_events"]),
+    ("multi-stream kernel body: pixel-warp polling loop, work queue, candidate walk, ring, state, records (track_multi_kernel)", ["track_multi_kernel", "mq_load_segment"]),
     ("leader: evaluation hand-off + totals + finalisation (leader_eval, post_request)", ["leader_eval", "post_request", "huber"]),
     ("leader: trust-region step (lm_solve, solve4, plus5, scale_system, rcp/rsqrt/sincos)",
      ["lm_solve", "solve4", "plus5", "scale_system", "rcp_fast", "rsqrt_fast", "sqrt_fast", "sincos_fast", "inv_len",
