@@ -149,6 +149,13 @@ struct ebt_ctx
 	cudaEvent_t join_event = nullptr;  // orders this context's own stream before a multi-stream launch
 	int shard_index = 0, shard_count = 1;  // ebt_set_shard: this context tracks track ids = index (mod count)
 	double opt_per_event = 0.25;       // optimisations per stream event of the last piece (bounds the next piece)
+	// ebt_replay: second CUDA stream, ping-pong device buffers and pinned staging of the pipelined event upload
+	cudaStream_t copy_stream = nullptr;
+	cudaEvent_t uploaded[2] = {nullptr, nullptr};
+	cudaEvent_t chunk_done[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+	ebt_event* d_replay[2] = {nullptr, nullptr};
+	ebt_event* h_replay[2] = {nullptr, nullptr};
+	size_t replay_cap = 0;
 	unsigned char* arch_stage = nullptr;  // pinned: products of the patches archived at a frame
 	size_t arch_stage_cap = 0;
 	size_t pending_records = 0;        // records on their way into rec_stage
@@ -530,6 +537,15 @@ int ebt_destroy(ebt_ctx* ctx)
 	cudaFreeHost(ctx->h_order);
 	cudaFreeHost(ctx->h_stage);
 	cudaFreeHost(ctx->arch_stage);
+	for (int i = 0; i < 2; ++i)
+	{
+		cudaFree(ctx->d_replay[i]);
+		cudaFreeHost(ctx->h_replay[i]);
+		if (ctx->uploaded[i]) cudaEventDestroy(ctx->uploaded[i]);
+		for (int j = 0; j < 2; ++j)
+			if (ctx->chunk_done[i][j]) cudaEventDestroy(ctx->chunk_done[i][j]);
+	}
+	if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
 	cudaFreeHost(ctx->rec_stage);
 	cudaFreeHost(ctx->nrec_stage);
 	cudaFree(ctx->d_text);
@@ -2493,6 +2509,69 @@ int ebt_parse_events_text(ebt_ctx* ctx, const char* text, size_t len, int final_
 // tools::Replayer::next (tools/replayer/src/replayer.cpp:56-98) over in-memory
 // samples: an event is delivered while its timestamp is < the next image's,
 // otherwise the image; replay ends when either runs out (finished(), :40-43).
+//
+// The whole recording is known here, so the event upload is pipelined (SURVEY 8f n2,
+// "chunked async H2D"): while the stream kernel of batch k runs on the context's
+// stream, batch k + 1 travels host -> pinned staging -> device in 4 MiB chunks on a
+// second CUDA stream (ping-pong device buffers, one CUDA event per batch orders the
+// kernel behind its own upload).  Results equal ebt_push_events + ebt_new_image.
+namespace
+{
+constexpr int64_t kReplayChunk = int64_t(1) << 18;  // events per H2D chunk (4 MiB)
+
+int replayBuffers(ebt_ctx* ctx, int64_t max_batch)
+{
+	if (!ctx->copy_stream)
+	{
+		CU(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+		for (int i = 0; i < 2; ++i) CU(cudaEventCreateWithFlags(&ctx->uploaded[i], cudaEventDisableTiming));
+	}
+	if (static_cast<size_t>(max_batch) > ctx->replay_cap)
+	{
+		CU(cudaStreamSynchronize(ctx->copy_stream));
+		CU(cudaStreamSynchronize(ctx->stream));
+		const size_t cap = static_cast<size_t>(max_batch) + static_cast<size_t>(max_batch) / 8 + 1024;
+		for (int i = 0; i < 2; ++i)
+		{
+			cudaFree(ctx->d_replay[i]);
+			ctx->d_replay[i] = nullptr;
+			cudaFreeHost(ctx->h_replay[i]);
+			ctx->h_replay[i] = nullptr;
+		}
+		ctx->replay_cap = 0;
+		for (int i = 0; i < 2; ++i)
+		{
+			CU(cudaMalloc(&ctx->d_replay[i], cap * sizeof(ebt_event)));
+			CU(cudaHostAlloc(&ctx->h_replay[i], static_cast<size_t>(2 * kReplayChunk) * sizeof(ebt_event), cudaHostAllocDefault));
+		}
+		ctx->replay_cap = cap;
+	}
+	return EBT_OK;
+}
+
+// host events [lo, hi) -> device buffer `slot`, chunk by chunk on the copy stream; the
+// pinned staging of a slot holds two chunks, so the host copy of a chunk overlaps the
+// DMA of the one before it
+int stageBatch(ebt_ctx* ctx, int slot, const ebt_event* events, int64_t lo, int64_t hi)
+{
+	int half = 0;
+	for (int64_t at = lo; at < hi; at += kReplayChunk, half ^= 1)
+	{
+		const int64_t m = std::min(kReplayChunk, hi - at);
+		ebt_event* stage = ctx->h_replay[slot] + static_cast<size_t>(half) * kReplayChunk;
+		// this half's previous DMA (two chunks ago) must have left the staging buffer
+		if (at - lo >= 2 * kReplayChunk) CU(cudaEventSynchronize(ctx->chunk_done[slot][half]));
+		std::memcpy(stage, events + at, static_cast<size_t>(m) * sizeof(ebt_event));
+		CU(cudaMemcpyAsync(ctx->d_replay[slot] + (at - lo), stage, static_cast<size_t>(m) * sizeof(ebt_event),
+						   cudaMemcpyHostToDevice, ctx->copy_stream));
+		if (!ctx->chunk_done[slot][half]) CU(cudaEventCreateWithFlags(&ctx->chunk_done[slot][half], cudaEventDisableTiming));
+		CU(cudaEventRecord(ctx->chunk_done[slot][half], ctx->copy_stream));
+	}
+	CU(cudaEventRecord(ctx->uploaded[slot], ctx->copy_stream));
+	return EBT_OK;
+}
+}  // namespace
+
 int ebt_replay(ebt_ctx* ctx, const ebt_event* events, int64_t n_events, const uint8_t* frames,
 			   const int64_t* frame_ts, int n_frames, int64_t* n_events_delivered, int64_t* n_optimizations)
 {
@@ -2500,12 +2579,14 @@ int ebt_replay(ebt_ctx* ctx, const ebt_event* events, int64_t n_events, const ui
 		return fail(ctx, EBT_E_INVALID, "ebt_replay: bad argument");
 	if (n_events_delivered) *n_events_delivered = 0;
 	if (n_optimizations) *n_optimizations = 0;
+	CU(cudaSetDevice(ctx->device));
 	const size_t npx = static_cast<size_t>(ctx->prm.width) * ctx->prm.height;
-	int64_t pos = 0, n_opt = 0;
-	for (int k = 0; k < n_frames && pos < n_events; ++k)
+	// the batch in front of every image: events strictly older than it
+	std::vector<int64_t> cut(static_cast<size_t>(n_frames) + 1, 0);
+	int64_t max_batch = 0;
+	for (int k = 0; k < n_frames; ++k)
 	{
-		// events strictly older than image k
-		int64_t lo = pos, hi = n_events;
+		int64_t lo = cut[static_cast<size_t>(k)], hi = n_events;
 		while (lo < hi)
 		{
 			const int64_t mid = lo + (hi - lo) / 2;
@@ -2514,18 +2595,51 @@ int ebt_replay(ebt_ctx* ctx, const ebt_event* events, int64_t n_events, const ui
 			else
 				hi = mid;
 		}
-		if (lo > pos)
+		cut[static_cast<size_t>(k) + 1] = lo;
+		max_batch = std::max(max_batch, lo - cut[static_cast<size_t>(k)]);
+	}
+	if (max_batch > 0)
+	{
+		const int rc = replayBuffers(ctx, max_batch);
+		if (rc != EBT_OK) return rc;
+	}
+	int64_t pos = 0, n_opt = 0;
+	int staged = -1;  // batch (image index) already on its way to the device
+	auto stage = [&](int k) -> int {
+		if (k >= n_frames || cut[static_cast<size_t>(k) + 1] <= cut[static_cast<size_t>(k)]) return EBT_OK;
+		staged = k;
+		return stageBatch(ctx, k & 1, events, cut[static_cast<size_t>(k)], cut[static_cast<size_t>(k) + 1]);
+	};
+	for (int k = 0; k < n_frames && pos < n_events; ++k)
+	{
+		const int64_t lo = cut[static_cast<size_t>(k)], hi = cut[static_cast<size_t>(k) + 1];
+		if (hi > lo)
 		{
+			if (staged != k)
+			{
+				const int rc = stage(k);
+				if (rc != EBT_OK) return rc;
+			}
+			CU(cudaStreamWaitEvent(ctx->stream, ctx->uploaded[k & 1], 0));
+			// the next batch travels while this one is tracked
+			int next = k + 1;
+			while (next < n_frames && cut[static_cast<size_t>(next) + 1] <= cut[static_cast<size_t>(next)]) ++next;
+			if (next < n_frames && (next & 1) != (k & 1))
+			{
+				const int rc = stage(next);
+				if (rc != EBT_OK) return rc;
+			}
 			int64_t m = 0;
-			const int rc = ebt_push_events(ctx, events + pos, lo - pos, &m);
+			const int rc = runPieces(ctx, ctx->d_replay[k & 1], hi - lo, &m);
 			n_opt += m;
 			if (rc != EBT_OK) return rc;
-			pos = lo;
+			pos = hi;
 		}
 		if (pos >= n_events) break;  // hasEvents_ is false before the image is reached
 		const int rc = ebt_new_image(ctx, frames + static_cast<size_t>(k) * npx, frame_ts[k]);
 		if (rc != EBT_OK) return rc;
 	}
+	if (ctx->copy_stream) CU(cudaStreamSynchronize(ctx->copy_stream));
 	if (n_events_delivered) *n_events_delivered = pos;
 	if (n_optimizations) *n_optimizations = n_opt;
 	return EBT_OK;

@@ -1951,8 +1951,8 @@ track_batch_kernel(DevPatch* __restrict__ patches, int n_patches, const int* __r
 //
 // Hand-off without barriers: a leader writes its request, then bumps
 // slot.req_seq; every pixel warp serves every job (its 32 of the 128 pixel
-// threads' share) in the order it discovers them and bumps slot.done_cnt; the
-// leader spins until done_cnt == SB_PIXW * req_seq.  A leader has at most one job
+// threads' share) in the order it discovers them and arrives on the slot's mbarrier; the
+// leader waits for that phase (mbarrier.try_wait).  A leader has at most one job
 // in flight, so the pixel warps need not agree on an order.
 // --------------------------------------------------------------------------
 #ifndef SB_LEADERS
@@ -1991,13 +1991,42 @@ struct __align__(16) SlotShared
 	double tot[20];
 	EvalCtx ctx;
 	int req_kind;             // 1 cost-only pass, 2 cost + Jacobian pass, 3 stage the tile, 4 leader has finished
+	unsigned long long done_bar;  // mbarrier: SB_PIXW pixel-warp arrivals complete a job
 	unsigned req_seq;         // jobs posted so far (written by the leader)
-	unsigned done_cnt;        // pixel-warp completions (SB_PIXW per job)
 	unsigned seq_local;       // leader's own copy of req_seq
 	long long t_last;         // EBT_PHASE_CLOCKS only
 };
 
 __device__ __forceinline__ unsigned ld_volatile_u32(const unsigned* p) { return *(const volatile unsigned*)p; }
+
+// Completion side of the hand-off: an mbarrier per slot (sm_90+ hardware barrier in shared
+// memory).  Each of the SB_PIXW pixel warps arrives once per job; the leader waits for the
+// phase of its job with mbarrier.try_wait, which parks the warp in hardware instead of
+// spinning on a shared-memory word (the polls took 12 % of the issued instructions of
+// the spinning version, profiles/r2_summary.md).  A leader has one job in flight and
+// observes every phase, so the phase parity is (jobs posted - 1) & 1.
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count)
+{
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar)
+{
+	asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity)
+{
+	asm volatile(
+		"{\n"
+		".reg .pred P1;\n"
+		"EBT_MBAR_WAIT:\n"
+		"mbarrier.try_wait.parity.acquire.cta.shared::cta.b64 P1, [%0], %1;\n"
+		"@P1 bra EBT_MBAR_DONE;\n"
+		"bra EBT_MBAR_WAIT;\n"
+		"EBT_MBAR_DONE:\n"
+		"}" ::"r"((unsigned)__cvta_generic_to_shared(bar)),
+		"r"(parity)
+		: "memory");
+}
 
 template <class SL>
 __device__ __forceinline__ void sb_post(SL& S)
@@ -2013,9 +2042,7 @@ __device__ __forceinline__ void sb_post(SL& S)
 template <class SL, class = decltype(SL::is_slot)>
 __device__ __forceinline__ void wait_partials(SL& S)
 {
-	const unsigned want = S.seq_local * SB_PIXW;
-	while (ld_volatile_u32(&S.done_cnt) != want) SB_BACKOFF();
-	__threadfence_block();
+	mbar_wait(&S.done_bar, (S.seq_local - 1u) & 1u);
 	__syncwarp();
 }
 template <class SL, class = decltype(SL::is_slot)>
@@ -2226,7 +2253,7 @@ optimize_batch_shared_kernel(const ebt_problem* __restrict__ problems, int n_pro
 	if (threadIdx.x < SB_LEADERS)
 	{
 		slots[threadIdx.x].req_seq = 0;
-		slots[threadIdx.x].done_cnt = 0;
+		mbar_init(&slots[threadIdx.x].done_bar, SB_PIXW);
 		slots[threadIdx.x].seq_local = 0;
 		slots[threadIdx.x].t_last = 0;
 	}
@@ -2266,7 +2293,7 @@ optimize_batch_shared_kernel(const ebt_problem* __restrict__ problems, int n_pro
 			sb_serve(S, kind, ptid);
 			__threadfence_block();
 			__syncwarp();
-			if (lane == 0) atomicAdd(&S.done_cnt, 1u);
+			if (lane == 0) mbar_arrive(&S.done_bar);
 		}
 		if (idle) SB_BACKOFF();
 	}
@@ -2312,8 +2339,9 @@ struct __align__(16) StreamSlot
 	const double2* job_grid;  // job 6: the latest frame's grid
 	int job_i[4];             // integer job arguments (5: window tail, size; 6: x0, y0)
 	int redi[SB_PIXW];        // job 5: per-warp sum of squares of the integer patch
+	unsigned long long done_bar;  // mbarrier: SB_PIXW pixel-warp arrivals complete a job
 	int req_kind;
-	unsigned req_seq, done_cnt, seq_local;
+	unsigned req_seq, seq_local;
 	long long t_last;
 };
 
@@ -2558,7 +2586,7 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 	if (threadIdx.x < SB_LEADERS)
 	{
 		slots[threadIdx.x].req_seq = 0;
-		slots[threadIdx.x].done_cnt = 0;
+		mbar_init(&slots[threadIdx.x].done_bar, SB_PIXW);
 		slots[threadIdx.x].seq_local = 0;
 		slots[threadIdx.x].t_last = 0;
 	}
@@ -2594,7 +2622,7 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 					mq_serve(S, kind, ptid);
 				__threadfence_block();
 				__syncwarp();
-				if (lane == 0) atomicAdd(&S.done_cnt, 1u);
+				if (lane == 0) mbar_arrive(&S.done_bar);
 			}
 			if (idle) SB_BACKOFF();
 		}
