@@ -1528,11 +1528,21 @@ __device__ __forceinline__ void store_state(const FeatState& st, DevPatch& p)
 	p.n_traj = st.n_traj;
 }
 
+__device__ void write_record_at(ebt_opt_record* records, unsigned long long slot, unsigned long long cap,
+								const FeatState& st, int track_id, const LmSummary& S, long long event_index);
+
 __device__ void write_record(ebt_opt_record* records, unsigned long long* n_records,
 							 unsigned long long cap, const FeatState& st, int track_id,
 							 const LmSummary& S, long long event_index)
 {
-	const unsigned long long slot = atomicAdd(n_records, 1ull);
+	write_record_at(records, atomicAdd(n_records, 1ull), cap, st, track_id, S, event_index);
+}
+
+// `slot`: the record's place in the push's buffer, reserved with one atomic (by the caller: the
+// multi-stream kernel reserves it BEFORE the solve, so the atomic's round trip hides behind it)
+__device__ void write_record_at(ebt_opt_record* records, unsigned long long slot, unsigned long long cap,
+								const FeatState& st, int track_id, const LmSummary& S, long long event_index)
+{
 	if (slot >= cap) return;
 	ebt_opt_record r;
 	r.track_id = track_id;
@@ -2320,6 +2330,11 @@ optimize_batch_shared_kernel(const ebt_problem* __restrict__ problems, int n_pro
 // While one leader walks, or runs its scalar step, the pixel warps serve the other.
 // Candidate walk: 128 mask words (4096 stream events) per segment, one 16-byte
 // load per lane, the next segment's words already in flight.
+// Shape (measured, profiles/r2_variants.md): two leaders per four pixel warps at 168
+// registers, two CTAs per SM.  Three leaders per pixel set — uniformly at 144 registers,
+// or with setmaxnreg moving registers from the leader warpgroup (88-112) to the pixel
+// warpgroup (144-168) — were 25-40 % slower: the leaders' scalar trust-region chain is
+// the critical path and it is the part that cannot give registers away.
 // --------------------------------------------------------------------------
 #define MQ_SEG_WORDS 128
 struct __align__(16) StreamSlot
@@ -2337,6 +2352,17 @@ struct __align__(16) StreamSlot
 	EvalCtx ctx;
 	unsigned short cand[MQ_SEG_WORDS * 32];
 	const double2* job_grid;  // job 6: the latest frame's grid
+	// of the feature's stream, read once per feature instead of once per optimisation
+	const double2* const* grids;
+	ebt_opt_record* records;
+	unsigned long long* n_records;
+	unsigned long long record_cap;
+	long long event_base;
+	int latest;
+	int pad_;
+	// the two newest entries of Patch::trajectory_ (DevPatch::traj_*), written back at the end
+	double traj_x[2], traj_y[2];
+	long long traj_ts[2];
 	int job_i[4];             // integer job arguments (5: window tail, size; 6: x0, y0)
 	int redi[SB_PIXW];        // job 5: per-warp sum of squares of the integer patch
 	unsigned long long done_bar;  // mbarrier: SB_PIXW pixel-warp arrivals complete a job
@@ -2653,6 +2679,21 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 		int* gnabla = D.nablas + (size_t)gp.store_slot * NPIX;
 		for (int k = lane; k < st.size; k += 32) S.ring[k] = gring[(st.tail + k) & RMASK];
 		if (lane < EBT_COST_HISTORY) S.costs[lane] = gp.costs[lane];
+		if (lane < 2)
+		{
+			S.traj_x[lane] = gp.traj_x[lane];
+			S.traj_y[lane] = gp.traj_y[lane];
+			S.traj_ts[lane] = gp.traj_ts[lane];
+		}
+		if (lane == 2)
+		{
+			S.grids = D.grids;
+			S.records = D.records;
+			S.n_records = D.n_records;
+			S.record_cap = D.record_cap;
+			S.event_base = D.event_base;
+			S.latest = D.latest;
+		}
 		st.tail = 0;
 		__syncwarp();
 		const ebt_event* events = D.events;
@@ -2670,7 +2711,7 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 		uint4 cur = mq_load_segment(row, seg, wpr, lane);
 		while (!st.lost && seg < n_words)
 		{
-			WALK_ADD(lane == 0, 7, 1);
+			WALK_T(ws0);
 			// the next segment's words travel while this one is walked
 			const uint4 nxt = mq_load_segment(row, seg + MQ_SEG_WORDS, wpr, lane);
 			unsigned w4[4] = {cur.x, cur.y, cur.z, cur.w};
@@ -2711,6 +2752,8 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 				}
 			}
 			__syncwarp();
+			WALK_T(ws1);
+			WALK_ADD(lane == 0, 3, ws1 - ws0);  // diagnostic builds: slot 3 = mask wait + expansion
 			bool restart = false;
 			// candidate records: chunk c + 1 is loaded before chunk c is walked
 			uint4 raw_next = make_uint4(0, 0, 0, 0);
@@ -2722,11 +2765,19 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 				if (cbase + 32 + lane < n_c) raw_next = __ldg(ev4 + ((seg << 5) + S.cand[cbase + 32 + lane]));
 				const int ex = (int)(raw.z & 0xffffu), ey = (int)(raw.z >> 16);
 				int resume = 0;
+				WALK_T(wc0);
 				while (resume < chunk_len)
 				{
 					const bool live = lane >= resume && lane < chunk_len;
 					const bool inside = live && in_rect(st.rx, st.ry, ex, ey);
 					const unsigned bal = __ballot_sync(0xffffffffu, inside);
+#ifdef EBT_WALK_CLOCKS
+					if (resume == 0)
+					{
+						WALK_T(wc1);
+						WALK_ADD(lane == 0, 7, wc1 - wc0);  // diagnostic builds: slot 7 = wait for the chunk's records + first test
+					}
+#endif
 					const int total = __popc(bal);
 					const int rank = __popc(bal & ((1u << lane) - 1u)) + 1;  // if inside
 					const int need = window_need(st, P);
@@ -2750,29 +2801,29 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 					// ---- one Optimizer::optimize at stream event `at` and the bookkeeping around it
 					LmSummary L;
 					WALK_T(w0);
-					mq_optimize(S, st, D.grids[st.frame_slot], P, L);
+					// the record's slot is reserved now: the atomic's round trip hides behind the solve
+					unsigned long long rec_slot = 0;
+					if (lane == 0) rec_slot = atomicAdd(S.n_records, 1ull);
+					mq_optimize(S, st, S.grids[st.frame_slot], P, L);
 					WALK_T(w1);
 					WALK_ADD(lane == 0, 1, w1 - w0);
 					WALK_ADD(lane == 0, 5, 1);
 					if (!L.filtered && lane == 0)
 					{
 						// Patch::addTrajectoryPosition: the two newest trajectory entries
-						const double lx = st.rx + (SIDE - 1) / 2., ly = st.ry + (SIDE - 1) / 2.;
-						gp.traj_x[0] = gp.traj_x[1]; gp.traj_y[0] = gp.traj_y[1]; gp.traj_ts[0] = gp.traj_ts[1];
-						gp.traj_x[1] = lx; gp.traj_y[1] = ly; gp.traj_ts[1] = st.cur_ts;
+						S.traj_x[0] = S.traj_x[1]; S.traj_y[0] = S.traj_y[1]; S.traj_ts[0] = S.traj_ts[1];
+						S.traj_x[1] = st.rx + (SIDE - 1) / 2.; S.traj_y[1] = st.ry + (SIDE - 1) / 2.; S.traj_ts[1] = st.cur_ts;
 					}
 					WALK_T(w2);
-					mq_update_num_of_events(S, st, D.grids[D.latest], P);
+					mq_update_num_of_events(S, st, S.grids[S.latest], P);
 					WALK_T(w3);
 					WALK_ADD(lane == 0, 6, w3 - w2);
-					if (lane == 0) write_record(D.records, D.n_records, D.record_cap, st, track_id, L, D.event_base + at);
+					if (lane == 0) write_record_at(S.records, rec_slot, S.record_cap, st, track_id, L, S.event_base + at);
 					++n_opt;
 					start = at + 1;
 					if (!st.lost && (fabs(st.rx - srx) > margin || fabs(st.ry - sry) > margin))
 					{
 						// rebuild the mask row from `start` on around the rect's current position
-						WALK_T(w4);
-						WALK_ADD(lane == 0, 4, 1);
 						const int4 bb = candidate_bounds(st.rx, st.ry, margin);
 						const unsigned* ev32 = reinterpret_cast<const unsigned*>(events);
 						// eight mask words per trip: eight independent loads in flight per lane
@@ -2797,8 +2848,6 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 							if (lane < 8 && w0 + lane < n_words) __stcg(row + w0 + lane, mine);
 						}
 						__syncwarp();
-						WALK_T(w5);
-						WALK_ADD(lane == 0, 3, w5 - w4);
 						srx = st.rx;
 						sry = st.ry;
 						restart = true;
@@ -2809,6 +2858,8 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 				}
 			}
 			__syncwarp();
+			WALK_T(ws2);
+			WALK_ADD(lane == 0, 4, ws2 - ws1);  // diagnostic builds: slot 4 = chunk phase incl. optimisations
 			if (pre)
 			{
 				pre = false;
@@ -2830,6 +2881,12 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 		if (n_opt > 0)
 			for (int i = lane; i < NPIX; i += 32) gnabla[i] = S.nabla[i];
 		if (lane < EBT_COST_HISTORY) gp.costs[lane] = S.costs[lane];
+		if (lane < 2 && n_opt > 0)
+		{
+			gp.traj_x[lane] = S.traj_x[lane];
+			gp.traj_y[lane] = S.traj_y[lane];
+			gp.traj_ts[lane] = S.traj_ts[lane];
+		}
 		st.tail = 0;
 		if (lane == 0)
 		{

@@ -58,6 +58,13 @@ for WL in sys.argv[1:] or ["c2", "c3"]:
                                      walk_and_rest=(c[0] - c[1] - c[3] - c[6]) / nopt),
                  rebuilds_per_opt=c[4] / nopt, segments_per_opt=c[7] / nopt,
                  cycles_per_rebuild=c[3] / max(c[4], 1))
+        if mode == 2:  # the multi-stream kernel reuses slots 3 / 4: mask wait + expansion, chunk phase
+            r["cycles_per_opt"]["expand"] = c[3] / nopt
+            r["cycles_per_opt"]["chunks_without_optimise"] = (c[4] - c[1] - c[6]) / nopt
+            r["cycles_per_opt"]["feature_entry_exit"] = (c[0] - c[3] - c[4]) / nopt
+            r["cycles_per_opt"]["chunk_record_wait_and_first_test"] = c[7] / nopt
+            del r["segments_per_opt"]
+            del r["cycles_per_opt"]["rebuild"], r["rebuilds_per_opt"], r["cycles_per_rebuild"]
         print(json.dumps(r))
         out.append(r)
         tr.close()
