@@ -11,7 +11,9 @@
 #include <cmath>
 #include <cstddef>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -158,8 +160,10 @@ struct ebt_ctx
 	size_t replay_cap = 0;
 	unsigned char* arch_stage = nullptr;  // pinned: products of the patches archived at a frame
 	size_t arch_stage_cap = 0;
-	size_t pending_records = 0;        // records on their way into rec_stage
-	bool pending_overflow = false;
+	// the records of the last push travel device -> pinned staging while the host goes on with the
+	// next image; finishRecords appends them to `records` (their range is already in the journal)
+	size_t pending_records = 0;
+	cudaEvent_t rec_event = nullptr;  // recorded behind the copy (the stream may belong to another context)
 	std::vector<ebt_opt_record> records;
 	size_t records_sorted = 0;  // records[0 .. records_sorted) are in reference order
 	std::vector<size_t> record_batches;  // end offset of every push behind records_sorted
@@ -340,8 +344,20 @@ void addTraj(ebt_ctx* c, DevPatch& p)
 	p.traj_ts[1] = p.cur_ts;
 }
 
+// Wait for the records of the last push and put them into their reserved place in c->records.
+// Everything that reads c->records or reuses the staging buffer calls this first.
+void finishRecords(ebt_ctx* c)
+{
+	if (c->pending_records == 0) return;
+	cudaEventSynchronize(c->rec_event);
+	// nothing else appends to c->records, so the range the journal already names starts at its end
+	c->records.insert(c->records.end(), c->rec_stage, c->rec_stage + c->pending_records);
+	c->pending_records = 0;
+}
+
 void materialise(ebt_ctx* c)
 {
+	finishRecords(c);
 	if (c->all_tracks.size() < static_cast<size_t>(c->next_track_id))
 		c->all_tracks.resize(static_cast<size_t>(c->next_track_id));
 	for (const auto& e : c->journal)
@@ -437,6 +453,7 @@ int downloadPatches(ebt_ctx* ctx)
 // increasing ids) and erases in place, so position order is track-id order.
 void sortRecords(ebt_ctx* ctx)
 {
+	finishRecords(ctx);
 	size_t lo = ctx->records_sorted;
 	for (size_t hi : ctx->record_batches)
 	{
@@ -508,6 +525,8 @@ int ebt_destroy(ebt_ctx* ctx)
 {
 	if (!ctx) return EBT_E_INVALID;
 	cudaSetDevice(ctx->device);
+	finishRecords(ctx);
+	if (ctx->rec_event) cudaEventDestroy(ctx->rec_event);
 	for (auto& f : ctx->frames) cudaFree(f.grid);
 	cudaFree(ctx->d_frame_ptrs);
 	cudaFree(ctx->d_patches);
@@ -707,6 +726,7 @@ int ebt_reset(ebt_ctx* ctx)
 	ctx->arch_mc.clear();
 	ctx->arch_pred.clear();
 	ctx->arch_cost.clear();
+	finishRecords(ctx);
 	ctx->records.clear();
 	ctx->records_sorted = 0;
 	ctx->record_batches.clear();
@@ -1260,36 +1280,24 @@ static int collectPush(ebt_ctx* ctx, int64_t n, cudaStream_t on, int64_t* n_opt,
 			CU(cudaHostAlloc(&ctx->rec_stage, cap * sizeof(ebt_opt_record), cudaHostAllocDefault));
 			ctx->rec_stage_cap = cap;
 		}
+		// The copy is queued and NOT waited for: it travels while the host handles the next image
+		// (finishRecords).  Its place in the record list and in the journal is reserved now, so the
+		// order of trajectory entries (image samples vs optimisations) stays the reference's.
+		// A feature's records sit in the buffer in the order it produced them, which is all the
+		// per-track histories need (built lazily, materialise()); the global reference order is
+		// restored lazily too (sortRecords).
 		CU(cudaMemcpyAsync(ctx->rec_stage, ctx->d_records, got * sizeof(ebt_opt_record), cudaMemcpyDeviceToHost, on));
+		const size_t first = ctx->records.size();  // the previous push's records are in by now
+		ctx->record_batches.push_back(first + static_cast<size_t>(got));
+		ctx->journal.push_back({1, first, first + static_cast<size_t>(got)});
+		if (!ctx->rec_event) CU(cudaEventCreateWithFlags(&ctx->rec_event, cudaEventDisableTiming));
+		CU(cudaEventRecord(ctx->rec_event, on));
+		ctx->pending_records = static_cast<size_t>(got);
 	}
-	ctx->pending_records = got;
-	ctx->pending_overflow = nrec > got;
-	return EBT_OK;
-}
-
-// The records of collectPush have arrived (the caller synchronised `on`).
-static int appendRecords(ebt_ctx* ctx)
-{
-	const size_t got = ctx->pending_records;
-	ctx->pending_records = 0;
-	if (got > 0)
-	{
-		// A feature's records sit in the buffer in the order it produced them,
-		// which is all the per-track histories need (built lazily, materialise());
-		// the global reference order is restored lazily too (sortRecords).
-		const ebt_opt_record* recs = ctx->rec_stage;
-		const size_t first = ctx->records.size();
-		ctx->records.insert(ctx->records.end(), recs, recs + got);
-		ctx->record_batches.push_back(ctx->records.size());
-		ctx->journal.push_back({1, first, ctx->records.size()});
-	}
-	if (ctx->pending_overflow)
-	{
-		ctx->pending_overflow = false;
+	if (nrec > got)
 		return fail(ctx, EBT_E_CAPACITY,
 					"ebt_push_events: record_capacity exceeded; tracks are valid, records/trajectories of this push are "
 					"truncated (raise ebt_params::record_capacity)");
-	}
 	return EBT_OK;
 }
 
@@ -1297,6 +1305,8 @@ static int appendRecords(ebt_ctx* ctx)
 static int runStream(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t* n_opt)
 {
 	const int P = static_cast<int>(ctx->h.size());
+	// the kernel below rewrites the device record buffer: it must start behind the previous push's record copy
+	if (ctx->pending_records) CU(cudaStreamWaitEvent(ctx->stream, ctx->rec_event, 0));
 	{
 		const int rc = uploadPatches(ctx);
 		if (rc != EBT_OK) return rc;
@@ -1321,13 +1331,43 @@ static int runStream(ebt_ctx* ctx, const ebt_event* d_events, int64_t n, int64_t
 							  ctx->dp, ctx->d_records, ctx->d_nrec,
 							  static_cast<unsigned long long>(ctx->prm.record_capacity), ctx->stream));
 	toc(ctx, K_TRACK);
-	{
-		const int rc = collectPush(ctx, n, ctx->stream, n_opt, false);
-		if (rc != EBT_OK) return rc;
-	}
-	CU(cudaStreamSynchronize(ctx->stream));
-	return appendRecords(ctx);
+	finishRecords(ctx);  // host side of the previous push's records, while this push's kernel runs
+	return collectPush(ctx, n, ctx->stream, n_opt, false);
 }
+
+// EBT_HOST_PROFILE=1: where the host time of a multi-stream push goes (printed at exit; measurement only)
+namespace
+{
+struct HostProfile
+{
+	bool on = getenv("EBT_HOST_PROFILE") != nullptr;
+	double t[8] = {};
+	long calls = 0;
+	~HostProfile()
+	{
+		if (!on || !calls) return;
+		static const char* names[8] = {"prepare (upload, mask, load estimate)", "sort work + descriptors", "launch calls",
+									   "previous records -> host list", "wait for the kernel", "collect (state copy, record copy queued)",
+									   "", ""};
+		std::fprintf(stderr, "[ebt host profile] %ld pushes, ms per push:", calls);
+		for (int i = 0; i < 6; ++i) std::fprintf(stderr, "  %s %.3f;", names[i], t[i] / calls * 1e3);
+		std::fprintf(stderr, "\n");
+	}
+} g_host_profile;
+inline double nowSeconds()
+{
+	timespec ts;
+	clock_gettime(CLOCK_MONOTONIC, &ts);
+	return ts.tv_sec + ts.tv_nsec * 1e-9;
+}
+#define HP_MARK(k)                                      \
+	if (g_host_profile.on)                              \
+	{                                                   \
+		const double now_ = nowSeconds();               \
+		g_host_profile.t[k] += now_ - hp_t;             \
+		hp_t = now_;                                    \
+	}
+}  // namespace
 
 // One piece of S streams on the shared-pixel-warp kernel: one prefilter launch and
 // one stream-kernel launch for all of them, on ctxs[0]'s CUDA stream.
@@ -1335,6 +1375,8 @@ static int runMulti(ebt_ctx* const* ctxs, int S, const ebt_event* const* d_event
 {
 	ebt_ctx* ctx = ctxs[0];  // owner of the launch scratch and the CUDA stream used
 	cudaStream_t on = ctx->stream;
+	double hp_t = g_host_profile.on ? nowSeconds() : 0.0;
+	if (g_host_profile.on) g_host_profile.calls++;
 	size_t n_work = 0;
 	for (int i = 0; i < S; ++i) n_work += ctxs[i]->h.size();
 	if (static_cast<size_t>(S) > ctx->descs_cap)
@@ -1370,6 +1412,8 @@ static int runMulti(ebt_ctx* const* ctxs, int S, const ebt_event* const* d_event
 	for (int i = 0; i < S; ++i)
 	{
 		ebt_ctx* c = ctxs[i];
+		// the kernel below rewrites the device record buffers: it must start behind the previous push's copies
+		if (c->pending_records) CU(cudaStreamWaitEvent(on, c->rec_event, 0));
 		// work of this context still in flight on its own CUDA stream comes first
 		if (c != ctx)
 		{
@@ -1416,6 +1460,7 @@ static int runMulti(ebt_ctx* const* ctxs, int S, const ebt_event* const* d_event
 			ctx->work_load.push_back(c->load_est[static_cast<size_t>(f)]);
 		}
 	}
+	HP_MARK(0);
 	{
 		// heaviest first over all streams (stable: equal loads keep stream / list order)
 		std::vector<int>& idx = ctx->work_idx;
@@ -1428,6 +1473,7 @@ static int runMulti(ebt_ctx* const* ctxs, int S, const ebt_event* const* d_event
 	}
 	CU(cudaMemcpyAsync(ctx->d_descs, ctx->h_descs, static_cast<size_t>(S) * sizeof(StreamDesc), cudaMemcpyHostToDevice, on));
 	CU(cudaMemcpyAsync(ctx->d_work, ctx->h_work, n_work * sizeof(WorkItem), cudaMemcpyHostToDevice, on));
+	HP_MARK(1);
 	tic(ctx);
 	CU(ebt_launch_track_multi(ctx->d_descs, S, ctx->d_work, static_cast<int>(n_work), max_events, max_patches, ctx->dp,
 							  ctx->d_queue, on));
@@ -1438,27 +1484,23 @@ static int runMulti(ebt_ctx* const* ctxs, int S, const ebt_event* const* d_event
 		CU(cudaMemcpyAsync(c->nrec_stage, c->d_nrec, sizeof(unsigned long long), cudaMemcpyDeviceToHost, on));
 		CU(cudaMemcpyAsync(c->h_stage, c->d_patches, c->h.size() * sizeof(DevPatch), cudaMemcpyDeviceToHost, on));
 	}
+	HP_MARK(2);
+	// host side of the previous push's records, while this push's kernel runs
+	for (int i = 0; i < S; ++i) finishRecords(ctxs[i]);
+	HP_MARK(3);
 	CU(cudaStreamSynchronize(on));
+	HP_MARK(4);
+	int result = EBT_OK;
 	for (int i = 0; i < S; ++i)
 	{
 		const int rc = collectPush(ctxs[i], n[i], on, n_opt ? n_opt + i : nullptr, true);
 		if (rc != EBT_OK)
 		{
 			if (ctxs[i] != ctx) ctx->err = ctxs[i]->err;
-			return rc;
-		}
-	}
-	CU(cudaStreamSynchronize(on));
-	int result = EBT_OK;
-	for (int i = 0; i < S; ++i)
-	{
-		const int rc = appendRecords(ctxs[i]);
-		if (rc != EBT_OK)
-		{
-			if (ctxs[i] != ctx) ctx->err = ctxs[i]->err;
 			result = rc;
 		}
 	}
+	HP_MARK(5);
 	return result;
 }
 

@@ -338,6 +338,129 @@ __device__ __forceinline__ void sample_taps_tile(const double2* base, const doub
 	}
 }
 
+#ifdef EBT_FP32_SAMPLING
+// MEASUREMENT-ONLY variant (never the shipped build): the bicubic
+// sampling, u and du of a pixel and the per-thread partial sums in FP32 (tile staged as float2),
+// the reduction from the per-thread partials on, the in-image decisions and everything on the
+// leader in FP64.  profiles/r2_variants.md reports its flip rate against the oracle and its speed.
+template <bool DERIV>
+__device__ __forceinline__ void cr_weights_f(float t, float (&w)[4], float (&d)[4])
+{
+	const float t2 = t * t, t3 = t2 * t;
+	w[0] = -t3 + 2.0f * t2 - t;
+	w[1] = 3.0f * t3 - 5.0f * t2 + 2.0f;
+	w[2] = -3.0f * t3 + 4.0f * t2 + t;
+	w[3] = t3 - t2;
+	if (DERIV)
+	{
+		d[0] = -3.0f * t2 + 4.0f * t - 1.0f;
+		d[1] = 9.0f * t2 - 10.0f * t;
+		d[2] = -9.0f * t2 + 8.0f * t + 1.0f;
+		d[3] = 3.0f * t2 - 2.0f * t;
+	}
+}
+// stores a template-grid texel into the staged tile (float2 in this variant)
+__device__ __forceinline__ void stage_texel(double2* tile, int idx, double2 g)
+{
+	reinterpret_cast<float2*>(tile)[idx] = make_float2((float)g.x, (float)g.y);
+}
+template <bool JAC, int STRIDE>
+__device__ __forceinline__ void eval_pixels_f32(const double2* __restrict__ grid, int W, int H, const double (&x)[5],
+												 double vx, double vy, double tlx, double tly, const double* m, int tid,
+												 double (&acc)[JAC ? 20 : 2], const double2* tile, int r0, int c0,
+												 bool staged)
+{
+	const double cs = x[0], sn = x[1], tx = x[2], ty = x[3];
+	const float csf = (float)cs, snf = (float)sn, vxf = (float)vx, vyf = (float)vy;
+	const float2* tf = reinterpret_cast<const float2*>(tile);
+	float a[JAC ? 20 : 2];
+#pragma unroll
+	for (int k = 0; k < (JAC ? 20 : 2); ++k) a[k] = 0.0f;
+#pragma unroll kPixUnroll
+	for (int i = tid; i < NPIX; i += STRIDE)
+	{
+		const int yy = i / SIDE, xx = i - yy * SIDE;
+		const double px = xx + tlx, py = yy + tly;
+		const double wx = cs * px + -sn * py + tx;
+		const double wy = sn * px + cs * py + ty;
+		if (wx >= W || wy >= H || wx < 0.0 || wy < 0.0) continue;  // decision: FP64
+		const double fr = floor(wy), fc = floor(wx);
+		const int row = (int)fr, col = (int)fc;
+		float wr[4], dr[4], wc[4], dc[4];
+		cr_weights_f<JAC>((float)(wy - fr), wr, dr);
+		cr_weights_f<JAC>((float)(wx - fc), wc, dc);
+		float g0 = 0, g1 = 0, gr0 = 0, gr1 = 0, gc0 = 0, gc1 = 0;
+		const int tr = row - 1 - r0, tc = col - 1 - c0;
+		const bool in_tile = staged && tr >= 0 && tr + 3 < TS && tc >= 0 && tc + 3 < TS;
+#pragma unroll
+		for (int r = 0; r < 4; ++r)
+		{
+			float f0 = 0, f1 = 0, d0 = 0, d1 = 0;
+#pragma unroll
+			for (int j = 0; j < 4; ++j)
+			{
+				float2 p;
+				if (in_tile)
+					p = tf[(tr + r) * TS + tc + j];
+				else
+				{
+					const double2 q = __ldg(grid + min(max(row - 1 + r, 0), H - 1) * W + min(max(col - 1 + j, 0), W - 1));
+					p = make_float2((float)q.x, (float)q.y);
+				}
+				f0 += wc[j] * p.x;
+				f1 += wc[j] * p.y;
+				if (JAC)
+				{
+					d0 += dc[j] * p.x;
+					d1 += dc[j] * p.y;
+				}
+			}
+			g0 += wr[r] * f0;
+			g1 += wr[r] * f1;
+			if (JAC)
+			{
+				gr0 += dr[r] * f0;
+				gr1 += dr[r] * f1;
+				gc0 += wr[r] * d0;
+				gc1 += wr[r] * d1;
+			}
+		}
+		g0 *= 0.25f;
+		g1 *= 0.25f;
+		const float u = g0 * vxf + g1 * vyf;
+		const float mi = (float)m[i];
+		a[0] += u * u;
+		a[1] += u * mi;
+		if (JAC)
+		{
+			gr0 *= 0.25f; gr1 *= 0.25f; gc0 *= 0.25f; gc1 *= 0.25f;
+			const float pxf = (float)px, pyf = (float)py;
+			const float ux = gc0 * vxf + gc1 * vyf, uy = gr0 * vxf + gr1 * vyf;
+			float du[4];
+			du[0] = ux * csf + uy * snf;
+			du[1] = -ux * snf + uy * csf;
+			du[2] = ux * (-csf * pyf - snf * pxf) + uy * (-snf * pyf + csf * pxf);
+			du[3] = -g0 * vyf + g1 * vxf;
+#pragma unroll
+			for (int q = 0; q < 4; ++q)
+			{
+				a[2 + q] += u * du[q];
+				a[6 + q] += du[q] * mi;
+			}
+			int k = 10;
+#pragma unroll
+			for (int q = 0; q < 4; ++q)
+#pragma unroll
+				for (int pp = q; pp < 4; ++pp) a[k++] += du[q] * du[pp];
+		}
+	}
+#pragma unroll
+	for (int k = 0; k < (JAC ? 20 : 2); ++k) acc[k] = (double)a[k];
+}
+#else
+__device__ __forceinline__ void stage_texel(double2* tile, int idx, double2 g) { tile[idx] = g; }
+#endif
+
 // The 625 pixels are strided over STRIDE threads; `tid` is this thread's index among them.
 template <bool JAC, int STRIDE>
 __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, int W, int H,
@@ -346,6 +469,10 @@ __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, in
 											 double (&acc)[JAC ? 20 : 2], const double2* tile, int r0, int c0,
 											 bool staged)
 {
+#ifdef EBT_FP32_SAMPLING
+	eval_pixels_f32<JAC, STRIDE>(grid, W, H, x, vx, vy, tlx, tly, m, tid, acc, tile, r0, c0, staged);
+	return;
+#endif
 	const double cs = x[0], sn = x[1], tx = x[2], ty = x[3];
 #pragma unroll
 	for (int k = 0; k < (JAC ? 20 : 2); ++k) acc[k] = 0.0;
@@ -1260,7 +1387,7 @@ __device__ EBT_NOINLINE void optimize_feature(FeatShared& sh, double* costs, Fea
 		{
 			const int i = idx / TS, j = idx - i * TS;
 			const int rr = min(max(r0 + i, 0), H - 1), cc = min(max(c0 + j, 0), W - 1);
-			sh.tile[idx] = __ldg(grid + rr * W + cc);
+			stage_texel(sh.tile, idx, __ldg(grid + rr * W + cc));
 		}
 	}
 	if (threadIdx.x == 0)
@@ -2081,7 +2208,7 @@ __device__ __noinline__ void sb_serve(SL& S, int kind, int ptid)
 		{
 			const int i = idx / TS, j = idx - i * TS;
 			const int rr = min(max(E.r0 + i, 0), E.H - 1), cc = min(max(E.c0 + j, 0), E.W - 1);
-			S.tile[idx] = __ldg(E.grid + rr * E.W + cc);
+			stage_texel(S.tile, idx, __ldg(E.grid + rr * E.W + cc));
 		}
 		return;
 	}
@@ -2422,7 +2549,7 @@ __device__ __noinline__ void mq_serve(StreamSlot& S, int kind, int ptid)
 			{
 				const int i = idx / TS, j = idx - i * TS;
 				const int rr = min(max(E.r0 + i, 0), E.H - 1), cc = min(max(E.c0 + j, 0), E.W - 1);
-				S.tile[idx] = __ldg(E.grid + rr * E.W + cc);
+				stage_texel(S.tile, idx, __ldg(E.grid + rr * E.W + cc));
 			}
 		return;
 	}

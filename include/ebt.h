@@ -130,8 +130,10 @@ int ebt_get_features(ebt_ctx* ctx, double* cornersXY, int cap, int* n_out);
 
 /* FeatureDetector::updatePatches (feature_detector.cpp:585-619) for n events in
  * stream order (the reference takes one event per call).  Host buffer; the
- * call copies it to the device, runs the stream kernel and returns after the
- * resulting track state and optimisation records are back on the host.
+ * call copies it to the device, runs the stream kernel and returns when the
+ * resulting track state is back on the host; the optimisation records of the
+ * push are still travelling then (their copy overlaps the caller's next image)
+ * and are complete whenever a getter that reads them returns.
  * *n_optimizations (may be NULL) receives the number of Optimizer::optimize
  * equivalents performed. */
 int ebt_push_events(ebt_ctx* ctx, const ebt_event* events, int64_t n, int64_t* n_optimizations);

@@ -7,7 +7,7 @@ from event_based_odomety_b200 import synth
 from event_based_odomety_b200.cabi import Tracker, K_TRACK
 import bench
 
-WL = sys.argv[1] if len(sys.argv) > 1 else "c2"
+WL = sys.argv[1] if len(sys.argv) > 1 else "c3"
 w, h, feat, rate, seed = bench.WORKLOADS[WL]
 S = synth.make_stream(w, h, 0.30, rate, seed, max_corners=feat)
 nF = len(S.frames)
