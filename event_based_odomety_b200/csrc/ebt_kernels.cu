@@ -342,7 +342,7 @@ __device__ __forceinline__ void sample_taps_tile(const double2* base, const doub
 // MEASUREMENT-ONLY variant (never the shipped build): the bicubic
 // sampling, u and du of a pixel and the per-thread partial sums in FP32 (tile staged as float2),
 // the reduction from the per-thread partials on, the in-image decisions and everything on the
-// leader in FP64.  profiles/r2_variants.md reports its flip rate against the oracle and its speed.
+// leader in FP64.  profiles/r2_variants.md reports its flip rate against the CPU reference and its speed.
 template <bool DERIV>
 __device__ __forceinline__ void cr_weights_f(float t, float (&w)[4], float (&d)[4])
 {
