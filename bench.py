@@ -34,7 +34,6 @@ import subprocess
 import sys
 import threading
 import time
-from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 
@@ -106,7 +105,7 @@ class FlowCache:
         return self.cache[key]
 
 
-def frame_phase(tr, S, flows, frame_fn, k):
+def frame_phase(tr, S, flows, frame_fn, k, end=True):
     """FeatureDetector::newImage for image k (Replayer/Evaluator order, replayer.cpp:56-98)."""
     frame_fn(k)
     ids, xy = tr.get_uninit()
@@ -117,7 +116,8 @@ def frame_phase(tr, S, flows, frame_fn, k):
         else:
             for i in range(len(ids)):
                 tr.set_flow(ids[i], found[i], nxt[i, 0], nxt[i, 1])
-    tr.new_frame_end()
+    if end:
+        tr.new_frame_end()
 
 
 class ClockSampler(threading.Thread):
@@ -346,7 +346,7 @@ class Lane:
 def main_ours(args):
     import torch
     import torch.distributed as dist
-    from event_based_odomety_b200.cabi import K_GRAD, K_NUMEV, K_TRACK, Tracker, push_events_multi
+    from event_based_odomety_b200.cabi import K_GRAD, K_NUMEV, K_TRACK, Tracker, new_frame_end_multi, push_events_multi
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -395,7 +395,6 @@ def main_ours(args):
     # every step, inside the timed region (~0.05 ms)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     torch.cuda.synchronize()
-    pool = ThreadPoolExecutor(max_workers=min(nS, max(1, min(cores, 8)))) if nS > 1 else None
 
     def barrier():
         if world > 1:
@@ -404,21 +403,22 @@ def main_ours(args):
 
     def step(host):
         """One step of every stream of this rank.  Per image: the frames of all streams
-        (host logic per stream: a few host threads, ctypes releases the GIL), then ONE
-        ebt_push_events_multi for the event batches of all of them."""
+        (association and flow injection per stream, their device tails in one
+        ebt_new_frame_end_multi), then ONE ebt_push_events_multi for the event batches of all
+        of them — one host thread per GPU."""
         for L in lanes:
             L.tr.reset()
         total = 0
         for k in range(nF):
             live = [L for L in lanes if k < L.nF]
 
-            def frame(L):
-                frame_phase(L.tr, L.S, L.flows, L.frame_host if host else L.frame_dev, k)
-            if pool is not None:
-                list(pool.map(frame, live))
-            else:
+            if len(live) > 1:
+                # association and flow injection per stream, then the frame tails of all streams in one call
                 for L in live:
-                    frame(L)
+                    frame_phase(L.tr, L.S, L.flows, L.frame_host if host else L.frame_dev, k, end=False)
+                new_frame_end_multi([L.tr for L in live])
+            else:
+                frame_phase(live[0].tr, live[0].S, live[0].flows, live[0].frame_host if host else live[0].frame_dev, k)
             if len(live) == 1:
                 ptr, n = live[0].batch(k, host)
                 pusher = shard if shard is not None else live[0].tr

@@ -57,6 +57,7 @@ EXPORTS = {
     "ebt_set_flow": (C.c_int, [_vp, C.c_int32, C.c_int, C.c_float, C.c_float]),
     "ebt_set_flows": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int]),
     "ebt_new_frame_end": (C.c_int, [_vp]),
+    "ebt_new_frame_end_multi": (C.c_int, [_vp, C.c_int]),
     "ebt_default_frontend_params": (C.c_int, [C.POINTER(FrontendParams)]),
     "ebt_set_frontend_params": (C.c_int, [_vp, C.POINTER(FrontendParams)]),
     "ebt_detect_features": (C.c_int, [_vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]),
@@ -165,6 +166,16 @@ def push_events_multi(trackers, events, counts=None, device_resident=False):
     if rc != 0:
         raise EbtError(f"ebt error {rc}: {lib.ebt_last_error(trackers[0].ctx).decode()}")
     return [int(v) for v in out]
+
+
+def new_frame_end_multi(trackers):
+    """ebt_new_frame_end_multi: the frame tails of several trackers, device work overlapped."""
+    lib = load()
+    S = len(trackers)
+    ctxs = (_vp * S)(*[t.ctx for t in trackers])
+    rc = lib.ebt_new_frame_end_multi(ctxs, S)
+    if rc != 0:
+        raise EbtError(f"ebt error {rc}: {lib.ebt_last_error(trackers[0].ctx).decode()}")
 
 
 STATIC_PARSE_MAX_BYTES = 64 << 20  # EBT_STATIC_PARSE_MAX_BYTES (include/ebt.h)
@@ -409,7 +420,7 @@ class Tracker:
         return ids[:k], nopt[:k], t0[:k], t1[:k], sm[:k]
 
     def set_stream_kernel(self, mode):
-        """0: one CTA per feature; 1: two features per CTA sharing its pixel warps."""
+        """0: one CTA per feature; 2: persistent CTAs of two leader warps sharing four pixel warps; 1: automatic."""
         self._ck(self.lib.ebt_set_stream_kernel(self.ctx, int(mode)))
 
     def set_cost_map(self, on=True):

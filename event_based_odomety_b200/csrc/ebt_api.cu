@@ -1091,22 +1091,59 @@ int ebt_set_flows(ebt_ctx* ctx, const int32_t* track_ids, const int32_t* found, 
 }
 
 // FeatureDetector::newImage, second half (feature_detector.cpp:499-535).
+// first half of newImage's tail: upload, updateNumOfEvents for every patch, state on its way back (queued only)
+static int frameEndEnqueue(ebt_ctx* ctx)
+{
+	CU(cudaSetDevice(ctx->device));
+	if (ctx->h.empty()) return EBT_OK;
+	const int rc = uploadPatches(ctx);
+	if (rc != EBT_OK) return rc;
+	const int rcf = syncFrameTable(ctx);
+	if (rcf != EBT_OK) return rcf;
+	tic(ctx);
+	CU(ebt_launch_num_events(ctx->d_patches, static_cast<int>(ctx->h.size()), frameTable(ctx), ctx->dp, ctx->stream));
+	toc(ctx, K_NUMEV);
+	CU(cudaMemcpyAsync(ctx->h_stage, ctx->d_patches, ctx->h.size() * sizeof(DevPatch), cudaMemcpyDeviceToHost, ctx->stream));
+	return EBT_OK;
+}
+
+static int frameEndFinish(ebt_ctx* ctx);
+
 int ebt_new_frame_end(ebt_ctx* ctx)
 {
 	if (!ctx) return EBT_E_INVALID;
+	const int rc = frameEndEnqueue(ctx);
+	return rc != EBT_OK ? rc : frameEndFinish(ctx);
+}
+
+// The same for the contexts of several streams (configs[3]): the device work of all of them is queued
+// first, each on its own CUDA stream, then waited for — one host thread, the latencies overlap.
+int ebt_new_frame_end_multi(ebt_ctx* const* ctxs, int n_streams)
+{
+	ebt_ctx* ctx = (ctxs && n_streams > 0) ? ctxs[0] : nullptr;
+	if (!ctx) return EBT_E_INVALID;
+	for (int i = 0; i < n_streams; ++i)
+		if (!ctxs[i]) return fail(ctx, EBT_E_INVALID, "ebt_new_frame_end_multi: null context");
+	int result = EBT_OK;
+	for (int i = 0; i < n_streams && result == EBT_OK; ++i) result = frameEndEnqueue(ctxs[i]);
+	for (int i = 0; i < n_streams; ++i)
+	{
+		const int rc = frameEndFinish(ctxs[i]);  // also after a failed enqueue elsewhere: every stream is drained
+		if (rc != EBT_OK && result == EBT_OK) result = rc;
+	}
+	if (result != EBT_OK)
+		for (int i = 1; i < n_streams; ++i)
+			if (!ctxs[i]->err.empty() && ctx->err.empty()) ctx->err = ctxs[i]->err;
+	return result;
+}
+
+static int frameEndFinish(ebt_ctx* ctx)
+{
 	CU(cudaSetDevice(ctx->device));
 	if (!ctx->h.empty())
 	{
-		const int rc = uploadPatches(ctx);
-		if (rc != EBT_OK) return rc;
-		const int rcf = syncFrameTable(ctx);
-		if (rcf != EBT_OK) return rcf;
-		tic(ctx);
-		CU(ebt_launch_num_events(ctx->d_patches, static_cast<int>(ctx->h.size()), frameTable(ctx),
-								 ctx->dp, ctx->stream));
-		toc(ctx, K_NUMEV);
-		const int rc2 = downloadPatches(ctx);
-		if (rc2 != EBT_OK) return rc2;
+		CU(cudaStreamSynchronize(ctx->stream));
+		std::memcpy(ctx->h.data(), ctx->h_stage, ctx->h.size() * sizeof(DevPatch));
 	}
 	// archive lost patches, keep list order (feature_detector.cpp:512-523): their
 	// patch products come back through one pinned staging buffer — every copy and

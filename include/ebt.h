@@ -83,6 +83,10 @@ int ebt_set_flow(ebt_ctx* ctx, int32_t track_id, int found, float next_x, float 
 /* ebt_set_flow for n patches in one call; nextXY = n (x, y) float pairs. */
 int ebt_set_flows(ebt_ctx* ctx, const int32_t* track_ids, const int32_t* found, const float* nextXY, int n);
 int ebt_new_frame_end(ebt_ctx* ctx);
+/* ebt_new_frame_end for the detectors of n_streams streams (configs[3]) from one host
+ * thread: the window-size kernels and state copies of all of them are queued first,
+ * each on its context's CUDA stream, then waited for.  Errors are reported on ctxs[0]. */
+int ebt_new_frame_end_multi(ebt_ctx* const* ctxs, int n_streams);
 
 /* ---- per-frame re-arm on the device ------------------------
  * What the reference delegates to OpenCV inside newImage, as sm_100a kernels

@@ -179,7 +179,7 @@ def test_multi_stream_push_equals_the_streams_alone():
     """ebt_push_events_multi (configs[3]: independent streams in one launch): three streams of different
     seeds, feature counts and batch sizes — one of them runs out of events early — each equal to the
     CPU oracle's per-event loop on that stream alone."""
-    from event_based_odomety_b200.cabi import push_events_multi
+    from event_based_odomety_b200.cabi import new_frame_end_multi, push_events_multi
     streams = [synth.make_stream(240, 180, 0.15, 500e3, seed=2000, max_corners=69),
                synth.make_stream(240, 180, 0.15, 300e3, seed=2001, max_corners=40),
                synth.make_stream(240, 180, 0.10, 600e3, seed=2002, max_corners=60)]
@@ -202,8 +202,8 @@ def test_multi_stream_push_equals_the_streams_alone():
                 for j, tid in enumerate(ids):
                     inside = (0 <= nxt[j, 0] < S.width) and (0 <= nxt[j, 1] < S.height)
                     g.set_flow(tid, int(inside), nxt[j, 0], nxt[j, 1])
-            g.new_frame_end()
             batches.append(S.events_between(k))
+        new_frame_end_multi([g for g, S in zip(gpus, streams) if k < len(S.frames)])
         got = push_events_multi(gpus, batches)
         n_gpu = [a + b for a, b in zip(n_gpu, got)]
     assert n_gpu == n_cpu and min(n_cpu) > 0
