@@ -11,9 +11,8 @@ namespace tracker
 {
 struct FlowEstimatorParams
 {
-	int32_t numLevels = 3;
-	cv::Size window = {21, 21};  // fixed on the device
-	// seconds in double to microseconds
-	double patchTimeWithoutUpdateScale = 1e6;
+	int32_t numLevels = 3;                     // ebt_frontend_params::lk_levels (maxLevel of calcOpticalFlowPyrLK)
+	cv::Size window = {21, 21};                // fixed on the device (lk_track_kernel's 21 x 21 template)
+	double patchTimeWithoutUpdateScale = 1e6;  // seconds in double to microseconds (fixed on the device)
 };
 }  // namespace tracker

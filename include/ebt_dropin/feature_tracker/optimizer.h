@@ -12,21 +12,20 @@ namespace tracker
 {
 struct OptimizerParams
 {
-	bool drawCostMap = false;
-	int maxNumIterations = 10;
-	int numThreads = 1;  // unused: one warp or CTA per feature on the device
-	double optimizerThreshold = 0.6;
-	double huberLoss = 0.3;
-	int costMapWidth = 11;   // fixed at 11 x 11 on the device
+	bool drawCostMap = false;          // ebt_set_cost_map: 121 extra pixel passes per optimisation
+	int maxNumIterations = 10;         // ebt_params::max_iterations (Ceres max_num_iterations)
+	int numThreads = 1;                // unused: one warp or CTA per feature on the device
+	double optimizerThreshold = 0.6;   // ebt_params::optimizer_threshold (median-of-5 cost filter)
+	double huberLoss = 0.3;            // ebt_params::huber_loss
+	int costMapWidth = 11;             // fixed at 11 x 11 on the device
 	int costMapHeight = 11;
-	// seconds in double to microseconds
-	double patchTimeWithoutUpdateScale = 1e6;
+	double patchTimeWithoutUpdateScale = 1e6;  // seconds in double to microseconds (fixed on the device)
 };
 
-struct OptimizerFinalLoss
+struct OptimizerFinalLoss  // one per optimisation: the (track, cost, time) projection of ebt_opt_record
 {
-	tracker::TrackId trackId;
-	double lossValue;
-	int64_t timeStampMicrosecond;
+	tracker::TrackId trackId;      // ebt_opt_record::track_id
+	double lossValue;              // ebt_opt_record::final_cost
+	int64_t timeStampMicrosecond;  // ebt_opt_record::ts
 };
 }  // namespace tracker
