@@ -2490,6 +2490,20 @@ struct __align__(16) StreamSlot
 	// the two newest entries of Patch::trajectory_ (DevPatch::traj_*), written back at the end
 	double traj_x[2], traj_y[2];
 	long long traj_ts[2];
+	// the feature's state between optimisations and where its walk stands in the batch: in shared
+	// memory so that nothing of it has to survive the solve in registers (see the leader loop)
+	FeatState st;
+	struct
+	{
+		double srx, sry;  // where the candidate region of the mask row is centred
+		double margin;
+		long long start;  // first stream event not consumed yet
+		long long n_events;
+		const ebt_event* events;
+		unsigned* row;
+		unsigned long long t_enter;
+		int wpr, n_opt, track_id, win_tail0;
+	} walk;
 	int job_i[4];             // integer job arguments (5: window tail, size; 6: x0, y0)
 	int redi[SB_PIXW];        // job 5: per-warp sum of squares of the integer patch
 	unsigned long long done_bar;  // mbarrier: SB_PIXW pixel-warp arrivals complete a job
@@ -2784,6 +2798,13 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 	// ---- leader warp `warp`.  First work item: CTA c pairs the c-th heaviest with the c-th
 	// lightest (work[] is heaviest first), so two long chains do not share pixel warps;
 	// afterwards the leaders pull the items in between from the queue, heaviest first.
+	//
+	// What the walk needs of the feature's state between optimisations (rect, window cursor,
+	// counters, where it stands in the batch) lives in the slot's shared memory (S.st, S.walk), not in
+	// registers: values that would have to survive the inlined solve in registers get spilled to local
+	// memory and come back through an L1 that the streaming loads keep evicting (measured: 3.4 k cycles
+	// per ballot round).  Discipline: every lane reads at the top of a round, lane 0 writes behind the
+	// round's ballot, __syncwarp() separates the write from the next round's reads.
 	StreamSlot& S = slots[warp];
 	static_assert(SB_LEADERS == 2, "work pairing below is written for two leaders per CTA");
 	const int n_ctas = (int)gridDim.x;
@@ -2796,24 +2817,23 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 		const StreamDesc& D = descs[item.stream];
 		DevPatch& gp = D.patches[item.feature];
 		if (gp.lost || gp.foreign) continue;
-		unsigned long long t_enter;
-		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_enter));
 		WALK_T(wk_enter);
-		FeatState st;
-		load_state(st, gp);
-		const int track_id = gp.track_id;
-		ebt_event* gring = D.rings + (size_t)gp.store_slot * EBT_RING;
-		int* gnabla = D.nablas + (size_t)gp.store_slot * NPIX;
-		for (int k = lane; k < st.size; k += 32) S.ring[k] = gring[(st.tail + k) & RMASK];
-		if (lane < EBT_COST_HISTORY) S.costs[lane] = gp.costs[lane];
-		if (lane < 2)
+		if (lane == 0)
 		{
-			S.traj_x[lane] = gp.traj_x[lane];
-			S.traj_y[lane] = gp.traj_y[lane];
-			S.traj_ts[lane] = gp.traj_ts[lane];
-		}
-		if (lane == 2)
-		{
+			asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(S.walk.t_enter));
+			load_state(S.st, gp);
+			S.walk.win_tail0 = S.st.tail;
+			S.st.tail = 0;
+			S.walk.srx = S.st.rx;
+			S.walk.sry = S.st.ry;
+			S.walk.start = 0;
+			S.walk.n_opt = 0;
+			S.walk.track_id = gp.track_id;
+			S.walk.margin = D.margin;
+			S.walk.events = D.events;
+			S.walk.n_events = D.n_events;
+			S.walk.row = D.mask + (size_t)item.feature * D.words_per_row;
+			S.walk.wpr = D.words_per_row;
 			S.grids = D.grids;
 			S.records = D.records;
 			S.n_records = D.n_records;
@@ -2821,24 +2841,31 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 			S.event_base = D.event_base;
 			S.latest = D.latest;
 		}
-		st.tail = 0;
+		if (lane < EBT_COST_HISTORY) S.costs[lane] = gp.costs[lane];
+		if (lane < 2)
+		{
+			S.traj_x[lane] = gp.traj_x[lane];
+			S.traj_y[lane] = gp.traj_y[lane];
+			S.traj_ts[lane] = gp.traj_ts[lane];
+		}
 		__syncwarp();
-		const ebt_event* events = D.events;
-		const long long n_events = D.n_events;
-		const int wpr = D.words_per_row;
-		const double margin = D.margin;
-		const uint4* ev4 = reinterpret_cast<const uint4*>(events);
-		unsigned* row = D.mask + (size_t)item.feature * wpr;
-		double srx = st.rx, sry = st.ry;
-		long long start = 0;
-		int n_opt = 0;
-		bool pre = st.init && n_events > 0 && window_need(st, P) <= 0;
+		{
+			const ebt_event* gring = D.rings + (size_t)gp.store_slot * EBT_RING;
+			const int tail0 = S.walk.win_tail0, size0 = S.st.size;
+			for (int k = lane; k < size0; k += 32) S.ring[k] = gring[(tail0 + k) & RMASK];
+		}
+		__syncwarp();
+		const long long n_events = S.walk.n_events;
 		const long long n_words = (n_events + 31) >> 5;
+		bool pre = S.st.init && n_events > 0 && window_need(S.st, P) <= 0;
 		long long seg = 0;
-		uint4 cur = mq_load_segment(row, seg, wpr, lane);
-		while (!st.lost && seg < n_words)
+		uint4 cur = mq_load_segment(S.walk.row, seg, S.walk.wpr, lane);
+		while (!S.st.lost && seg < n_words)
 		{
 			WALK_T(ws0);
+			const unsigned* row = S.walk.row;
+			const int wpr = S.walk.wpr;
+			const long long start = S.walk.start;
 			// the next segment's words travel while this one is walked
 			const uint4 nxt = mq_load_segment(row, seg + MQ_SEG_WORDS, wpr, lane);
 			unsigned w4[4] = {cur.x, cur.y, cur.z, cur.w};
@@ -2881,106 +2908,126 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 			__syncwarp();
 			WALK_T(ws1);
 			WALK_ADD(lane == 0, 3, ws1 - ws0);  // diagnostic builds: slot 3 = mask wait + expansion
-			bool restart = false;
+			bool restart = false, lost = false;
+			const uint4* ev4 = reinterpret_cast<const uint4*>(S.walk.events);
 			// candidate records: chunk c + 1 is loaded before chunk c is walked
 			uint4 raw_next = make_uint4(0, 0, 0, 0);
 			if (lane < n_c) raw_next = __ldg(ev4 + ((seg << 5) + S.cand[lane]));
-			for (int cbase = 0; cbase < n_c && !restart && !st.lost; cbase += 32)
+			for (int cbase = 0; cbase < n_c && !restart && !lost; cbase += 32)
 			{
 				const int chunk_len = min(32, n_c - cbase);
 				const uint4 raw = raw_next;
 				if (cbase + 32 + lane < n_c) raw_next = __ldg(ev4 + ((seg << 5) + S.cand[cbase + 32 + lane]));
 				const int ex = (int)(raw.z & 0xffffu), ey = (int)(raw.z >> 16);
 				int resume = 0;
-				WALK_T(wc0);
 				while (resume < chunk_len)
 				{
+					// this round's view of the window state (lane 0 rewrites it behind the ballot)
+					const double rx = S.st.rx, ry = S.st.ry;
+					const int w_init = S.st.init, w_counter = S.st.counter, w_size = S.st.size, w_tail = S.st.tail,
+							  w_noe = S.st.num_of_events;
 					const bool live = lane >= resume && lane < chunk_len;
-					const bool inside = live && in_rect(st.rx, st.ry, ex, ey);
+					const bool inside = live && in_rect(rx, ry, ex, ey);
 					const unsigned bal = __ballot_sync(0xffffffffu, inside);
-#ifdef EBT_WALK_CLOCKS
-					if (resume == 0)
-					{
-						WALK_T(wc1);
-						WALK_ADD(lane == 0, 7, wc1 - wc0);  // diagnostic builds: slot 7 = wait for the chunk's records + first test
-					}
-#endif
 					const int total = __popc(bal);
 					const int rank = __popc(bal & ((1u << lane) - 1u)) + 1;  // if inside
-					const int need = window_need(st, P);
+					const int need = max(P.batch_stride - w_counter, w_noe - w_size);  // window_need
 					int trig = -1, take = total;
-					if (st.init && need <= 0)
+					if (w_init && need <= 0)
 					{
 						trig = resume;
 						take = (int)((bal >> resume) & 1u);
 					}
-					else if (st.init && total >= need)
+					else if (w_init && total >= need)
 					{
 						take = need;
 						trig = (int)__fns(bal, 0, need);
 					}
 					if (inside && rank <= take)
-						*reinterpret_cast<uint4*>(&S.ring[(st.tail + st.size + rank - 1) & RMASK]) = raw;
-					if (take > 0) window_grow(st, take);
+						*reinterpret_cast<uint4*>(&S.ring[(w_tail + w_size + rank - 1) & RMASK]) = raw;
+					if (take > 0 && lane == 0)
+					{
+						// Patch::addEvent (patch.cpp:37-47): append, trim to numOfEvents_ (window_grow)
+						const int grown = w_size + take;
+						const int kept = min(grown, w_noe);
+						S.st.tail = (w_tail + grown - kept) & RMASK;
+						S.st.size = kept;
+						S.st.counter = w_counter + take;
+					}
 					__syncwarp();
 					if (trig < 0) break;
 					const long long at = (seg << 5) + S.cand[cbase + trig];
-					// ---- one Optimizer::optimize at stream event `at` and the bookkeeping around it
-					LmSummary L;
-					WALK_T(w0);
-					// the record's slot is reserved now: the atomic's round trip hides behind the solve
-					unsigned long long rec_slot = 0;
-					if (lane == 0) rec_slot = atomicAdd(S.n_records, 1ull);
-					mq_optimize(S, st, S.grids[st.frame_slot], P, L);
-					WALK_T(w1);
-					WALK_ADD(lane == 0, 1, w1 - w0);
-					WALK_ADD(lane == 0, 5, 1);
-					if (!L.filtered && lane == 0)
+					// ---- one Optimizer::optimize at stream event `at` and the bookkeeping around it, on a
+					// register copy of the state that lives only inside this block
 					{
-						// Patch::addTrajectoryPosition: the two newest trajectory entries
-						S.traj_x[0] = S.traj_x[1]; S.traj_y[0] = S.traj_y[1]; S.traj_ts[0] = S.traj_ts[1];
-						S.traj_x[1] = st.rx + (SIDE - 1) / 2.; S.traj_y[1] = st.ry + (SIDE - 1) / 2.; S.traj_ts[1] = st.cur_ts;
-					}
-					WALK_T(w2);
-					mq_update_num_of_events(S, st, S.grids[S.latest], P);
-					WALK_T(w3);
-					WALK_ADD(lane == 0, 6, w3 - w2);
-					if (lane == 0) write_record_at(S.records, rec_slot, S.record_cap, st, track_id, L, S.event_base + at);
-					++n_opt;
-					start = at + 1;
-					if (!st.lost && (fabs(st.rx - srx) > margin || fabs(st.ry - sry) > margin))
-					{
-						// rebuild the mask row from `start` on around the rect's current position
-						const int4 bb = candidate_bounds(st.rx, st.ry, margin);
-						const unsigned* ev32 = reinterpret_cast<const unsigned*>(events);
-						// eight mask words per trip: eight independent loads in flight per lane
-						for (long long w0 = (start >> 5); w0 < n_words; w0 += 8)
+						FeatState st = S.st;
+						LmSummary L;
+						WALK_T(w0);
+						// the record's slot is reserved now: the atomic's round trip hides behind the solve
+						unsigned long long rec_slot = 0;
+						if (lane == 0) rec_slot = atomicAdd(S.n_records, 1ull);
+						mq_optimize(S, st, S.grids[st.frame_slot], P, L);
+						WALK_T(w1);
+						WALK_ADD(lane == 0, 1, w1 - w0);
+						WALK_ADD(lane == 0, 5, 1);
+						if (!L.filtered && lane == 0)
 						{
-							unsigned v[8];
-#pragma unroll
-							for (int j = 0; j < 8; ++j)
+							// Patch::addTrajectoryPosition: the two newest trajectory entries
+							S.traj_x[0] = S.traj_x[1]; S.traj_y[0] = S.traj_y[1]; S.traj_ts[0] = S.traj_ts[1];
+							S.traj_x[1] = st.rx + (SIDE - 1) / 2.; S.traj_y[1] = st.ry + (SIDE - 1) / 2.; S.traj_ts[1] = st.cur_ts;
+						}
+						WALK_T(w2);
+						mq_update_num_of_events(S, st, S.grids[S.latest], P);
+						WALK_T(w3);
+						WALK_ADD(lane == 0, 6, w3 - w2);
+						lost = st.lost != 0;
+						const bool drifted = !lost && (fabs(st.rx - S.walk.srx) > S.walk.margin || fabs(st.ry - S.walk.sry) > S.walk.margin);
+						__syncwarp();  // every lane has taken its copy and read the walk state
+						if (lane == 0)
+						{
+							write_record_at(S.records, rec_slot, S.record_cap, st, S.walk.track_id, L, S.event_base + at);
+							S.st = st;
+							S.walk.n_opt++;
+							S.walk.start = at + 1;
+							if (drifted)
 							{
-								const long long e = (w0 + j) * 32 + lane;
-								v[j] = e < n_events ? __ldg(ev32 + 4 * e + 2) : 0xffffffffu;  // no region holds 65535
+								S.walk.srx = st.rx;
+								S.walk.sry = st.ry;
 							}
-							unsigned mine = 0;
-#pragma unroll
-							for (int j = 0; j < 8; ++j)
-							{
-								const int x = (int)(v[j] & 0xffffu), y = (int)(v[j] >> 16);
-								const unsigned b2 =
-									__ballot_sync(0xffffffffu, x >= bb.x && x <= bb.y && y >= bb.z && y <= bb.w);
-								if (lane == j) mine = b2;
-							}
-							if (lane < 8 && w0 + lane < n_words) __stcg(row + w0 + lane, mine);
 						}
 						__syncwarp();
-						srx = st.rx;
-						sry = st.ry;
-						restart = true;
-						break;
+						if (drifted)
+						{
+							// rebuild the mask row from the next event on around the rect's current position
+							const int4 bb = candidate_bounds(st.rx, st.ry, S.walk.margin);
+							const unsigned* ev32 = reinterpret_cast<const unsigned*>(S.walk.events);
+							unsigned* wrow = S.walk.row;
+							// eight mask words per trip: eight independent loads in flight per lane
+							for (long long w0 = ((at + 1) >> 5); w0 < n_words; w0 += 8)
+							{
+								unsigned v[8];
+#pragma unroll
+								for (int j = 0; j < 8; ++j)
+								{
+									const long long e = (w0 + j) * 32 + lane;
+									v[j] = e < n_events ? __ldg(ev32 + 4 * e + 2) : 0xffffffffu;  // no region holds 65535
+								}
+								unsigned mine = 0;
+#pragma unroll
+								for (int j = 0; j < 8; ++j)
+								{
+									const int x = (int)(v[j] & 0xffffu), y = (int)(v[j] >> 16);
+									const unsigned b2 =
+										__ballot_sync(0xffffffffu, x >= bb.x && x <= bb.y && y >= bb.z && y <= bb.w);
+									if (lane == j) mine = b2;
+								}
+								if (lane < 8 && w0 + lane < n_words) __stcg(wrow + w0 + lane, mine);
+							}
+							__syncwarp();
+							restart = true;
+						}
 					}
-					if (st.lost) break;
+					if (restart || lost) break;
 					resume = trig + 1;
 				}
 			}
@@ -2994,8 +3041,8 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 			}
 			if (restart)
 			{
-				seg = (start >> 5) & ~3LL;
-				cur = mq_load_segment(row, seg, wpr, lane);
+				seg = (S.walk.start >> 5) & ~3LL;
+				cur = mq_load_segment(S.walk.row, seg, S.walk.wpr, lane);
 			}
 			else
 			{
@@ -3004,30 +3051,36 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 			}
 		}
 		__syncwarp();
-		for (int k = lane; k < st.size; k += 32) gring[k] = S.ring[(st.tail + k) & RMASK];
-		if (n_opt > 0)
-			for (int i = lane; i < NPIX; i += 32) gnabla[i] = S.nabla[i];
-		if (lane < EBT_COST_HISTORY) gp.costs[lane] = S.costs[lane];
-		if (lane < 2 && n_opt > 0)
 		{
-			gp.traj_x[lane] = S.traj_x[lane];
-			gp.traj_y[lane] = S.traj_y[lane];
-			gp.traj_ts[lane] = S.traj_ts[lane];
-		}
-		st.tail = 0;
-		if (lane == 0)
-		{
-			store_state(st, gp);
-			gp.last_n_opt = n_opt;
-			WALK_T(wk_exit);
-			WALK_ADD(true, 0, wk_exit - wk_enter);
-			unsigned long long t_exit;
-			unsigned sm;
-			asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_exit));
-			asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
-			gp.last_t0_ns = t_enter;
-			gp.last_t1_ns = t_exit;
-			gp.last_sm = (int)sm;
+			ebt_event* gring = D.rings + (size_t)gp.store_slot * EBT_RING;
+			int* gnabla = D.nablas + (size_t)gp.store_slot * NPIX;
+			const int tail = S.st.tail, size = S.st.size, n_opt = S.walk.n_opt;
+			for (int k = lane; k < size; k += 32) gring[k] = S.ring[(tail + k) & RMASK];
+			if (n_opt > 0)
+				for (int i = lane; i < NPIX; i += 32) gnabla[i] = S.nabla[i];
+			if (lane < EBT_COST_HISTORY) gp.costs[lane] = S.costs[lane];
+			if (lane < 2 && n_opt > 0)
+			{
+				gp.traj_x[lane] = S.traj_x[lane];
+				gp.traj_y[lane] = S.traj_y[lane];
+				gp.traj_ts[lane] = S.traj_ts[lane];
+			}
+			__syncwarp();
+			if (lane == 0)
+			{
+				S.st.tail = 0;
+				store_state(S.st, gp);
+				gp.last_n_opt = n_opt;
+				WALK_T(wk_exit);
+				WALK_ADD(true, 0, wk_exit - wk_enter);
+				unsigned long long t_exit;
+				unsigned sm;
+				asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_exit));
+				asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+				gp.last_t0_ns = S.walk.t_enter;
+				gp.last_t1_ns = t_exit;
+				gp.last_sm = (int)sm;
+			}
 		}
 		__syncwarp();
 	}
