@@ -2450,13 +2450,13 @@ optimize_batch_shared_kernel(const ebt_problem* __restrict__ problems, int n_pro
 //   5  Patch::integrateEvents: the 625 pixels are dealt out to the pixel warps
 //      (pixel i belongs to warp i mod 4), every warp scans the whole window and
 //      accumulates the events that fall on its own pixels, then sums their squares
-//      — no ordering between the pixel warps is needed
-//   3  normalised patch m = nabla * inv + its squared sum, and the staged tile
+//      — no ordering between the pixel warps is needed; the same job stages the
+//      template-grid tile of the solve (the leader then normalises the patch itself)
 //   1/2 cost / cost + Jacobian pixel pass of the LM solve
 //   6  the 625 nearest-neighbour samples of FeatureDetector::updateNumOfEvents
 // While one leader walks, or runs its scalar step, the pixel warps serve the other.
 // Candidate walk: 128 mask words (4096 stream events) per segment, one 16-byte
-// load per lane, the next segment's words already in flight.
+// load per lane, the words of the next two segments already in flight.
 // Shape (measured, profiles/r2_variants.md): two leaders per four pixel warps at 168
 // registers, two CTAs per SM.  Three leaders per pixel set — uniformly at 144 registers,
 // or with setmaxnreg moving registers from the leader warpgroup (88-112) to the pixel
@@ -2543,21 +2543,7 @@ __device__ __noinline__ void mq_serve(StreamSlot& S, int kind, int ptid)
 #pragma unroll
 		for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
 		if (lane == 0) S.redi[pw] = ss;
-		return;
-	}
-	if (kind == 3)
-	{
-		// Patch::getNormalizedIntegratedNabla (patch.cpp:156-159): Mat * (1/s)
-		const double inv = S.req[0];
-		double a = 0;
-		for (int i = ptid; i < NPIX; i += SB_PIXW * 32)
-		{
-			const double v = (double)S.nabla[i] * inv;
-			S.m[i] = v;
-			a += v * v;
-		}
-		a = warp_sum(a);
-		if (lane == 0) S.red[pw][0] = a;
+		// ... and, in the same job, the template-grid tile of the solve (independent of the integration)
 		if (E.staged)
 			for (int idx = ptid; idx < TS * TS; idx += SB_PIXW * 32)
 			{
@@ -2622,22 +2608,7 @@ __device__ void mq_optimize(StreamSlot& S, FeatState& st, const double2* grid, c
 {
 	const int lane = threadIdx.x & 31;
 	L.filtered = 0;
-	if (lane == 0)
-	{
-		S.req[0] = st.rx;
-		S.req[1] = st.ry;
-		S.job_i[0] = st.tail;
-		S.job_i[1] = st.size;
-		S.req_kind = 5;
-	}
-	sb_post(S);
-	// while the pixel warps integrate: timestamps and the tile origin
-	{
-		const long long front = S.ring[(st.tail + st.size - 1) & RMASK].t_us;
-		const long long back = S.ring[st.tail & RMASK].t_us;
-		st.cur_ts = to_i32((double)(front + back) * 0.5);
-		st.time_last_update = to_i32((double)back);
-	}
+	// tile origin: the bounding box of the rect warped by the initial estimate, + the 4x4 tap footprint
 	int r0 = 0, c0 = 0, staged = 0;
 	{
 		const double c = st.warp[0], s = st.warp[1], tx = st.warp[2], ty = st.warp[3];
@@ -2664,11 +2635,7 @@ __device__ void mq_optimize(StreamSlot& S, FeatState& st, const double2* grid, c
 			}
 		}
 	}
-	wait_partials(S);
-	// the sum of squares of an integer patch is an exact integer in any order
-	const long long ssq = ((long long)S.redi[0] + S.redi[1]) + ((long long)S.redi[2] + S.redi[3]);
-	static_assert(SB_PIXW == 4, "job 5 deals the pixels out to four warps");
-	const double inv = 1.0 / sqrt((double)ssq);
+	// job 5: the pixel warps integrate the window and stage the tile
 	if (lane == 0)
 	{
 		EvalCtx& E = S.ctx;
@@ -2681,14 +2648,37 @@ __device__ void mq_optimize(StreamSlot& S, FeatState& st, const double2* grid, c
 		E.tlx = st.rx;
 		E.tly = st.ry;
 		E.huber_a = P.huber_a;
-		S.req[0] = inv;
-		S.req_kind = 3;
+		S.req[0] = st.rx;
+		S.req[1] = st.ry;
+		S.job_i[0] = st.tail;
+		S.job_i[1] = st.size;
+		S.req_kind = 5;
 	}
 	sb_post(S);
-	wait_partials(S);
+	// meanwhile: timestamps
 	{
-		const double smm = red_total(S, 0);
-		if (lane == 0) S.ctx.smm = smm;
+		const long long front = S.ring[(st.tail + st.size - 1) & RMASK].t_us;
+		const long long back = S.ring[st.tail & RMASK].t_us;
+		st.cur_ts = to_i32((double)(front + back) * 0.5);
+		st.time_last_update = to_i32((double)back);
+	}
+	wait_partials(S);
+	// the sum of squares of an integer patch is an exact integer in any order
+	const long long ssq = ((long long)S.redi[0] + S.redi[1]) + ((long long)S.redi[2] + S.redi[3]);
+	static_assert(SB_PIXW == 4, "job 5 deals the pixels out to four warps");
+	// Patch::getNormalizedIntegratedNabla (patch.cpp:156-159): Mat * (1/s), on the leader itself —
+	// 20 trips are cheaper than another job's round trip behind the sibling's pixel pass
+	const double inv = 1.0 / sqrt((double)ssq);
+	{
+		double a = 0;
+		for (int i = lane; i < NPIX; i += 32)
+		{
+			const double v = (double)S.nabla[i] * inv;
+			S.m[i] = v;
+			a += v * v;
+		}
+		a = warp_sum(a);
+		if (lane == 0) S.ctx.smm = a;
 		__syncwarp();
 	}
 	double x[5] = {st.warp[0], st.warp[1], st.warp[2], st.warp[3], (double)__double2float_rn(st.flow)};
@@ -2860,14 +2850,15 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 		bool pre = S.st.init && n_events > 0 && window_need(S.st, P) <= 0;
 		long long seg = 0;
 		uint4 cur = mq_load_segment(S.walk.row, seg, S.walk.wpr, lane);
+		uint4 nxt = mq_load_segment(S.walk.row, seg + MQ_SEG_WORDS, S.walk.wpr, lane);
 		while (!S.st.lost && seg < n_words)
 		{
 			WALK_T(ws0);
 			const unsigned* row = S.walk.row;
 			const int wpr = S.walk.wpr;
 			const long long start = S.walk.start;
-			// the next segment's words travel while this one is walked
-			const uint4 nxt = mq_load_segment(row, seg + MQ_SEG_WORDS, wpr, lane);
+			// the words of the next two segments travel while this one is walked
+			const uint4 nxt2 = mq_load_segment(row, seg + 2 * MQ_SEG_WORDS, wpr, lane);
 			unsigned w4[4] = {cur.x, cur.y, cur.z, cur.w};
 			int c = 0;
 #pragma unroll
@@ -3043,11 +3034,13 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 			{
 				seg = (S.walk.start >> 5) & ~3LL;
 				cur = mq_load_segment(S.walk.row, seg, S.walk.wpr, lane);
+				nxt = mq_load_segment(S.walk.row, seg + MQ_SEG_WORDS, S.walk.wpr, lane);
 			}
 			else
 			{
 				seg += MQ_SEG_WORDS;
 				cur = nxt;
+				nxt = nxt2;
 			}
 		}
 		__syncwarp();
