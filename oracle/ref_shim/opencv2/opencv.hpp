@@ -10,11 +10,13 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <list>
 #include <memory>
+#include <string>
 #include <vector>
 
 #define CV_8U 0
@@ -206,12 +208,46 @@ class Mat
 		return m;
 	}
 
+	// 8-bit image that owns its pixels (what cv::imread returns)
+	static Mat owned8(int r, int c, const unsigned char* px)
+	{
+		Mat m;
+		m.rows = r;
+		m.cols = c;
+		m.type_ = CV_8U;
+		m.step_ = c;
+		m.bytes_ = std::make_shared<std::vector<unsigned char>>(px, px + static_cast<size_t>(r) * c);
+		m.data = m.bytes_->data();
+		return m;
+	}
+
    private:
 	int type_ = CV_64F;
 	int step_ = 0;
 	std::shared_ptr<std::vector<double>> buf_;
+	std::shared_ptr<std::vector<unsigned char>> bytes_;
 	double* base_ = nullptr;
 };
+
+// cv::imread(path, flags) for the one format the replay test writes: binary PGM ("P5", maxval
+// 255), whatever the file is called (the reference's images.txt names .png files; OpenCV picks
+// the decoder by content as well).  An unreadable file gives an empty Mat, as in OpenCV.
+static inline Mat imread(const std::string& path, int /*flags*/ = 0)
+{
+	FILE* f = std::fopen(path.c_str(), "rb");
+	if (!f) return Mat();
+	int w = 0, h = 0, maxv = 0;
+	char magic[3] = {0, 0, 0};
+	Mat out;
+	if (std::fscanf(f, "%2s %d %d %d", magic, &w, &h, &maxv) == 4 && magic[0] == 'P' && magic[1] == '5' && maxv == 255 &&
+		w > 0 && h > 0 && std::fgetc(f) != EOF)
+	{
+		std::vector<unsigned char> px(static_cast<size_t>(w) * h);
+		if (std::fread(px.data(), 1, px.size(), f) == px.size()) out = Mat::owned8(h, w, px.data());
+	}
+	std::fclose(f);
+	return out;
+}
 
 // dst = a*alpha + b*beta  (the evaluation OpenCV's lazy MatExpr performs for
 // scaled sums; b may be empty).
