@@ -2664,8 +2664,9 @@ __device__ void mq_optimize(StreamSlot& S, FeatState& st, const double2* grid, c
 	}
 	wait_partials(S);
 	// the sum of squares of an integer patch is an exact integer in any order
-	const long long ssq = ((long long)S.redi[0] + S.redi[1]) + ((long long)S.redi[2] + S.redi[3]);
-	static_assert(SB_PIXW == 4, "job 5 deals the pixels out to four warps");
+	long long ssq = 0;
+#pragma unroll
+	for (int w = 0; w < SB_PIXW; ++w) ssq += (long long)S.redi[w];
 	// Patch::getNormalizedIntegratedNabla (patch.cpp:156-159): Mat * (1/s), on the leader itself —
 	// 20 trips are cheaper than another job's round trip behind the sibling's pixel pass
 	const double inv = 1.0 / sqrt((double)ssq);
@@ -2796,12 +2797,17 @@ track_multi_kernel(const StreamDesc* __restrict__ descs, const WorkItem* __restr
 	// per ballot round).  Discipline: every lane reads at the top of a round, lane 0 writes behind the
 	// round's ballot, __syncwarp() separates the write from the next round's reads.
 	StreamSlot& S = slots[warp];
-	static_assert(SB_LEADERS == 2, "work pairing below is written for two leaders per CTA");
 	const int n_ctas = (int)gridDim.x;
+#if SB_LEADERS == 2
 	int oi = warp == 0 ? (int)blockIdx.x : n_work - 1 - (int)blockIdx.x;
 	if (warp == 1 && oi < n_ctas) oi = n_work;  // that one belongs to a first leader
 	for (; oi < n_work;
 		 oi = __shfl_sync(0xffffffffu, lane == 0 ? atomicAdd(queue, 1) : 0, 0), oi = oi < n_work - n_ctas ? oi : n_work)
+#else
+	// other shapes (measurement builds): leader 0 starts on the CTA's own item, everyone else on the queue
+	int oi = warp == 0 ? (int)blockIdx.x : __shfl_sync(0xffffffffu, lane == 0 ? atomicAdd(queue, 1) : 0, 0);
+	for (; oi < n_work; oi = __shfl_sync(0xffffffffu, lane == 0 ? atomicAdd(queue, 1) : 0, 0))
+#endif
 	{
 		const WorkItem item = work[oi];
 		const StreamDesc& D = descs[item.stream];
@@ -3291,7 +3297,7 @@ cudaError_t ebt_launch_track_multi(const StreamDesc* descs, int n_streams, const
 		if (e != cudaSuccess) return e;
 		attr_devices |= 1ull << dev;
 	}
-	const int ctas = min((n_work + 1) / 2, SB_CTAS * device_sm_count());
+	const int ctas = min((n_work + SB_LEADERS - 1) / SB_LEADERS, SB_CTAS * device_sm_count());
 	cudaError_t e = cudaMemcpyAsync(queue, &ctas, sizeof(int), cudaMemcpyHostToDevice, stream);  // pageable: staged by the driver
 	if (e != cudaSuccess) return e;
 	track_multi_kernel<<<ctas, SB_THREADS, smem, stream>>>(descs, work, n_work, P, queue);
