@@ -17,10 +17,14 @@ t = S.events["t_us"]
 bounds = [(int(np.searchsorted(t, S.frame_ts[k], "left")),
            int(np.searchsorted(t, S.frame_ts[k + 1], "left")) if k + 1 < nF else len(S.events)) for k in range(nF)]
 tr = Tracker(w, h, feat, record_capacity=1 << 20)
+MODE = int(sys.argv[2]) if len(sys.argv) > 2 else 2
+tr.set_stream_kernel(MODE)
+SLOTS = 148 * 3 if MODE == 0 else 148 * 4  # resident feature slots: 3 CTAs/SM, or 2 CTAs x 2 leaders
 flows = bench.FlowCache(S)
 d_events = torch.from_numpy(S.events.view(np.uint8).reshape(-1).copy()).cuda()
 d_frames = [torch.from_numpy(f.copy()).cuda() for f in S.frames]
 rows = []
+raw = []
 
 
 def step(collect):
@@ -37,6 +41,7 @@ def step(collect):
         if collect:
             ids, nopt, t0, t1, sm = tr.feature_load()
             ran = t1 > 0
+            raw.append(dict(push=k, ids=ids.copy(), nopt=nopt.copy(), t0=t0.copy(), t1=t1.copy(), sm=sm.copy()))
             rows.append((k, nopt[ran].copy(), t0[ran].astype(np.int64), t1[ran].astype(np.int64), sm[ran].copy()))
 
 
@@ -57,7 +62,8 @@ for k, nopt, t0, t1, sm in rows:
     late = t0 > t0.min() + 100_000  # CTAs that had to wait for a free slot
     r = dict(push=k, ctas=int(len(nopt)), opts=int(nopt.sum()), span_us=float(span), mean_cta_us=float(dur.mean()),
              max_cta_us=float(dur.max()), max_cta_opts=int(nopt[heavy]), max_opts=int(nopt.max()),
-             mean_opts=float(nopt.mean()), balanced_bound_us=float(dur.sum() / (148 * 3)),
+             mean_opts=float(nopt.mean()), balanced_bound_us=float(dur.sum() / SLOTS), busy_fraction=float(dur.sum() / (min(SLOTS, len(dur)) * span)),
+             opts_p50=float(np.median(nopt)), opts_p90=float(np.percentile(nopt, 90)), opts_p99=float(np.percentile(nopt, 99)),
              us_per_opt_top10pct=float(dur[top].sum() / max(nopt[top].sum(), 1)),
              us_per_opt_bottom_half=float(dur[bot].sum() / max(nopt[bot].sum(), 1)),
              late_start_us=float((t0.max() - t0.min()) / 1e3), ctas_per_sm_max=int(per_sm.max()),
@@ -67,3 +73,8 @@ for k, nopt, t0, t1, sm in rows:
     print(json.dumps(r))
 os.makedirs("gpurun_out", exist_ok=True)
 json.dump(out, open(f"gpurun_out/load_profile_{WL}.json", "w"), indent=1)
+np.savez(f"gpurun_out/load_raw_{WL}.npz", **{f"{key}{r['push']}": r[key] for r in raw for key in ("ids", "nopt", "t0", "t1", "sm")})
+# how well last push's count predicts this push's (the work order is built from it)
+for (k0, n0, *_), (k1, n1, *_) in zip(rows[1:-1], rows[2:]):
+    if len(n0) == len(n1):
+        print(f"push {k1}: corr(prev, this) = {np.corrcoef(n0, n1)[0, 1]:.3f}, mean |diff| = {np.abs(n1 - n0).mean():.2f}")
