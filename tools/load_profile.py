@@ -25,6 +25,7 @@ d_events = torch.from_numpy(S.events.view(np.uint8).reshape(-1).copy()).cuda()
 d_frames = [torch.from_numpy(f.copy()).cuda() for f in S.frames]
 rows = []
 raw = []
+pre = []
 
 
 def step(collect):
@@ -37,8 +38,10 @@ def step(collect):
             tr.set_flows(ids, found, nxt)
         tr.new_frame_end()
         lo, hi = bounds[k]
+        before = tr.tracks() if collect else None
         tr.push_events_device(d_events.data_ptr() + lo * 16, hi - lo)
         if collect:
+            pre.append(before)
             ids, nopt, t0, t1, sm = tr.feature_load()
             ran = t1 > 0
             raw.append(dict(push=k, ids=ids.copy(), nopt=nopt.copy(), t0=t0.copy(), t1=t1.copy(), sm=sm.copy()))
@@ -74,6 +77,7 @@ for k, nopt, t0, t1, sm in rows:
 os.makedirs("gpurun_out", exist_ok=True)
 json.dump(out, open(f"gpurun_out/load_profile_{WL}.json", "w"), indent=1)
 np.savez(f"gpurun_out/load_raw_{WL}.npz", **{f"{key}{r['push']}": r[key] for r in raw for key in ("ids", "nopt", "t0", "t1", "sm")})
+np.savez(f"gpurun_out/load_pre_{WL}.npz", **{f"t{i}": b for i, b in enumerate(pre)})
 # how well last push's count predicts this push's (the work order is built from it)
 for (k0, n0, *_), (k1, n1, *_) in zip(rows[1:-1], rows[2:]):
     if len(n0) == len(n1):
