@@ -1124,11 +1124,14 @@ int ebt_new_frame_end_multi(ebt_ctx* const* ctxs, int n_streams)
 	if (!ctx) return EBT_E_INVALID;
 	for (int i = 0; i < n_streams; ++i)
 		if (!ctxs[i]) return fail(ctx, EBT_E_INVALID, "ebt_new_frame_end_multi: null context");
-	int result = EBT_OK;
-	for (int i = 0; i < n_streams && result == EBT_OK; ++i) result = frameEndEnqueue(ctxs[i]);
-	for (int i = 0; i < n_streams; ++i)
+	int result = EBT_OK, queued = 0;
+	for (; queued < n_streams && result == EBT_OK; ++queued) result = frameEndEnqueue(ctxs[queued]);
+	if (result != EBT_OK) --queued;  // that one failed part-way: its staging buffer holds nothing to take back
+	// every stream whose work was queued is finished, also after a failure elsewhere; the streams
+	// behind a failed one were not touched and keep their state for a retry
+	for (int i = 0; i < queued; ++i)
 	{
-		const int rc = frameEndFinish(ctxs[i]);  // also after a failed enqueue elsewhere: every stream is drained
+		const int rc = frameEndFinish(ctxs[i]);
 		if (rc != EBT_OK && result == EBT_OK) result = rc;
 	}
 	if (result != EBT_OK)
