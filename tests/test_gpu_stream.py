@@ -175,10 +175,13 @@ def test_stream_shared_pixel_warps_few_features():
 
 
 @pytest.mark.gpu
-def test_multi_stream_push_equals_the_streams_alone():
+@pytest.mark.parametrize("one_with_products", [False, True])
+def test_multi_stream_push_equals_the_streams_alone(one_with_products):
     """ebt_push_events_multi (configs[3]: independent streams in one launch): three streams of different
     seeds, feature counts and batch sizes — one of them runs out of events early — each equal to the
-    CPU oracle's per-event loop on that stream alone."""
+    CPU oracle's per-event loop on that stream alone.  With the getter-only patch products switched on in
+    one context the call takes the one-CTA-per-feature kernel for every stream (the shared-pixel-warp
+    kernel does not produce them) and must give the same tracks."""
     from event_based_odomety_b200.cabi import new_frame_end_multi, push_events_multi
     streams = [synth.make_stream(240, 180, 0.15, 500e3, seed=2000, max_corners=69),
                synth.make_stream(240, 180, 0.15, 300e3, seed=2001, max_corners=40),
@@ -186,6 +189,8 @@ def test_multi_stream_push_equals_the_streams_alone():
     caps = [100, 100, 60]
     cpus = [CpuTracker(load_oracle(), S.width, S.height, c) for S, c in zip(streams, caps)]
     gpus = [Tracker(S.width, S.height, c) for S, c in zip(streams, caps)]
+    if one_with_products:
+        gpus[1].set_products(1)
     n_cpu = [synth.run_stream(c, S) for c, S in zip(cpus, streams)]
     n_gpu = [0, 0, 0]
     n_frames = max(len(S.frames) for S in streams)
@@ -251,6 +256,57 @@ def test_stream_c3_shape():
     frame intervals; the CPU oracle needs about a minute for them)."""
     S = synth.make_stream(640, 480, 0.09, 10e6, seed=1003, max_corners=2000)
     compare(S, 2000, n_frames=2)
+
+
+@pytest.mark.gpu
+def test_stream_c3_full_size_properties():
+    """BASELINE.json configs[2] at the size bench.py runs it (0.3 s, ~3 M events, 2000 features, ~3e5
+    optimisations) — too long for the CPU checkers inside a test, so properties that do not depend on the
+    size: (i) the persistent shared-pixel-warp kernel and the one-CTA-per-feature kernel make the same
+    optimisations at the same events and agree to 1e-9 px; (ii) cutting every batch in three pieces changes
+    nothing, bit for bit (the kernels are sequential in a feature's events); (iii) every track's
+    optimisations come at strictly increasing stream events inside the pushed range, on live tracks only."""
+    S = synth.make_stream(640, 480, 0.30, 10e6, seed=1003, max_corners=2000)
+
+    class Split:
+        def __init__(self, g):
+            self.g = g
+
+        def __getattr__(self, k):
+            return getattr(self.g, k)
+
+        def push_events(self, ev):
+            return sum(self.g.push_events(part) for part in np.array_split(ev, 3))
+
+    def run(mode, split=False):
+        g = Tracker(S.width, S.height, 2000, record_capacity=1 << 20)
+        g.set_stream_kernel(mode)
+        n = synth.run_stream(Split(g) if split else g, S)
+        r = g.records().copy()
+        live, arch = g.tracks(False).copy(), g.tracks(True).copy()
+        g.close()
+        assert n == len(r)
+        return r, live, arch
+
+    a, live_a, arch_a = run(2)
+    b, live_b, arch_b = run(0)
+    c, live_c, arch_c = run(2, split=True)
+    assert len(a) > 200000
+    # (ii)
+    assert a.tobytes() == c.tobytes() and live_a.tobytes() == live_c.tobytes() and arch_a.tobytes() == arch_c.tobytes()
+    # (i)
+    for k in ("track_id", "event_index", "ts", "num_of_events", "lost", "n_successful", "n_unsuccessful", "termination"):
+        assert np.array_equal(a[k], b[k]), k
+    assert np.hypot(a["x"] - b["x"], a["y"] - b["y"]).max() < 1e-9
+    assert _angle_diff_deg(a["flow_dir"], b["flow_dir"]).max() < 1e-7
+    assert np.array_equal(live_a["track_id"], live_b["track_id"]) and np.array_equal(arch_a["track_id"], arch_b["track_id"])
+    # (iii)
+    assert a["event_index"].min() >= 0 and a["event_index"].max() < len(S.events)
+    order = np.lexsort((np.arange(len(a)), a["track_id"]))
+    t, e, lost = a["track_id"][order], a["event_index"][order], a["lost"][order]
+    same = t[1:] == t[:-1]
+    assert (e[1:][same] > e[:-1][same]).all()
+    assert not lost[:-1][same].any()  # nothing is optimised after the record that lost it
 
 
 @pytest.mark.gpu
