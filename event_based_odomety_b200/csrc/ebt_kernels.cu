@@ -598,14 +598,24 @@ __device__ __forceinline__ double sqrt_fast(double x)
 	return fma(fma(-s, s, x), 0.5 * y, s);
 }
 
+// Paths that are (almost) never taken on real data are kept out of line.  Inlined, each of them sits in
+// the middle of the leader's trust-region loop with a library call inside; with the three below behind
+// calls the c3 stream kernel runs 5 % faster (60.2 -> 57.0 ms per step, profiles/r2_variants.md 7).
+#ifndef EBT_COLD
+#define EBT_COLD __noinline__
+#endif
+
 // sin and cos for the leader's chain: Cody-Waite reduction by pi/2 (three FMA
 // terms, exact products) and the fdlibm kernel polynomials on [-pi/4, pi/4];
 // < 1.5 ulp, no slow-path call for |x| < 1e6 (angles here are a few radians).
+// (the library routine for huge / non-finite arguments stays out of line: it is never taken
+// on real data and would otherwise be copied into each of the five places this inlines)
+__device__ EBT_COLD void sincos_huge(double x, double* sn, double* cs) { sincos(x, sn, cs); }
 __device__ __forceinline__ void sincos_fast(double x, double* sn, double* cs)
 {
 	if (!(fabs(x) < 1e6))
 	{
-		sincos(x, sn, cs);
+		sincos_huge(x, sn, cs);
 		return;
 	}
 	const double q = rint(x * 0.6366197723675814);
@@ -632,6 +642,14 @@ __device__ __forceinline__ void sincos_fast(double x, double* sn, double* cs)
 	const double cv = (n & 1) ? s0 : c0;
 	*sn = (n & 2) ? -sv : sv;
 	*cs = ((n + 1) & 2) ? -cv : cv;
+}
+
+// fmod(phi, 2 pi) (optimizer.cpp:170): for |phi| < 2 pi — every solve but a handful — fmod returns
+// its argument; the library loop for the rest stays out of line.
+__device__ EBT_COLD double wrap_flow_cold(double phi) { return fmod(phi, 2 * 3.14159265358979323846); }
+__device__ __forceinline__ double wrap_flow(double phi)
+{
+	return fabs(phi) < 2 * 3.14159265358979323846 ? phi : wrap_flow_cold(phi);
 }
 
 __device__ __forceinline__ void post_request(FeatShared& sh, int kind, const double (&x)[5], double vx,
@@ -954,6 +972,22 @@ __device__ __forceinline__ double norm5(const double (&a)[5])
 	return sqrt_fast(s);
 }
 
+// max |x - Plus(x, -g)| in full.  Out of line (EBT_COLD): the lower bound in scale_system decides
+// the gradient-tolerance test on all but a handful of iterations, and inlined this is ~260
+// instructions (a Plus with its sincos) in the middle of the trust-region loop, twice.
+__device__ EBT_COLD double projected_gradient_norm(double x0, double x1, double x2, double x3, double x4, double g0,
+												   double g1, double g2, double g3)
+{
+	const double x[5] = {x0, x1, x2, x3, x4};
+	const double ng[4] = {-g0, -g1, -g2, -g3};
+	double xp[5];
+	plus5(x, ng, xp);
+	double mx = 0;
+#pragma unroll
+	for (int k = 0; k < 5; ++k) mx = sel_max(mx, fabs(x[k] - xp[k]));
+	return mx;
+}
+
 // Scaled system of EvaluateGradientAndJacobian (ceres/internal/ceres/
 // trust_region_minimizer.cc:231-288): Jacobi column scaling fixed at iteration
 // 0, Hs = S H S, gs = S g, and the projected gradient max norm
@@ -983,14 +1017,7 @@ __device__ __forceinline__ void scale_system(const double (&x)[5], bool iter0, c
 		grad_max_norm = fabs(g[3]);
 		return;
 	}
-	double ng[4], xp[5];
-#pragma unroll
-	for (int q = 0; q < 4; ++q) ng[q] = -g[q];
-	plus5(x, ng, xp);
-	double mx = 0;
-#pragma unroll
-	for (int k = 0; k < 5; ++k) mx = sel_max(mx, fabs(x[k] - xp[k]));
-	grad_max_norm = mx;
+	grad_max_norm = projected_gradient_norm(x[0], x[1], x[2], x[3], x[4], g[0], g[1], g[2], g[3]);
 }
 
 // TrustRegionMinimizer::Minimize (trust_region_minimizer.cc:67-121 and helpers
@@ -1012,7 +1039,10 @@ __device__ void lm_solve(SH& sh, const DevParams& P, double (&params)[5], LmSumm
 	double Hm[10], g[4];
 	double Hs[10], gs[4], scale[4] = {1, 1, 1, 1}, diag[4] = {0, 0, 0, 0};
 	double x_cost = DBL_MAX, minimum_cost = DBL_MAX, x_norm = -1;
-	double radius = P.initial_radius, decrease_factor = 2.0;
+	// decrease_factor_ of the trust-region strategy is 2, 4, 8, ...: its reciprocal is kept instead, so
+	// that radius / decrease_factor is one exact multiplication (same bits: a power of two, no underflow
+	// above min_radius) and no IEEE division sits in the loop
+	double radius = P.initial_radius, inv_decrease = 0.5;
 	bool reuse_diagonal = false;
 	int consecutive_invalid = 0;
 	double grad_max_norm = 0, final_cost = DBL_MAX;
@@ -1109,8 +1139,8 @@ __device__ void lm_solve(SH& sh, const DevParams& P, double (&params)[5], LmSumm
 				failed = true;
 				break;
 			}
-			radius /= decrease_factor;
-			decrease_factor *= 2.0;
+			radius *= inv_decrease;
+			inv_decrease *= 0.5;
 			iter_cost = x_cost;
 			continue;
 		}
@@ -1162,8 +1192,8 @@ __device__ void lm_solve(SH& sh, const DevParams& P, double (&params)[5], LmSumm
 		if (!(rho > P.min_relative_decrease))
 		{
 			// HandleUnsuccessfulStep
-			radius /= decrease_factor;
-			decrease_factor *= 2.0;
+			radius *= inv_decrease;
+			inv_decrease *= 0.5;
 			iter_cost = cand_cost;
 			continue;
 		}
@@ -1184,7 +1214,7 @@ __device__ void lm_solve(SH& sh, const DevParams& P, double (&params)[5], LmSumm
 			const double t = 2.0 * rho - 1.0;
 			radius = sel_min(P.max_radius, radius * rcp_fast(sel_max(1.0 / 3.0, 1.0 - t * t * t)));
 		}
-		decrease_factor = 2.0;
+		inv_decrease = 0.5;
 		reuse_diagonal = false;
 		se_cur = cand_cost;
 		se_acc_cand += model_cost_change;
@@ -1465,7 +1495,7 @@ __device__ EBT_NOINLINE void optimize_feature(FeatShared& sh, double* costs, Fea
 			return;
 		}
 	}
-	st.flow = fmod(x[4], 2 * 3.14159265358979323846);
+	st.flow = wrap_flow(x[4]);
 #pragma unroll
 	for (int k = 0; k < 4; ++k) st.warp[k] = x[k];
 	st.init = 1;
@@ -2350,7 +2380,7 @@ __device__ void sb_optimize(SlotShared& S, const ebt_problem& pr, const ebt_even
 	L.filtered = 0;
 	lm_solve(S, P, x, L);
 	// post-solve (optimizer.cpp:127-189); one final cost => the cost filter cannot fire
-	st.flow = fmod(x[4], 2 * 3.14159265358979323846);
+	st.flow = wrap_flow(x[4]);
 #pragma unroll
 	for (int k = 0; k < 4; ++k) st.warp[k] = x[k];
 	update_rect(st);
@@ -2713,7 +2743,7 @@ __device__ void mq_optimize(StreamSlot& S, FeatState& st, const double2* grid, c
 			return;
 		}
 	}
-	st.flow = fmod(x[4], 2 * 3.14159265358979323846);
+	st.flow = wrap_flow(x[4]);
 #pragma unroll
 	for (int k = 0; k < 4; ++k) st.warp[k] = x[k];
 	st.init = 1;
