@@ -278,16 +278,8 @@ __device__ __forceinline__ void sample_taps(const double2* __restrict__ grid, in
 			gc1 += wr[r] * d1;
 		}
 	}
-	// the two 0.5 factors cr_weights leaves out
-	g0 *= 0.25;
-	g1 *= 0.25;
-	if (JAC)
-	{
-		gr0 *= 0.25;
-		gr1 *= 0.25;
-		gc0 *= 0.25;
-		gc1 *= 0.25;
-	}
+	// the two 0.5 factors cr_weights leaves out are applied by the caller (eval_pixels scales the flow
+	// direction instead: a factor 0.25 is exact wherever it is applied)
 }
 
 // The same sums from the staged tile: `base` = texel (row - 1, col - 1) in shared
@@ -326,15 +318,6 @@ __device__ __forceinline__ void sample_taps_tile(const double2* base, const doub
 			gc0 += wr[r] * d0;
 			gc1 += wr[r] * d1;
 		}
-	}
-	g0 *= 0.25;
-	g1 *= 0.25;
-	if (JAC)
-	{
-		gr0 *= 0.25;
-		gr1 *= 0.25;
-		gc0 *= 0.25;
-		gc1 *= 0.25;
 	}
 }
 
@@ -474,6 +457,12 @@ __device__ __forceinline__ void eval_pixels(const double2* __restrict__ grid, in
 	return;
 #endif
 	const double cs = x[0], sn = x[1], tx = x[2], ty = x[3];
+	// The samplers return 4x the interpolated values (the two 0.5 factors of the Catmull-Rom weights
+	// are left out); everything below is linear in (vx, vy), so the factor goes onto the flow direction
+	// once per pass instead of onto six sums per pixel.  A power of two is exact wherever it is
+	// applied: the results are bit-identical.
+	vx *= 0.25;
+	vy *= 0.25;
 #pragma unroll
 	for (int k = 0; k < (JAC ? 20 : 2); ++k) acc[k] = 0.0;
 #pragma unroll kPixUnroll
