@@ -260,39 +260,39 @@ class FeatureDetector
 		{
 			Patch p(Corner(k.rect_x + EBT_PATCH_EXTENT, k.rect_y + EBT_PATCH_EXTENT), EBT_PATCH_EXTENT,
 					common::timestamp_t(k.current_ts));
-			p.init_ = k.init != 0;
-			p.lost_ = k.lost != 0;
-			p.trackId_ = k.track_id;
-			p.initPoint_ = common::Point2d(k.init_x, k.init_y);
-			p.timeLastUpdate_ = common::timestamp_t(k.time_last_update);
-			p.timeWithoutUpdate_ = common::timestamp_t(k.time_without_update);
-			p.initTime_ = common::timestamp_t(k.init_time);
-			p.numOfEvents_ = static_cast<size_t>(k.num_of_events);
-			p.flowDir_ = k.flow_dir;
-			p.warp_ = common::Pose2d(Sophus::SO2d(k.warp[0], k.warp[1]), Eigen::Vector2d(k.warp[2], k.warp[3]));
+			p.v_.has_flow = k.init != 0;
+			p.v_.lost = k.lost != 0;
+			p.v_.id = k.track_id;
+			p.v_.origin = common::Point2d(k.init_x, k.init_y);
+			p.v_.last_update = common::timestamp_t(k.time_last_update);
+			p.v_.stale_after = common::timestamp_t(k.time_without_update);
+			p.v_.created = common::timestamp_t(k.init_time);
+			p.v_.window = static_cast<size_t>(k.num_of_events);
+			p.v_.flow_angle = k.flow_dir;
+			p.v_.warp = common::Pose2d(Sophus::SO2d(k.warp[0], k.warp[1]), Eigen::Vector2d(k.warp[2], k.warp[3]));
 			std::vector<double> xyt(static_cast<size_t>(k.n_trajectory) * 3);
 			int m = 0;
 			check(ebt_get_trajectory(ctx_, k.track_id, xyt.data(), k.n_trajectory, &m), "ebt_get_trajectory");
-			p.trajectory_.clear();
+			p.v_.path.clear();
 			for (int i = 0; i < k.n_trajectory; ++i)
-				p.trajectory_.emplace_back(common::Point2d(xyt[3 * i], xyt[3 * i + 1]),
+				p.v_.path.emplace_back(common::Point2d(xyt[3 * i], xyt[3 * i + 1]),
 										   common::timestamp_t(static_cast<int64_t>(xyt[3 * i + 2])));
-			p.finalCosts_.resize(static_cast<size_t>(k.n_optimizations));
-			check(ebt_get_final_costs(ctx_, k.track_id, p.finalCosts_.data(), k.n_optimizations, &m), "ebt_get_final_costs");
+			p.v_.costs.resize(static_cast<size_t>(k.n_optimizations));
+			check(ebt_get_final_costs(ctx_, k.track_id, p.v_.costs.data(), k.n_optimizations, &m), "ebt_get_final_costs");
 			check(ebt_get_patch(ctx_, k.track_id, 0, buf.data()), "ebt_get_patch");
-			p.integratedNabla_ = toMat(buf, EBT_PATCH_SIDE, EBT_PATCH_SIDE);
+			p.v_.events_patch = toMat(buf, EBT_PATCH_SIDE, EBT_PATCH_SIDE);
 			if (products)
 			{
 				check(ebt_get_patch(ctx_, k.track_id, 1, buf.data()), "ebt_get_patch");
-				p.motionCompensatedIntegratedNabla_ = toMat(buf, EBT_PATCH_SIDE, EBT_PATCH_SIDE);
+				p.v_.compensated_patch = toMat(buf, EBT_PATCH_SIDE, EBT_PATCH_SIDE);
 				check(ebt_get_patch(ctx_, k.track_id, 2, buf.data()), "ebt_get_patch");
-				p.predictedNabla_ = toMat(buf, EBT_PATCH_SIDE, EBT_PATCH_SIDE);
+				p.v_.predicted_patch = toMat(buf, EBT_PATCH_SIDE, EBT_PATCH_SIDE);
 			}
 			if (params_.optimizerParams.drawCostMap && k.n_optimizations > 0)
 			{
 				std::vector<double> cm(121);
 				check(ebt_get_cost_map(ctx_, k.track_id, cm.data()), "ebt_get_cost_map");
-				p.costMap_ = toMat(cm, 11, 11);
+				p.v_.cost_map = toMat(cm, 11, 11);
 			}
 			dst.push_back(std::move(p));
 		}

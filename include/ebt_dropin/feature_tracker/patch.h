@@ -39,69 +39,81 @@ using TrackId = int32_t;
 class Patch
 {
    public:
-	// Patch::Patch + init (patch.cpp:8-35): a fresh patch around `corner`
-	Patch(const Corner& corner, int extent, const common::timestamp_t& timestamp)
-		: currentTimestamp_(timestamp), initTime_(timestamp)
+	// What a snapshot holds: the tracker's state of one patch as the C-ABI reports it (ebt_track,
+	// ebt_get_patch, ebt_get_trajectory, ebt_get_final_costs), in the reference's types.  The
+	// drop-in FeatureDetector fills it; the reference's callers only see the getters below.
+	struct View
 	{
-		patch_ = cv::Rect2d(corner.x - extent, corner.y - extent, 2 * extent + 1, 2 * extent + 1);
-		initPoint_ = toCorner();
-		integratedNabla_ = cv::Mat::zeros(static_cast<int>(patch_.height), static_cast<int>(patch_.width), CV_64F);
-		motionCompensatedIntegratedNabla_ = integratedNabla_.clone();
-		predictedNabla_ = integratedNabla_.clone();
-		costMap_ = cv::Mat::zeros(1, 1, CV_64F);
-		trajectory_.emplace_back(toCorner(), currentTimestamp_);
+		cv::Rect2d rect;                  // 25x25 window in image coordinates (top-left, size)
+		common::Point2d origin;           // where the patch was created
+		TrackId id = -1;
+		bool has_flow = false;            // LK flow / warp initialised (Patch::init_)
+		bool lost = false;
+		size_t window = 75;               // events per optimisation window (patch.cpp:22)
+		double flow_angle = 0;            // rad
+		common::Pose2d warp;
+		common::timestamp_t now{0}, last_update{0}, created{0};
+		common::timestamp_t stale_after{static_cast<int64_t>(1e7)};
+		cv::Mat events_patch;             // integrated event polarities
+		cv::Mat compensated_patch;        // the same, motion compensated (getter-only product)
+		cv::Mat predicted_patch;          // template gradient under the current warp and flow (getter-only product)
+		cv::Mat cost_map;                 // 11x11 sweep, when OptimizerParams::drawCostMap is on
+		std::vector<common::Sample<common::Point2d>> path;  // image-time samples and kept optimisations
+		std::vector<double> costs;        // final cost of every optimisation
+	};
+
+	// Patch::Patch + init (patch.cpp:8-35): a fresh patch of half-width `extent` around `corner`
+	Patch(const Corner& corner, int extent, const common::timestamp_t& timestamp)
+	{
+		const double side = 2 * extent + 1;
+		v_.rect = cv::Rect2d(corner.x - extent, corner.y - extent, side, side);
+		v_.now = v_.created = timestamp;
+		v_.origin = toCorner();
+		v_.events_patch = cv::Mat::zeros(static_cast<int>(side), static_cast<int>(side), CV_64F);
+		v_.compensated_patch = v_.events_patch.clone();
+		v_.predicted_patch = v_.events_patch.clone();
+		v_.cost_map = cv::Mat::zeros(1, 1, CV_64F);
+		v_.path.emplace_back(v_.origin, timestamp);
 	}
 
-	Corner toCorner() const { return Corner(patch_.x + (patch_.width - 1) / 2., patch_.y + (patch_.height - 1) / 2.); }
-	bool isInPatch(const common::Point2i& point) const { return patch_.contains(point); }
-	bool isLost() const { return lost_; }
-
-	cv::Mat const& getIntegratedNabla() const { return integratedNabla_; }
-	cv::Mat const& getPredictedNabla() const { return predictedNabla_; }
-	cv::Mat const& getCompenatedIntegratedNabla() const { return motionCompensatedIntegratedNabla_; }
-	cv::Rect2d const& getPatch() const { return patch_; }
-	TrackId getTrackId() const { return trackId_; }
-	const common::Pose2d& getWarp() const { return warp_; }
-	float getFlow() const { return static_cast<float>(flowDir_); }
-	const cv::Mat& getCostMap() const { return costMap_; }
-	bool isInit() { return init_; }
-	std::vector<common::Sample<common::Point2d>> const& getTrajectory() const { return trajectory_; }
-	size_t getNumOfEvents() const { return numOfEvents_; }
+	// ---- geometry (patch.cpp:161-176)
+	Corner toCorner() const { return Corner(v_.rect.x + (v_.rect.width - 1) / 2., v_.rect.y + (v_.rect.height - 1) / 2.); }
+	cv::Rect2d const& getPatch() const { return v_.rect; }
 	cv::Rect2d getInitPatch() const
 	{
-		return cv::Rect2d(initPoint_.x - (patch_.width - 1) / 2., initPoint_.y - (patch_.height - 1) / 2., patch_.width,
-						  patch_.height);
+		const double hw = (v_.rect.width - 1) / 2., hh = (v_.rect.height - 1) / 2.;
+		return cv::Rect2d(v_.origin.x - hw, v_.origin.y - hh, v_.rect.width, v_.rect.height);
 	}
-	common::timestamp_t getCurrentTimestamp() const { return currentTimestamp_; }
-	common::timestamp_t getTimeWithoutUpdate() const { return timeWithoutUpdate_; }
-	const std::vector<double>& getFinalCosts() const { return finalCosts_; }
-	common::timestamp_t getTimeLastUpdate() const { return timeLastUpdate_; }
-	common::timestamp_t getInitTime() const { return initTime_; }
+	bool isInPatch(const common::Point2i& point) const { return v_.rect.contains(point); }
 
-	void setLost() { lost_ = true; }
-	void setTrackId(TrackId trackId) { trackId_ = trackId; }
-	void setTs(const common::timestamp_t& ts) { currentTimestamp_ = ts; }
+	// ---- identity and life cycle
+	TrackId getTrackId() const { return v_.id; }
+	void setTrackId(TrackId trackId) { v_.id = trackId; }
+	bool isInit() { return v_.has_flow; }
+	bool isLost() const { return v_.lost; }
+	void setLost() { v_.lost = true; }
+	common::timestamp_t getInitTime() const { return v_.created; }
+	common::timestamp_t getCurrentTimestamp() const { return v_.now; }
+	void setTs(const common::timestamp_t& ts) { v_.now = ts; }
+	common::timestamp_t getTimeLastUpdate() const { return v_.last_update; }
+	common::timestamp_t getTimeWithoutUpdate() const { return v_.stale_after; }
+
+	// ---- what the optimiser estimated (the reference reads the flow back as a float, patch.h:54)
+	const common::Pose2d& getWarp() const { return v_.warp; }
+	float getFlow() const { return static_cast<float>(v_.flow_angle); }
+	size_t getNumOfEvents() const { return v_.window; }
+	const std::vector<double>& getFinalCosts() const { return v_.costs; }
+	std::vector<common::Sample<common::Point2d>> const& getTrajectory() const { return v_.path; }
+
+	// ---- 25x25 images (CV_64F) and the cost map
+	cv::Mat const& getIntegratedNabla() const { return v_.events_patch; }
+	cv::Mat const& getCompenatedIntegratedNabla() const { return v_.compensated_patch; }
+	cv::Mat const& getPredictedNabla() const { return v_.predicted_patch; }
+	const cv::Mat& getCostMap() const { return v_.cost_map; }
 
    private:
 	friend class FeatureDetector;
-	bool init_ = false;
-	bool lost_ = false;
-	cv::Rect2d patch_;
-	common::Point2d initPoint_;
-	TrackId trackId_ = -1;
-	common::timestamp_t currentTimestamp_{0};
-	common::timestamp_t timeLastUpdate_{0};
-	common::timestamp_t timeWithoutUpdate_{static_cast<int64_t>(1e7)};
-	common::timestamp_t initTime_{0};
-	size_t numOfEvents_ = 75;
-	cv::Mat integratedNabla_;
-	cv::Mat motionCompensatedIntegratedNabla_;
-	cv::Mat predictedNabla_;
-	cv::Mat costMap_;
-	double flowDir_ = 0;
-	common::Pose2d warp_;
-	std::vector<common::Sample<common::Point2d>> trajectory_;
-	std::vector<double> finalCosts_;
+	View v_;
 };
 
 using Patches = std::list<Patch>;
